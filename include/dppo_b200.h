@@ -1,0 +1,136 @@
+/*
+ * dppo_b200.h - C ABI of the B200-native PPO update path (libdppo_b200.so).
+ *
+ * The reference (kibeomKim/Pytorch-DPPO) is pure Python on torch CPU and has no
+ * FFI of its own; every entry point below replaces an inline block of the
+ * reference, cited as file:line.  The Python modules in pytorch-dppo_b200/
+ * (model.py, train.py, chief.py, ppo.py, utils.py - same names as the
+ * reference's) bind these with ctypes; INTEGRATION.md shows the stub.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - the library owns no device memory: the caller allocates inputs, outputs
+ *     and scratch (sizes from the *_scratch_bytes queries) and keeps them
+ *     alive until the stream has drained;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*)
+ *     and may be captured in a CUDA graph;
+ *   - return value: 0 = ok, < 0 = DPPO_E_* argument error, > 0 = cudaError_t;
+ *   - all arithmetic is IEEE fp32 unless stated (no fast-math), indices int32;
+ *   - one host thread per device.
+ */
+#ifndef DPPO_B200_H
+#define DPPO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DPPO_E_BADARG    (-1)   /* null pointer, negative size, unknown flavour */
+#define DPPO_E_TOOLARGE  (-2)   /* a dimension beyond what the kernels are built for */
+#define DPPO_E_SCRATCH   (-3)   /* scratch buffer smaller than *_scratch_bytes says */
+#define DPPO_E_ALIGN     (-4)   /* pointer not aligned as documented */
+#define DPPO_E_COMM      (-5)   /* communicator misuse */
+
+#define DPPO_FLAVOUR_DPPO 0     /* train.py:140-166: per-dim pdf ratio, clipped value loss */
+#define DPPO_FLAVOUR_PPO  1     /* ppo.py:147-172 : log-prob ratio, plain value loss, entropy */
+
+#define DPPO_N_PARAMS 13        /* model.py:14-22 */
+
+/* Network shape.  Policy trunk O->H1->H2->A, value trunk O->G1->G2->1
+ * (model.py:11-22 hard-codes H1=H2=100, G1=500, G2=100). */
+typedef struct dppo_dims {
+    int O, A, H1, H2, G1, G2;
+} dppo_dims;
+
+int         dppo_version(void);
+const char* dppo_error_string(int code);
+
+/* Flat parameter bucket.  The 13 tensors are laid out in named_parameters()
+ * order (log_std, p_fc1.{weight,bias}, p_fc2.*, v_fc1.*, v_fc2.*, mu.*, v.*;
+ * model.py:14-22), weights row-major (out,in) as nn.Linear stores them, each
+ * tensor starting on a 16-byte boundary (padding floats stay 0).  Fills
+ * offsets_host[13] / sizes_host[13] (in floats) and returns the padded length
+ * P_pad, or a DPPO_E_* code. */
+int dppo_param_layout(const dppo_dims* d, int* offsets_host, int* sizes_host);
+
+/* ---- K1: GAE / returns -------------------------------------------------
+ * Replaces the reverse Python loop train.py:113-122 / ppo.py:124-133 for all
+ * segments of a rollout buffer at once.
+ *   rewards[T], values[T]   r_i (already clipped, train.py:96) and V(s_i)
+ *   seg_end[T] (uint8)      1 on the last step of a segment (done, or num_steps
+ *                           reached); element T-1 is always treated as one
+ *   boot[T]                 read only where seg_end: V_{i+1} there (0 if done,
+ *                           else the bootstrap value, train.py:109-112)
+ *   adv[T], ret[T]          A_i = td_i + (gamma*lam) A_{i+1},  R_i = A_i + V_i
+ * scratch: dppo_gae_scratch_bytes(T) bytes; contents need not be initialised. */
+size_t dppo_gae_scratch_bytes(int64_t T);
+int dppo_gae_scan(const float* rewards, const float* values, const float* boot, const uint8_t* seg_end,
+                  float* adv, float* ret, int64_t T, double gamma, double lam,
+                  void* scratch, size_t scratch_bytes, void* stream);
+
+/* ---- K4: running observation statistics --------------------------------
+ * Replaces Shared_obs_stats.observes + normalize (model.py:68-80) applied row
+ * by row to a rollout of T observations: row t is normalised with the
+ * statistics that include rows 0..t, then clamped to [-5,5].
+ *   obs[T*O] row-major raw observations, out[T*O] normalised (may alias obs)
+ *   n[O], mean[O], mean_diff[O], var[O]: the four state vectors, updated in
+ *   place to the state after row T-1 (n is a vector in the reference; all its
+ *   entries are equal and n[0] is the one read).  Faithful while n < 2^24.
+ * Prefix sums are carried in fp64, the normalisation itself is fp32. */
+size_t dppo_welford_scratch_bytes(int64_t T, int O);
+int dppo_welford(const float* obs, float* out, int64_t T, int O,
+                 float* n, float* mean, float* mean_diff, float* var,
+                 void* scratch, size_t scratch_bytes, void* stream);
+
+/* ---- K2: fused minibatch gather + actor-critic forward/backward + losses --
+ * Replaces ReplayMemory.sample (train.py:31-33) + train.py:140-166 (flavour
+ * DPPO) or ppo.py:147-172 (flavour PPO) + Model.forward (model.py:35-45) and
+ * the autograd backward.  One launch = one minibatch ("epoch" in the
+ * reference's wording).
+ *   obs[T*O], act[T*A], adv[T], ret[T], logp_old[T] (PPO flavour only)
+ *                         the rollout buffer, struct-of-arrays
+ *   idx[B]                positions to gather (Python random.sample order)
+ *   theta, theta_old      flat parameter buckets (theta_old: DPPO flavour only,
+ *                         the lagging copy train.py:128-129,164)
+ *   partials              OUT [nparts][P_pad] per-CTA gradient partial sums,
+ *                         nparts = dppo_update_nparts(B); their sum in index
+ *                         order is the gradient (done by dppo_reduce_adam)
+ *   loss_partials         OUT [nparts][4] per-CTA sums of the loss terms
+ *                         (clip, value, entropy, unused), already scaled
+ * Deterministic: no atomics, fixed reduction order. */
+int    dppo_update_nparts(const dppo_dims* d, int B);
+size_t dppo_update_partials_bytes(const dppo_dims* d, int B);
+int dppo_update_fused(int flavour, const dppo_dims* d,
+                      const float* obs, const float* act, const float* adv, const float* ret,
+                      const float* logp_old, const int32_t* idx, int B,
+                      const float* theta, const float* theta_old,
+                      float clip, float ent_coeff,
+                      float* partials, float* loss_partials, void* stream);
+
+/* ---- K3: gradient sum + [global-norm clip] + Adam ------------------------
+ * Replaces Shared_grad_buffers.add_gradient/reset (model.py:53-59), the
+ * chief's Adam step on the summed gradient (chief.py:13-20), and for the PPO
+ * flavour clip_grad_norm + optimizer.step (ppo.py:173-174).
+ *   G = gshared + sum_parts partials[p]      (fixed order; gshared may be NULL)
+ *   if max_grad_norm > 0: G *= min(1, max_grad_norm / (||G||_2 + 1e-6))
+ *   Adam exactly as torch 2.11 _single_tensor_adam (lerp / addcmul / addcdiv)
+ *   with the 1-based update count `step`; gshared is reset to 0 (chief.py:19).
+ *   theta_prev (nullable) receives theta before the update (the next epoch's
+ *   theta_old); grad_out (nullable) receives G (after clipping);
+ *   loss_partials/loss_out (nullable): loss_out[4] = sum of the K2 partials.
+ * scratch: dppo_reduce_adam_scratch_bytes(P_pad). */
+size_t dppo_reduce_adam_scratch_bytes(int P_pad);
+int dppo_reduce_adam(const float* partials, int nparts, float* gshared,
+                     float* theta, float* theta_prev, float* m, float* v, int P_pad,
+                     int step, double lr, double beta1, double beta2, double eps,
+                     double max_grad_norm, float* grad_out,
+                     const float* loss_partials, float* loss_out,
+                     void* scratch, size_t scratch_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DPPO_B200_H */

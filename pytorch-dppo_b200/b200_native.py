@@ -1,0 +1,158 @@
+"""ctypes binding of libdppo_b200.so (include/dppo_b200.h).
+
+The product path goes through here and nowhere else: there is no CPU or
+PyTorch fallback.  If the library is missing it is built once with nvcc
+(build.py); if that is impossible the import fails loudly."""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdppo_b200.so")
+
+FLAVOUR_DPPO = 0
+FLAVOUR_PPO = 1
+N_PARAMS = 13
+
+PARAM_NAMES = (
+    "log_std",
+    "p_fc1.weight", "p_fc1.bias", "p_fc2.weight", "p_fc2.bias",
+    "v_fc1.weight", "v_fc1.bias", "v_fc2.weight", "v_fc2.bias",
+    "mu.weight", "mu.bias", "v.weight", "v.bias",
+)
+
+
+class Dims(ctypes.Structure):
+    """dppo_dims: policy O->H1->H2->A, value O->G1->G2->1 (model.py:11-22)."""
+    _fields_ = [("O", ctypes.c_int), ("A", ctypes.c_int), ("H1", ctypes.c_int), ("H2", ctypes.c_int),
+                ("G1", ctypes.c_int), ("G2", ctypes.c_int)]
+
+    def shapes(self):
+        return {
+            "log_std": (1, self.A),
+            "p_fc1.weight": (self.H1, self.O), "p_fc1.bias": (self.H1,),
+            "p_fc2.weight": (self.H2, self.H1), "p_fc2.bias": (self.H2,),
+            "v_fc1.weight": (self.G1, self.O), "v_fc1.bias": (self.G1,),
+            "v_fc2.weight": (self.G2, self.G1), "v_fc2.bias": (self.G2,),
+            "mu.weight": (self.A, self.H2), "mu.bias": (self.A,),
+            "v.weight": (1, self.G2), "v.bias": (1,),
+        }
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("_dppo_build", os.path.join(_HERE, "build.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        mod.build()
+    lib = ctypes.CDLL(LIB_PATH)
+    c = ctypes
+    vp, i32, i64, dbl, flt, sz = c.c_void_p, c.c_int, c.c_int64, c.c_double, c.c_float, c.c_size_t
+    dp = c.POINTER(Dims)
+    sig = {
+        "dppo_version": (i32, []),
+        "dppo_error_string": (c.c_char_p, [i32]),
+        "dppo_param_layout": (i32, [dp, c.POINTER(i32), c.POINTER(i32)]),
+        "dppo_gae_scratch_bytes": (sz, [i64]),
+        "dppo_gae_scan": (i32, [vp, vp, vp, vp, vp, vp, i64, dbl, dbl, vp, sz, vp]),
+        "dppo_welford_scratch_bytes": (sz, [i64, i32]),
+        "dppo_welford": (i32, [vp, vp, i64, i32, vp, vp, vp, vp, vp, sz, vp]),
+        "dppo_update_nparts": (i32, [dp, i32]),
+        "dppo_update_partials_bytes": (sz, [dp, i32]),
+        "dppo_update_fused": (i32, [i32, dp, vp, vp, vp, vp, vp, vp, i32, vp, vp, flt, flt, vp, vp, vp]),
+        "dppo_reduce_adam_scratch_bytes": (sz, [i32]),
+        "dppo_reduce_adam": (i32, [vp, i32, vp, vp, vp, vp, vp, i32, i32, dbl, dbl, dbl, dbl, dbl, vp, vp, vp, vp, sz, vp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)            # AttributeError = the library is stale: rebuild
+        fn.restype = res
+        fn.argtypes = args
+    return lib, sig
+
+
+lib, SIGNATURES = _load()
+
+
+class DppoError(RuntimeError):
+    pass
+
+
+def check(rc):
+    if rc != 0:
+        raise DppoError("libdppo_b200: %s (code %d)" % (lib.dppo_error_string(rc).decode(), rc))
+
+
+def _ptr(t, dtype=torch.float32, allow_none=False):
+    if t is None:
+        if allow_none:
+            return None
+        raise DppoError("libdppo_b200: missing tensor")
+    if not t.is_cuda:
+        raise DppoError("libdppo_b200: tensor is not on a CUDA device - there is no CPU path")
+    if t.dtype != dtype or not t.is_contiguous():
+        raise DppoError("libdppo_b200: expected a contiguous %s tensor, got %s" % (dtype, t.dtype))
+    return t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def param_layout(dims):
+    off = (ctypes.c_int * N_PARAMS)()
+    size = (ctypes.c_int * N_PARAMS)()
+    p_pad = lib.dppo_param_layout(ctypes.byref(dims), off, size)
+    if p_pad < 0:
+        check(p_pad)
+    return list(off), list(size), p_pad
+
+
+def gae_scratch_bytes(T):
+    return lib.dppo_gae_scratch_bytes(T)
+
+
+def gae_scan(rewards, values, boot, seg_end, adv, ret, gamma, lam, scratch):
+    T = rewards.numel()
+    check(lib.dppo_gae_scan(_ptr(rewards), _ptr(values), _ptr(boot), _ptr(seg_end, torch.uint8), _ptr(adv), _ptr(ret),
+                            T, gamma, lam, _ptr(scratch, torch.uint8), scratch.numel(), _stream()))
+
+
+def welford_scratch_bytes(T, O):
+    return lib.dppo_welford_scratch_bytes(T, O)
+
+
+def welford(obs, out, n, mean, mean_diff, var, scratch):
+    T, O = obs.shape
+    check(lib.dppo_welford(_ptr(obs), _ptr(out), T, O, _ptr(n), _ptr(mean), _ptr(mean_diff), _ptr(var),
+                           _ptr(scratch, torch.uint8), scratch.numel(), _stream()))
+
+
+def update_nparts(dims, B):
+    n = lib.dppo_update_nparts(ctypes.byref(dims), B)
+    if n < 0:
+        check(n)
+    return n
+
+
+def update_fused(flavour, dims, obs, act, adv, ret, logp_old, idx, theta, theta_old, clip, ent_coeff, partials,
+                 loss_partials):
+    check(lib.dppo_update_fused(flavour, ctypes.byref(dims), _ptr(obs), _ptr(act), _ptr(adv), _ptr(ret),
+                                _ptr(logp_old, allow_none=True), _ptr(idx, torch.int32), idx.numel(), _ptr(theta),
+                                _ptr(theta_old, allow_none=True), clip, ent_coeff, _ptr(partials), _ptr(loss_partials),
+                                _stream()))
+
+
+def reduce_adam_scratch_bytes(P_pad):
+    return lib.dppo_reduce_adam_scratch_bytes(P_pad)
+
+
+def reduce_adam(partials, nparts, gshared, theta, theta_prev, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8,
+                max_grad_norm=0.0, grad_out=None, loss_partials=None, loss_out=None, scratch=None):
+    check(lib.dppo_reduce_adam(_ptr(partials, allow_none=True), nparts, _ptr(gshared, allow_none=True), _ptr(theta),
+                               _ptr(theta_prev, allow_none=True), _ptr(m), _ptr(v), theta.numel(), step, lr, beta1,
+                               beta2, eps, max_grad_norm, _ptr(grad_out, allow_none=True),
+                               _ptr(loss_partials, allow_none=True), _ptr(loss_out, allow_none=True),
+                               _ptr(scratch, torch.uint8, allow_none=True), 0 if scratch is None else scratch.numel(),
+                               _stream()))

@@ -1,0 +1,214 @@
+// K1 - GAE / returns as a reverse segmented linear-recurrence scan.
+//
+// Reference: train.py:113-122 / ppo.py:124-133
+//     td = r[i] + gamma*V[i+1] - V[i];  A = td + (gamma*lam)*A;  R = A + V[i]
+// per rollout segment, A reset to 0 and V[i+1] := bootstrap at a segment end.
+//
+// Formulation: step i is the affine map  f_i(x) = td_i + a_i * x  with
+// a_i = 0 at a segment end (this is how the done-mask enters: it zeroes the
+// coefficient, and the zero propagates through the warp shuffles) and
+// a_i = fp32(gamma*lam) elsewhere.  A_i = (f_i o f_{i+1} o ...)(0).
+//
+// One pass over HBM (20 B/step + 1 B flag): every thread owns 8 consecutive
+// steps, composes them, a warp-shuffle suffix scan and a block scan give each
+// thread its carry-in, and tiles are chained right-to-left with a decoupled
+// look-back (tile order is handed out by an atomic ticket, so a tile's
+// right-hand neighbours always started earlier).  Because |a| < 1 the
+// composed coefficient of a whole tile underflows to 0, so the look-back
+// normally ends after one hop.  With its carry known, each thread REPLAYS its
+// 8 steps with the reference's exact fp32 operation order (no FMA), so the
+// only rounding difference to the sequential loop sits in the carries.
+#include "common.cuh"
+
+namespace {
+
+constexpr int GAE_THREADS = 256;
+constexpr int GAE_K = 8;                          // steps per thread
+constexpr int GAE_TILE = GAE_THREADS * GAE_K;     // 2048 steps per CTA
+
+struct Aff { float a, b; };                       // x -> b + a*x
+// (f o g)(x) = f.b + f.a*(g.b + g.a*x)
+__device__ __forceinline__ Aff compose(Aff f, Aff g) {
+    Aff r;
+    r.a = f.a * g.a;
+    r.b = fmaf(f.a, g.b, f.b);
+    return r;
+}
+
+// scratch layout: int ticket; int status[ntiles]; float2 ab[ntiles]
+// status: 0 = nothing, 1 = ab is the tile-local composition, 2 = ab.b is the
+// resolved A at the tile's first step (ab.a = 0)
+template <bool VEC>
+__global__ void __launch_bounds__(GAE_THREADS)
+gae_scan_kernel(const float* __restrict__ rew, const float* __restrict__ val, const float* __restrict__ boot,
+                const uint8_t* __restrict__ seg_end, float* __restrict__ adv, float* __restrict__ ret,
+                int64_t T, float g, float gl, int ntiles, int* __restrict__ ticket, int* __restrict__ status,
+                float2* __restrict__ ab) {
+    __shared__ int s_tile;
+    __shared__ Aff s_warp[GAE_THREADS / 32];
+    __shared__ float s_carry;
+
+    if (threadIdx.x == 0) s_tile = ntiles - 1 - atomicAdd(ticket, 1);   // right-most tile first
+    __syncthreads();
+    const int tile = s_tile;
+    const int64_t base = (int64_t)tile * GAE_TILE + (int64_t)threadIdx.x * GAE_K;
+
+    float r[GAE_K], v[GAE_K + 1], bt[GAE_K];
+    uint8_t se[GAE_K];
+    if (VEC && base + GAE_K <= T) {
+        const float4* r4 = reinterpret_cast<const float4*>(rew + base);
+        const float4* v4 = reinterpret_cast<const float4*>(val + base);
+        const float4* b4 = reinterpret_cast<const float4*>(boot + base);
+        float4 x0 = r4[0], x1 = r4[1], y0 = v4[0], y1 = v4[1], z0 = b4[0], z1 = b4[1];
+        uint2 e = *reinterpret_cast<const uint2*>(seg_end + base);
+        r[0] = x0.x; r[1] = x0.y; r[2] = x0.z; r[3] = x0.w; r[4] = x1.x; r[5] = x1.y; r[6] = x1.z; r[7] = x1.w;
+        v[0] = y0.x; v[1] = y0.y; v[2] = y0.z; v[3] = y0.w; v[4] = y1.x; v[5] = y1.y; v[6] = y1.z; v[7] = y1.w;
+        bt[0] = z0.x; bt[1] = z0.y; bt[2] = z0.z; bt[3] = z0.w; bt[4] = z1.x; bt[5] = z1.y; bt[6] = z1.z; bt[7] = z1.w;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { se[k] = (e.x >> (8 * k)) & 0xff; se[4 + k] = (e.y >> (8 * k)) & 0xff; }
+    } else {
+#pragma unroll
+        for (int k = 0; k < GAE_K; ++k) {
+            const int64_t i = base + k;
+            const bool in = i < T;
+            r[k] = in ? rew[i] : 0.f;
+            v[k] = in ? val[i] : 0.f;
+            bt[k] = in ? boot[i] : 0.f;
+            se[k] = in ? seg_end[i] : (uint8_t)1;
+        }
+    }
+    v[GAE_K] = (base + GAE_K < T) ? val[base + GAE_K] : 0.f;
+#pragma unroll
+    for (int k = 0; k < GAE_K; ++k)
+        if (base + k >= T - 1) se[k] = 1;          // the buffer's last step always closes a segment
+
+    // td_i with the reference's roundings: fl(fl(r + fl(g*Vnext)) - V)
+    float td[GAE_K];
+#pragma unroll
+    for (int k = 0; k < GAE_K; ++k) {
+        const float vn = se[k] ? bt[k] : v[k + 1];
+        td[k] = __fsub_rn(__fadd_rn(r[k], __fmul_rn(g, vn)), v[k]);
+    }
+    // thread-local composition f_0 o f_1 o ... o f_7
+    Aff loc;
+    loc.a = 1.f; loc.b = 0.f;
+#pragma unroll
+    for (int k = GAE_K - 1; k >= 0; --k) {
+        Aff f; f.a = se[k] ? 0.f : gl; f.b = td[k];
+        loc = compose(f, loc);
+    }
+    // inclusive suffix scan over the lanes of a warp: inc_l = f_l o f_{l+1} o ... o f_31
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    Aff inc = loc;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        Aff o;
+        o.a = __shfl_down_sync(0xffffffffu, inc.a, d);
+        o.b = __shfl_down_sync(0xffffffffu, inc.b, d);
+        if (lane + d < 32) inc = compose(inc, o);
+    }
+    if (lane == 0) s_warp[warp] = inc;
+    __syncthreads();
+    // composition of everything to the right of this thread inside the tile
+    Aff right;                                       // lanes right of me in my warp
+    right.a = __shfl_down_sync(0xffffffffu, inc.a, 1);
+    right.b = __shfl_down_sync(0xffffffffu, inc.b, 1);
+    if (lane == 31) { right.a = 1.f; right.b = 0.f; }
+#pragma unroll
+    for (int w = 0; w < GAE_THREADS / 32; ++w)
+        if (w > warp) right = compose(right, s_warp[w]);
+
+    // tile aggregate and look-back (thread 0)
+    if (threadIdx.x == 0) {
+        Aff agg = compose(loc, right);
+        float carry = 0.f;
+        if (tile == ntiles - 1) {
+            __stcg(&ab[tile], make_float2(0.f, agg.b));
+            __threadfence();
+            st_release_gpu(&status[tile], 2);
+        } else {
+            __stcg(&ab[tile], make_float2(agg.a, agg.b));
+            __threadfence();
+            st_release_gpu(&status[tile], 1);
+            Aff acc; acc.a = 1.f; acc.b = 0.f;
+            int t = tile + 1;
+            while (true) {
+                int st;
+                while ((st = ld_acquire_gpu(&status[t])) == 0) { }
+                const float2 d = __ldcg(&ab[t]);         // one 64-bit L2 read: (a,b) never tears
+                Aff o; o.a = (st == 2) ? 0.f : d.x; o.b = d.y;
+                acc = compose(acc, o);
+                if (acc.a == 0.f) break;
+                ++t;                                  // t <= ntiles-1 always ends with status 2
+            }
+            carry = acc.b;
+            const float first = (agg.a == 0.f) ? agg.b : fmaf(agg.a, carry, agg.b);
+            __stcg(&ab[tile], make_float2(0.f, first));
+            __threadfence();
+            st_release_gpu(&status[tile], 2);
+        }
+        s_carry = carry;
+    }
+    __syncthreads();
+    // A at the first step right of this thread
+    float A = (right.a == 0.f) ? right.b : fmaf(right.a, s_carry, right.b);
+    // replay with the reference's op order: A = fl(td + fl(gl*A)); R = fl(A + V)
+    float oa[GAE_K], orr[GAE_K];
+#pragma unroll
+    for (int k = GAE_K - 1; k >= 0; --k) {
+        A = se[k] ? td[k] : __fadd_rn(td[k], __fmul_rn(gl, A));
+        oa[k] = A;
+        orr[k] = __fadd_rn(A, v[k]);
+    }
+    if (VEC && base + GAE_K <= T) {
+        float4* a4 = reinterpret_cast<float4*>(adv + base);
+        float4* q4 = reinterpret_cast<float4*>(ret + base);
+        a4[0] = make_float4(oa[0], oa[1], oa[2], oa[3]);
+        a4[1] = make_float4(oa[4], oa[5], oa[6], oa[7]);
+        q4[0] = make_float4(orr[0], orr[1], orr[2], orr[3]);
+        q4[1] = make_float4(orr[4], orr[5], orr[6], orr[7]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < GAE_K; ++k)
+            if (base + k < T) { adv[base + k] = oa[k]; ret[base + k] = orr[k]; }
+    }
+}
+
+}  // namespace
+
+extern "C" size_t dppo_gae_scratch_bytes(int64_t T) {
+    if (T <= 0) return 16;
+    const int64_t ntiles = ceil_div64(T, GAE_TILE);
+    return align_up(sizeof(int) * (size_t)(1 + ntiles), 16) + sizeof(float2) * (size_t)ntiles;
+}
+
+extern "C" int dppo_gae_scan(const float* rewards, const float* values, const float* boot, const uint8_t* seg_end,
+                             float* adv, float* ret, int64_t T, double gamma, double lam,
+                             void* scratch, size_t scratch_bytes, void* stream_) {
+    if (T < 0) return DPPO_E_BADARG;
+    if (T == 0) return 0;
+    if (!rewards || !values || !boot || !seg_end || !adv || !ret || !scratch) return DPPO_E_BADARG;
+    if (ceil_div64(T, GAE_TILE) > 0x7fffffff) return DPPO_E_TOOLARGE;
+    if (scratch_bytes < dppo_gae_scratch_bytes(T)) return DPPO_E_SCRATCH;
+    if (!aligned16(scratch)) return DPPO_E_ALIGN;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int ntiles = (int)ceil_div64(T, GAE_TILE);
+    const size_t flag_bytes = align_up(sizeof(int) * (size_t)(1 + ntiles), 16);
+    int* ticket = (int*)scratch;
+    int* status = ticket + 1;
+    float2* ab = (float2*)((char*)scratch + flag_bytes);
+    DPPO_CUDA_TRY(cudaMemsetAsync(scratch, 0, flag_bytes, stream));
+    // gamma multiplies a 0-dim fp32 tensor, gamma*lam is a Python double product
+    // that multiplies an fp32 tensor (train.py:118-119): both end up as fp32 scalars
+    const float g = (float)gamma, gl = (float)(gamma * lam);
+    const bool vec = aligned16(rewards) && aligned16(values) && aligned16(boot) && aligned16(adv) && aligned16(ret) &&
+                     ((reinterpret_cast<uintptr_t>(seg_end) & 7u) == 0);
+    if (vec)
+        gae_scan_kernel<true><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T, g, gl,
+                                                                   ntiles, ticket, status, ab);
+    else
+        gae_scan_kernel<false><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T, g, gl,
+                                                                    ntiles, ticket, status, ab);
+    DPPO_LAUNCH_CHECK();
+    return 0;
+}
