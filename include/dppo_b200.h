@@ -121,12 +121,17 @@ int dppo_update_fused(int flavour, const dppo_dims* d,
  *   theta_prev (nullable) receives theta before the update (the next epoch's
  *   theta_old); grad_out (nullable) receives G (after clipping);
  *   loss_partials/loss_out (nullable): loss_out[4] = sum of the K2 partials.
- * scratch: dppo_reduce_adam_scratch_bytes(P_pad). */
+ *   scalars_dev (nullable): 6 floats in DEVICE memory as written by
+ *   dppo_adam_scalars_host for the update count / learning rate to use; when
+ *   given, step/lr/beta/eps arguments are ignored.  This lets a captured CUDA
+ *   graph be replayed with a new update count (the host refreshes the 24 bytes).
+ * scratch: dppo_reduce_adam_scratch_bytes(P_pad) (only needed when clipping). */
 size_t dppo_reduce_adam_scratch_bytes(int P_pad);
+int dppo_adam_scalars_host(int step, double lr, double beta1, double beta2, double eps, float* out6_host);
 int dppo_reduce_adam(const float* partials, int nparts, float* gshared,
                      float* theta, float* theta_prev, float* m, float* v, int P_pad,
                      int step, double lr, double beta1, double beta2, double eps,
-                     double max_grad_norm, float* grad_out,
+                     const float* scalars_dev, double max_grad_norm, float* grad_out,
                      const float* loss_partials, float* loss_out,
                      void* scratch, size_t scratch_bytes, void* stream);
 

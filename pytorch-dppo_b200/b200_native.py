@@ -63,7 +63,8 @@ def _load():
         "dppo_update_partials_bytes": (sz, [dp, i32]),
         "dppo_update_fused": (i32, [i32, dp, vp, vp, vp, vp, vp, vp, i32, vp, vp, flt, flt, vp, vp, vp]),
         "dppo_reduce_adam_scratch_bytes": (sz, [i32]),
-        "dppo_reduce_adam": (i32, [vp, i32, vp, vp, vp, vp, vp, i32, i32, dbl, dbl, dbl, dbl, dbl, vp, vp, vp, vp, sz, vp]),
+        "dppo_adam_scalars_host": (i32, [i32, dbl, dbl, dbl, dbl, c.POINTER(flt)]),
+        "dppo_reduce_adam": (i32, [vp, i32, vp, vp, vp, vp, vp, i32, i32, dbl, dbl, dbl, dbl, vp, dbl, vp, vp, vp, vp, sz, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)            # AttributeError = the library is stale: rebuild
@@ -148,11 +149,19 @@ def reduce_adam_scratch_bytes(P_pad):
     return lib.dppo_reduce_adam_scratch_bytes(P_pad)
 
 
+def adam_scalars(step, lr, beta1=0.9, beta2=0.999, eps=1e-8):
+    """The six fp32 scalars of one Adam update (host side of scalars_dev)."""
+    out = (ctypes.c_float * 6)()
+    check(lib.dppo_adam_scalars_host(step, lr, beta1, beta2, eps, out))
+    return list(out)
+
+
 def reduce_adam(partials, nparts, gshared, theta, theta_prev, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8,
-                max_grad_norm=0.0, grad_out=None, loss_partials=None, loss_out=None, scratch=None):
+                max_grad_norm=0.0, grad_out=None, loss_partials=None, loss_out=None, scratch=None, scalars_dev=None):
     check(lib.dppo_reduce_adam(_ptr(partials, allow_none=True), nparts, _ptr(gshared, allow_none=True), _ptr(theta),
                                _ptr(theta_prev, allow_none=True), _ptr(m), _ptr(v), theta.numel(), step, lr, beta1,
-                               beta2, eps, max_grad_norm, _ptr(grad_out, allow_none=True),
+                               beta2, eps, _ptr(scalars_dev, allow_none=True), max_grad_norm,
+                               _ptr(grad_out, allow_none=True),
                                _ptr(loss_partials, allow_none=True), _ptr(loss_out, allow_none=True),
                                _ptr(scratch, torch.uint8, allow_none=True), 0 if scratch is None else scratch.numel(),
                                _stream()))

@@ -55,8 +55,10 @@ __device__ __forceinline__ void reduce_losses(const float* __restrict__ loss_par
 __global__ void __launch_bounds__(ADAM_THREADS)
 reduce_adam_kernel(const float4* __restrict__ partials, int nparts, float4* __restrict__ gshared,
                    float4* __restrict__ theta, float4* __restrict__ theta_prev, float4* __restrict__ m,
-                   float4* __restrict__ v, int n4, AdamScalars s, float4* __restrict__ grad_out,
-                   const float* __restrict__ loss_partials, float* __restrict__ loss_out) {
+                   float4* __restrict__ v, int n4, AdamScalars s, const AdamScalars* __restrict__ sdev,
+                   float4* __restrict__ grad_out, const float* __restrict__ loss_partials,
+                   float* __restrict__ loss_out) {
+    if (sdev) s = *sdev;
     reduce_losses(loss_partials, nparts, loss_out);
     const int i = blockIdx.x * ADAM_THREADS + threadIdx.x;
     if (i >= n4) return;
@@ -100,9 +102,10 @@ reduce_sumsq_kernel(const float4* __restrict__ partials, int nparts, float4* __r
 __global__ void __launch_bounds__(ADAM_THREADS)
 clip_adam_kernel(const float4* __restrict__ gtmp, const double* __restrict__ blocksums, int nblocks, float max_norm,
                  float4* __restrict__ theta, float4* __restrict__ theta_prev, float4* __restrict__ m,
-                 float4* __restrict__ v, int n4, AdamScalars s, float4* __restrict__ grad_out,
-                 float* __restrict__ norm_out) {
+                 float4* __restrict__ v, int n4, AdamScalars s, const AdamScalars* __restrict__ sdev,
+                 float4* __restrict__ grad_out, float* __restrict__ norm_out) {
     __shared__ double red[ADAM_THREADS];
+    if (sdev) s = *sdev;
     double ss = 0.0;
     for (int b = threadIdx.x; b < nblocks; b += ADAM_THREADS) ss += blocksums[b];
     red[threadIdx.x] = ss;
@@ -138,7 +141,7 @@ extern "C" size_t dppo_reduce_adam_scratch_bytes(int P_pad) {
     return align_up(sizeof(float) * (size_t)P_pad, 16) + sizeof(double) * (size_t)nblocks + 16;
 }
 
-AdamScalars dppo_adam_scalars(int step, double lr, double beta1, double beta2, double eps) {
+static AdamScalars dppo_adam_scalars(int step, double lr, double beta1, double beta2, double eps) {
     AdamScalars s;
     const double bc1 = 1.0 - pow(beta1, (double)step);
     const double bc2 = 1.0 - pow(beta2, (double)step);
@@ -151,11 +154,20 @@ AdamScalars dppo_adam_scalars(int step, double lr, double beta1, double beta2, d
     return s;
 }
 
+extern "C" int dppo_adam_scalars_host(int step, double lr, double beta1, double beta2, double eps, float* out6_host) {
+    if (step < 1 || !out6_host) return DPPO_E_BADARG;
+    const AdamScalars s = dppo_adam_scalars(step, lr, beta1, beta2, eps);
+    out6_host[0] = s.w1; out6_host[1] = s.b2; out6_host[2] = s.a2;
+    out6_host[3] = s.bc2_sqrt; out6_host[4] = s.eps; out6_host[5] = s.alpha;
+    return 0;
+}
+
 extern "C" int dppo_reduce_adam(const float* partials, int nparts, float* gshared, float* theta, float* theta_prev,
                                 float* m, float* v, int P_pad, int step, double lr, double beta1, double beta2,
-                                double eps, double max_grad_norm, float* grad_out, const float* loss_partials,
-                                float* loss_out, void* scratch, size_t scratch_bytes, void* stream_) {
-    if (P_pad <= 0 || (P_pad & 3) || nparts < 0 || step < 1) return DPPO_E_BADARG;
+                                double eps, const float* scalars_dev, double max_grad_norm, float* grad_out,
+                                const float* loss_partials, float* loss_out, void* scratch, size_t scratch_bytes,
+                                void* stream_) {
+    if (P_pad <= 0 || (P_pad & 3) || nparts < 0 || (step < 1 && !scalars_dev)) return DPPO_E_BADARG;
     if (!theta || !m || !v || (nparts > 0 && !partials)) return DPPO_E_BADARG;
     if (!aligned16(partials) || !aligned16(gshared) || !aligned16(theta) || !aligned16(theta_prev) || !aligned16(m) ||
         !aligned16(v) || !aligned16(grad_out))
@@ -163,7 +175,7 @@ extern "C" int dppo_reduce_adam(const float* partials, int nparts, float* gshare
     cudaStream_t stream = (cudaStream_t)stream_;
     const int n4 = P_pad / 4;
     const int nblocks = ceil_div(n4, ADAM_THREADS);
-    const AdamScalars s = dppo_adam_scalars(step, lr, beta1, beta2, eps);
+    const AdamScalars s = dppo_adam_scalars(step < 1 ? 1 : step, lr, beta1, beta2, eps);
     if (max_grad_norm > 0.0) {
         if (!scratch || scratch_bytes < dppo_reduce_adam_scratch_bytes(P_pad)) return DPPO_E_SCRATCH;
         if (!aligned16(scratch)) return DPPO_E_ALIGN;
@@ -175,13 +187,14 @@ extern "C" int dppo_reduce_adam(const float* partials, int nparts, float* gshare
         DPPO_LAUNCH_CHECK();
         clip_adam_kernel<<<nblocks, ADAM_THREADS, 0, stream>>>(gtmp, blocksums, nblocks, (float)max_grad_norm,
                                                                 (float4*)theta, (float4*)theta_prev, (float4*)m,
-                                                                (float4*)v, n4, s, (float4*)grad_out, norm);
+                                                                (float4*)v, n4, s, (const AdamScalars*)scalars_dev,
+                                                                (float4*)grad_out, norm);
         DPPO_LAUNCH_CHECK();
     } else {
         reduce_adam_kernel<<<nblocks, ADAM_THREADS, 0, stream>>>((const float4*)partials, nparts, (float4*)gshared,
                                                                   (float4*)theta, (float4*)theta_prev, (float4*)m,
-                                                                  (float4*)v, n4, s, (float4*)grad_out, loss_partials,
-                                                                  loss_out);
+                                                                  (float4*)v, n4, s, (const AdamScalars*)scalars_dev,
+                                                                  (float4*)grad_out, loss_partials, loss_out);
         DPPO_LAUNCH_CHECK();
     }
     return 0;

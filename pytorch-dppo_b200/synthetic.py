@@ -1,0 +1,63 @@
+"""Synthetic rollouts of the named MuJoCo/PyBullet shapes (gym is not available;
+only shapes matter to the update path).  SURVEY.md section 8(d): raw observations
+~ loc_f + scale_f*N(0,1) normalised by K4 into states clamped to [-5,5],
+actions = mu_theta0(state) + std*N(0,1) with the flavour's convention
+(train.py:89 / ppo.py:93), rewards ~ clamp(N(0,1),-1,1) (train.py:96), values
+= V_theta0(state), segments of ``seg_len`` steps plus a ragged tail, each ending
+with done (p = 1/2, bootstrap 0) or a bootstrap value (train.py:109-112)."""
+import math
+
+import torch
+
+import b200_native as nv
+from b200_engine import RolloutBuffer
+
+SHAPES = {                       # env name -> (obs dim, act dim)
+    "InvertedPendulum": (4, 1), "HalfCheetah": (17, 6), "HopperBullet": (15, 3), "Humanoid": (376, 17),
+}
+
+
+def make_rollout(model, obs_stats, T, seed, flavour, seg_len=1000, pinned_host=True):
+    """Returns (host RolloutBuffer in pinned memory, device RolloutBuffer), both filled
+    up to (and excluding) adv/ret, which K1 produces."""
+    O, A = model.dims.O, model.dims.A
+    dev = model.flat.device
+    g = torch.Generator().manual_seed(seed)
+    host = RolloutBuffer(T, O, A, dev, pinned_host=pinned_host)
+    loc = torch.rand(O, generator=g) * 2 - 1
+    scale = torch.rand(O, generator=g) * 1.5 + 0.25
+    host.raw_obs.copy_(loc + scale * torch.randn(T, O, generator=g))
+    host.rew.copy_(torch.randn(T, generator=g).clamp_(-1, 1))
+    eps = torch.randn(T, A, generator=g)
+    boot_noise = torch.randn(T, generator=g)
+    coin = torch.rand(T, generator=g)
+    d = RolloutBuffer(T, O, A, dev)
+    d.raw_obs.copy_(host.raw_obs)
+    if obs_stats is not None:
+        # normalise with a scratch copy of the statistics so that the caller's stay untouched
+        import copy
+        st = copy.copy(obs_stats)
+        st.n, st.mean, st.mean_diff, st.var = (t.clone() for t in (obs_stats.n, obs_stats.mean, obs_stats.mean_diff, obs_stats.var))
+        st.observes_batch(d.raw_obs, out=d.obs)
+    else:
+        d.obs.copy_(d.raw_obs.clamp(-5, 5))
+    with torch.no_grad():
+        mu, sigma_sq, v = model(d.obs)
+        std = sigma_sq.sqrt() if flavour == nv.FLAVOUR_DPPO else sigma_sq
+        d.act.copy_(mu + std * eps.to(dev))
+        d.val.copy_(v.reshape(-1))
+        logp = (-0.5 * ((d.act - mu) / sigma_sq).pow(2) - 0.5 * math.log(2 * math.pi) - model.log_std).sum(-1)
+        d.logp.copy_(logp)
+    seg_end = torch.zeros(T, dtype=torch.uint8)
+    seg_end[seg_len - 1::seg_len] = 1
+    seg_end[T - 1] = 1
+    ends = seg_end.bool()
+    boot = torch.where(ends & (coin >= 0.5), boot_noise * 0.5, torch.zeros(T))
+    host.seg_end.copy_(seg_end)
+    host.boot.copy_(boot)
+    for f in ("obs", "act", "val", "logp"):
+        getattr(host, f).copy_(getattr(d, f))
+    for f in ("rew", "boot", "seg_end"):
+        getattr(d, f).copy_(getattr(host, f))
+    torch.cuda.synchronize()
+    return host, d

@@ -1,0 +1,218 @@
+"""Whole update cycles on the GPU (engine + CUDA graph + drop-in surface) against
+the fixtures recorded from the reference and against the oracle."""
+import os
+import random
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ppo_oracle as orc
+from util import assert_close_scaled, to_flat, unpadded
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _load_model(g, O, A):
+    from model import Model
+    m = Model(O, A, device=DEV)
+    sh = orc.param_shapes(O, A)
+    p = orc.unflatten(torch.from_numpy(g["theta0"]), sh)
+    m.load_state_dict({k: v.to(DEV) for k, v in p.items()})
+    return m
+
+
+def _buffer(g, pre, O, A, with_logp=False):
+    from b200_engine import RolloutBuffer
+    T = g[pre + "states"].shape[0]
+    b = RolloutBuffer(T, O, A, DEV)
+    b.obs.copy_(torch.from_numpy(g[pre + "states"]))
+    b.act.copy_(torch.from_numpy(g[pre + "actions"]))
+    b.adv.copy_(torch.from_numpy(g[pre + "advantages"]).reshape(-1))
+    b.ret.copy_(torch.from_numpy(g[pre + "returns"]).reshape(-1))
+    if with_logp:
+        b.logp.copy_(torch.from_numpy(g[pre + "logprobs"]).reshape(-1))
+    return b
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_dppo_w1_cycle_matches_reference(golden_dir, use_graph):
+    """train.py:128-175 + chief.py:13-20 for one worker: parameters after every epoch,
+    Adam moments, the ones-initialised shared buffer (model.py:51)."""
+    import b200_native as nv
+    from b200_engine import UpdateEngine
+    from model import Shared_grad_buffers
+    g = np.load(os.path.join(golden_dir, "dppo_w1_o3a2.npz"))
+    O, A, E, B = int(g["O"]), int(g["A"]), int(g["E"]), int(g["B"])
+    m = _load_model(g, O, A)
+    sgb = Shared_grad_buffers(m)
+    buf = _buffer(g, "w0_", O, A)
+    eng = UpdateEngine(m, nv.FLAVOUR_DPPO, B, 1, float(g["lr"]), clip=float(g["clip"]), ent_coeff=float(g["ent_coeff"]))
+    # E = 1 per call so that every epoch's parameters can be compared; theta_old must
+    # then lag across calls exactly as inside one call
+    for k in range(E):
+        eng.idx_host[0] = torch.from_numpy(g["w0_idx"][k])
+        prev = m.flat.clone()
+        if k > 0:
+            eng.theta_old.copy_(prev_prev)
+            eng.flavour_keep_old = True
+        eng_launch(eng, buf, sgb.flat, use_graph, first=(k == 0))
+        prev_prev = prev
+        torch.cuda.synchronize()
+        assert_close_scaled(unpadded(eng.grad, m.offsets, m.sizes), g["G_%d" % k], 1e-5, "G_%d" % k)
+        assert_close_scaled(unpadded(m.flat, m.offsets, m.sizes), g["theta_%d" % k], 1e-5, "theta_%d" % k)
+        t = g["w0_terms"][k]
+        L = eng.loss_out[0].cpu()
+        assert float(L[0]) == pytest.approx(t[0], rel=1e-5, abs=1e-7)
+        assert float(L[1]) == pytest.approx(t[1], rel=1e-5)
+    assert_close_scaled(unpadded(eng.m, m.offsets, m.sizes), g["m_final"], 1e-5, "m")
+    assert_close_scaled(unpadded(eng.v, m.offsets, m.sizes), g["v_final"], 1e-5, "v")
+    assert float(sgb.flat.abs().max()) == 0.0
+
+
+def eng_launch(eng, buf, gshared, use_graph, first):
+    """One epoch through the engine without resetting theta_old (the engine copies
+    theta -> theta_old at the start of a cycle; for k > 0 we restore the lagged copy)."""
+    import b200_native as nv
+    eng.idx_dev.copy_(eng.idx_host)
+    eng._stage_scalars()
+    if first:
+        eng.theta_old.copy_(eng.theta)
+    nv.update_fused(eng.flavour, eng.dims, buf.obs, buf.act, buf.adv, buf.ret, None, eng.idx_dev[0], eng.theta,
+                    eng.theta_old, eng.clip, eng.ent_coeff, eng.partials, eng.loss_partials)
+    nv.reduce_adam(eng.partials, eng.nparts, gshared, eng.theta, None, eng.m, eng.v, 0, eng.lr,
+                   grad_out=eng.grad, loss_partials=eng.loss_partials, loss_out=eng.loss_out[0],
+                   scalars_dev=eng.scalars_dev[0])
+    eng.step += 1
+
+
+def test_dppo_w1_full_cycle_graph_vs_reference(golden_dir):
+    """The engine's own E-epoch cycle (graph replay, theta_old written by K3) must land on
+    the reference's final parameters."""
+    import b200_native as nv
+    from b200_engine import UpdateEngine
+    from model import Shared_grad_buffers
+    g = np.load(os.path.join(golden_dir, "dppo_w1_o3a2.npz"))
+    O, A, E, B = int(g["O"]), int(g["A"]), int(g["E"]), int(g["B"])
+    for use_graph in (False, True):
+        m = _load_model(g, O, A)
+        sgb = Shared_grad_buffers(m)
+        buf = _buffer(g, "w0_", O, A)
+        eng = UpdateEngine(m, nv.FLAVOUR_DPPO, B, E, float(g["lr"]), clip=float(g["clip"]), ent_coeff=float(g["ent_coeff"]))
+        eng.idx_host.copy_(torch.from_numpy(g["w0_idx"]))
+        losses = eng.run_epochs(buf, gshared=sgb.flat, use_graph=use_graph)
+        torch.cuda.synchronize()
+        assert_close_scaled(unpadded(m.flat, m.offsets, m.sizes), g["theta_%d" % (E - 1)], 1e-5, "theta final")
+        assert_close_scaled(unpadded(eng.m, m.offsets, m.sizes), g["m_final"], 1e-5, "m")
+        assert_close_scaled(unpadded(eng.v, m.offsets, m.sizes), g["v_final"], 1e-5, "v")
+        assert eng.step == int(g["step_final"])
+        for k in range(E):
+            assert float(losses[k, 1]) == pytest.approx(g["w0_terms"][k][1], rel=1e-5)
+
+
+def test_dppo_w2_cycle_matches_reference(golden_dir):
+    """Two workers' gradients summed into the shared buffer in rank order, then Adam
+    (model.py:53-55, chief.py:13-20).  Both workers run on this one GPU; K3 sums the
+    concatenated partials (the multi-GPU exchange is tested in test_gpu_comm.py)."""
+    import b200_native as nv
+    from model import Shared_grad_buffers
+    g = np.load(os.path.join(golden_dir, "dppo_w2_o17a6.npz"))
+    O, A, E, B = int(g["O"]), int(g["A"]), int(g["E"]), int(g["B"])
+    m = _load_model(g, O, A)
+    sgb = Shared_grad_buffers(m)
+    bufs = [_buffer(g, "w%d_" % w, O, A) for w in range(2)]
+    npart = nv.update_nparts(m.dims, B)
+    partials = torch.empty(2 * npart, m.P_pad, device=DEV)
+    lparts = torch.empty(2 * npart, 4, device=DEV)
+    theta_old = m.flat.clone()
+    mm, vv = torch.zeros_like(m.flat), torch.zeros_like(m.flat)
+    G = torch.empty_like(m.flat)
+    for k in range(E):
+        for w in range(2):
+            idx = torch.from_numpy(g["w%d_idx" % w][k]).to(DEV)
+            nv.update_fused(nv.FLAVOUR_DPPO, m.dims, bufs[w].obs, bufs[w].act, bufs[w].adv, bufs[w].ret, None, idx,
+                            m.flat, theta_old, float(g["clip"]), float(g["ent_coeff"]),
+                            partials[w * npart:(w + 1) * npart], lparts[w * npart:(w + 1) * npart])
+            torch.cuda.synchronize()
+            gw = partials[w * npart:(w + 1) * npart].double().sum(0).float()
+            assert_close_scaled(unpadded(gw, m.offsets, m.sizes), g["w%d_grad_%d" % (w, k)], 1e-5, "grad w%d e%d" % (w, k))
+            L = lparts[w * npart:(w + 1) * npart].double().sum(0).cpu()
+            assert float(L[0]) == pytest.approx(g["w%d_terms" % w][k][0], rel=1e-5, abs=1e-7)
+            assert float(L[1]) == pytest.approx(g["w%d_terms" % w][k][1], rel=1e-5)
+        nv.reduce_adam(partials, 2 * npart, sgb.flat, m.flat, theta_old, mm, vv, k + 1, float(g["lr"]), grad_out=G)
+        torch.cuda.synchronize()
+        if "G_%d" % k in g.files:
+            assert_close_scaled(unpadded(G, m.offsets, m.sizes), g["G_%d" % k], 1e-5, "G_%d" % k)
+        assert_close_scaled(unpadded(m.flat, m.offsets, m.sizes), g["theta_%d" % k], 1e-5, "theta_%d" % k)
+    assert_close_scaled(unpadded(mm, m.offsets, m.sizes), g["m_final"], 1e-5, "m")
+    assert_close_scaled(unpadded(vv, m.offsets, m.sizes), g["v_final"], 1e-5, "v")
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_ppo_cycle_matches_reference(golden_dir, use_graph):
+    """ppo.py:139-174, ten epochs: losses, clipped gradient norm path, final parameters."""
+    import ppo as ppo_mod
+    g = np.load(os.path.join(golden_dir, "ppo_o4a2.npz"))
+    O, A, E, B = int(g["O"]), int(g["A"]), int(g["E"]), int(g["B"])
+    m = _load_model(g, O, A)
+    buf = _buffer(g, "", O, A, with_logp=True)
+    p = ppo_mod.Params()
+    p.batch_size, p.num_epoch, p.num_steps = B, E, int(g["T"])
+    eng = ppo_mod.make_engine(p, m)
+    eng.idx_host.copy_(torch.from_numpy(g["idx"]))
+    losses = eng.run_epochs(buf, use_graph=use_graph)
+    torch.cuda.synchronize()
+    for k in range(E):
+        t = g["terms"][k]
+        assert float(losses[k, 0]) == pytest.approx(t[0], rel=2e-5, abs=1e-7)
+        assert float(losses[k, 1]) == pytest.approx(t[1], rel=2e-5)
+        assert float(losses[k, 2]) == pytest.approx(t[2], rel=2e-5)
+    assert_close_scaled(unpadded(eng.grad, m.offsets, m.sizes), g["g_clip_9"], 2e-5, "clipped grad, epoch 9")
+    assert_close_scaled(unpadded(m.flat, m.offsets, m.sizes), g["theta_9"], 1e-5, "theta after 10 epochs")
+    assert_close_scaled(unpadded(eng.m, m.offsets, m.sizes), g["m_final"], 2e-5, "m")
+    assert_close_scaled(unpadded(eng.v, m.offsets, m.sizes), g["v_final"], 2e-5, "v")
+
+
+def test_engine_vs_oracle_c2_shape_ten_epochs():
+    """C2 (HalfCheetah shape, reference arch, T = B = 2048, 10 epochs) end to end through
+    K4 -> K1 -> 10 x (K2 -> K3) from a host rollout, against the oracle on the same data
+    and the same random.sample stream."""
+    import b200_native as nv
+    from b200_engine import UpdateEngine
+    from model import Model, Shared_grad_buffers, Shared_obs_stats
+    from synthetic import make_rollout
+    torch.manual_seed(1)
+    m = Model(17, 6, device=DEV)
+    stats = Shared_obs_stats(17)
+    T = B = 2048
+    E = 10
+    host, dev = make_rollout(m, stats, T, seed=3, flavour=nv.FLAVOUR_DPPO, seg_len=700)
+    p0 = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    sgb = Shared_grad_buffers(m)
+    eng = UpdateEngine(m, nv.FLAVOUR_DPPO, B, E, 3e-4)
+    rng = random.Random(5)
+    loss, h2d, d2h = eng.update_from_host(host, dev, obs_stats=stats, rng=rng)
+    assert h2d > T * 17 * 4 and d2h == E * 4 * 4
+    # oracle on the same inputs
+    st = orc.welford_new(17)
+    states = orc.welford_observe_normalize(st, host.raw_obs.clone())
+    assert_close_scaled(dev.obs.cpu(), states, 1e-5, "states")
+    adv, ret = orc.gae(host.rew.numpy(), host.val.numpy(), host.boot.numpy(), host.seg_end.numpy())
+    assert_close_scaled(dev.adv.cpu(), adv, 1e-5, "adv")
+    rng = random.Random(5)
+    idx = [orc.sample_indices(T, B, rng) for _ in range(E)]
+    assert np.array_equal(np.asarray(idx, np.int32), eng.idx_host.numpy())        # indices bit-exact
+    p = {k: v.clone() for k, v in p0.items()}
+    mo, vo = orc.zeros_like_params(p), orc.zeros_like_params(p)
+    gsh = orc.zeros_like_params(p, 0.0)
+    worker = dict(states=dev.obs.cpu(), actions=host.act.clone(), returns=dev.ret.cpu().reshape(-1, 1),
+                  advantages=dev.adv.cpu().reshape(-1, 1))
+    terms = []
+    orc.dppo_update_cycle(p, mo, vo, 0, [worker], [idx], gsh, lr=3e-4, num_epoch=E,
+                          record=lambda k, w, t, gr: terms.append(t))
+    for k in range(E):
+        assert float(loss[k, 0]) == pytest.approx(terms[k]["loss_clip"], rel=1e-4, abs=1e-6)
+        assert float(loss[k, 1]) == pytest.approx(terms[k]["loss_value"], rel=1e-4)
+    assert_close_scaled(unpadded(m.flat, m.offsets, m.sizes), orc.flatten(p), 1e-5, "theta after 10 epochs")
+    assert eng.step == E
