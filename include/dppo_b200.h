@@ -135,6 +135,20 @@ int dppo_reduce_adam(const float* partials, int nparts, float* gshared,
                      const float* loss_partials, float* loss_out,
                      void* scratch, size_t scratch_bytes, void* stream);
 
+/* ---- a4: minibatch positions (HOST function, no GPU work) ------------------
+ * Replaces ``random.sample(self.memory, batch_size)`` (train.py:31-33 /
+ * ppo.py:58-60): `rounds` consecutive samples of k distinct positions out of
+ * range(n), bit-identical to CPython 3.12 random.sample driven by the same
+ * Mersenne Twister.  mt_state624_host / mt_index_host are the 624 state words
+ * and the position taken from ``random.getstate()[1]``; both are advanced in
+ * place so the caller can ``random.setstate`` them back.  out_host[rounds*k]. */
+int dppo_sample_indices_host(uint32_t* mt_state624_host, int* mt_index_host, int64_t n, int k, int rounds,
+                             int32_t* out_host);
+
+/* ---- bench utility: FP32 FMA throughput probe (no reference counterpart) ---
+ * Launches 8 CTAs per SM of dependent-chain FMAs; *flops_host = FLOPs issued. */
+int dppo_fp32_probe(int iters, float* out, double* flops_host, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -99,9 +99,9 @@ class UpdateEngine:
     # ---- minibatch positions (a4) --------------------------------------------------------------
     def draw_indices(self, T, rng=random):
         """E minibatches of B positions, exactly ReplayMemory.sample's index stream
-        (``random.sample`` without replacement, independent per epoch; train.py:31-33)."""
-        for k in range(self.E):
-            self.idx_host[k] = torch.tensor(rng.sample(range(T), self.B), dtype=torch.int32)
+        (``random.sample`` without replacement, independent per epoch; train.py:31-33),
+        generated by the C restatement of CPython's algorithm on ``rng``'s own state."""
+        nv.sample_indices(T, self.B, self.E, rng=rng, out=self.idx_host)
         return self.idx_host
 
     # ---- E x (K2 -> K3) -----------------------------------------------------------------------
@@ -167,7 +167,7 @@ class UpdateEngine:
         return self.loss_out
 
     # ---- whole outer iteration from a host rollout (the end-to-end call) ----------------------
-    def update_from_host(self, host, dev, obs_stats=None, rng=random, use_graph=True):
+    def update_from_host(self, host, dev, obs_stats=None, rng=random, use_graph=True, gshared=None):
         """H2D copy of one rollout (pinned ``host`` buffer -> ``dev``), K4 (if obs_stats),
         K1, E x (K2,K3), D2H copy of the per-epoch losses.  Returns (loss_host, h2d_bytes,
         d2h_bytes)."""
@@ -181,7 +181,7 @@ class UpdateEngine:
         if obs_stats is not None:
             obs_stats.observes_batch(dev.raw_obs, out=dev.obs)
         self.gae(dev)
-        self.run_epochs(dev, use_graph=use_graph, indices_staged=True)
+        self.run_epochs(dev, gshared=gshared, use_graph=use_graph, indices_staged=True)
         self.loss_host.copy_(self.loss_out, non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return self.loss_host, h2d, self.loss_host.numel() * 4

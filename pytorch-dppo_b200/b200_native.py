@@ -63,6 +63,8 @@ def _load():
         "dppo_update_partials_bytes": (sz, [dp, i32]),
         "dppo_update_fused": (i32, [i32, dp, vp, vp, vp, vp, vp, vp, i32, vp, vp, flt, flt, vp, vp, vp]),
         "dppo_reduce_adam_scratch_bytes": (sz, [i32]),
+        "dppo_sample_indices_host": (i32, [c.POINTER(c.c_uint32), c.POINTER(i32), i64, i32, i32, c.POINTER(c.c_int32)]),
+        "dppo_fp32_probe": (i32, [i32, vp, c.POINTER(dbl), vp]),
         "dppo_adam_scalars_host": (i32, [i32, dbl, dbl, dbl, dbl, c.POINTER(flt)]),
         "dppo_reduce_adam": (i32, [vp, i32, vp, vp, vp, vp, vp, i32, i32, dbl, dbl, dbl, dbl, vp, dbl, vp, vp, vp, vp, sz, vp]),
     }
@@ -165,3 +167,41 @@ def reduce_adam(partials, nparts, gshared, theta, theta_prev, m, v, step, lr, be
                                _ptr(loss_partials, allow_none=True), _ptr(loss_out, allow_none=True),
                                _ptr(scratch, torch.uint8, allow_none=True), 0 if scratch is None else scratch.numel(),
                                _stream()))
+
+
+def sample_indices(n, k, rounds=1, rng=None, out=None):
+    """``rounds`` x ``random.sample(range(n), k)`` as an int32 (rounds,k) CPU tensor,
+    bit-identical to Python's and leaving ``rng`` (default: the ``random`` module's
+    generator) in the state Python's own calls would have left it in."""
+    import random as _random
+    rng = _random if rng is None else rng
+    ver, internal, gauss = rng.getstate()
+    state = (ctypes.c_uint32 * 624)(*internal[:624])
+    index = ctypes.c_int(internal[624])
+    if out is None:
+        out = torch.empty(rounds, k, dtype=torch.int32)
+    if out.dtype != torch.int32 or not out.is_contiguous() or out.numel() < rounds * k or out.is_cuda:
+        raise DppoError("sample_indices: out must be a contiguous int32 CPU tensor of rounds*k elements")
+    if rounds * k == 0:
+        if k > n or n < 1:
+            raise DppoError("sample_indices: need 1 <= n and k <= n")
+        return out                                  # random.sample(pop, 0) draws nothing
+    check(lib.dppo_sample_indices_host(state, ctypes.byref(index), n, k, rounds,
+                                       ctypes.cast(out.data_ptr(), ctypes.POINTER(ctypes.c_int32))))
+    rng.setstate((ver, tuple(state) + (index.value,), gauss))
+    return out
+
+
+def fp32_probe(iters=4096):
+    """Measured FP32 FMA throughput of this GPU in TFLOP/s (best of 5)."""
+    out = torch.zeros(4, device="cuda")
+    flops = ctypes.c_double(0)
+    best = 0.0
+    for _ in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        check(lib.dppo_fp32_probe(iters, _ptr(out), ctypes.byref(flops), _stream()))
+        e1.record()
+        e1.synchronize()
+        best = max(best, flops.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best
