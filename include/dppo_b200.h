@@ -33,6 +33,7 @@ extern "C" {
 #define DPPO_E_SCRATCH   (-3)   /* scratch buffer smaller than *_scratch_bytes says */
 #define DPPO_E_ALIGN     (-4)   /* pointer not aligned as documented */
 #define DPPO_E_COMM      (-5)   /* communicator misuse */
+#define DPPO_E_NOALLOC_LIMIT (-6) /* size beyond the built-in scratch of a *_noalloc entry point */
 
 #define DPPO_FLAVOUR_DPPO 0     /* train.py:140-166: per-dim pdf ratio, clipped value loss */
 #define DPPO_FLAVOUR_PPO  1     /* ppo.py:147-172 : log-prob ratio, plain value loss, entropy */
@@ -70,6 +71,19 @@ size_t dppo_gae_scratch_bytes(int64_t T);
 int dppo_gae_scan(const float* rewards, const float* values, const float* boot, const uint8_t* seg_end,
                   float* adv, float* ret, int64_t T, double gamma, double lam,
                   void* scratch, size_t scratch_bytes, void* stream);
+
+/* dppo_gae_scan for callers that cannot allocate scratch (no counterpart in the
+ * reference; added for host programs that own no device allocator or must not call
+ * cudaMalloc while running).  Same inputs, outputs and results as dppo_gae_scan; the
+ * look-back chain lives in a ~24 KB array inside the library image, resident on every
+ * GPU that loads the library.  T <= DPPO_GAE_NOALLOC_MAX_T, otherwise
+ * DPPO_E_NOALLOC_LIMIT.  The first call on a device resolves the array's device address:
+ * make it before any stream capture.  Allocates and frees nothing.  All calls on a
+ * device share the array (flags are re-cleared on `stream` each call): calls that may
+ * overlap on the GPU race and must be serialised by the caller. */
+#define DPPO_GAE_NOALLOC_MAX_T 4194304
+int dppo_gae_scan_noalloc(const float* rewards, const float* values, const float* boot, const uint8_t* seg_end,
+                          float* adv, float* ret, int64_t T, double gamma, double lam, void* stream);
 
 /* ---- K4: running observation statistics --------------------------------
  * Replaces Shared_obs_stats.observes + normalize (model.py:68-80) applied row

@@ -57,6 +57,7 @@ def _load():
         "dppo_param_layout": (i32, [dp, c.POINTER(i32), c.POINTER(i32)]),
         "dppo_gae_scratch_bytes": (sz, [i64]),
         "dppo_gae_scan": (i32, [vp, vp, vp, vp, vp, vp, i64, dbl, dbl, vp, sz, vp]),
+        "dppo_gae_scan_noalloc": (i32, [vp, vp, vp, vp, vp, vp, i64, dbl, dbl, vp]),
         "dppo_welford_scratch_bytes": (sz, [i64, i32]),
         "dppo_welford": (i32, [vp, vp, i64, i32, vp, vp, vp, vp, vp, sz, vp]),
         "dppo_update_nparts": (i32, [dp, i32]),
@@ -120,6 +121,17 @@ def gae_scan(rewards, values, boot, seg_end, adv, ret, gamma, lam, scratch):
     T = rewards.numel()
     check(lib.dppo_gae_scan(_ptr(rewards), _ptr(values), _ptr(boot), _ptr(seg_end, torch.uint8), _ptr(adv), _ptr(ret),
                             T, gamma, lam, _ptr(scratch, torch.uint8), scratch.numel(), _stream()))
+
+
+GAE_NOALLOC_MAX_T = 4194304
+
+
+def gae_scan_noalloc(rewards, values, boot, seg_end, adv, ret, gamma, lam):
+    """K1 without caller scratch, for users who cannot allocate device memory at call time
+    (the look-back chain sits in an array built into the library).  At most GAE_NOALLOC_MAX_T
+    steps; calls on one device must not overlap; first call per device outside stream capture."""
+    check(lib.dppo_gae_scan_noalloc(_ptr(rewards), _ptr(values), _ptr(boot), _ptr(seg_end, torch.uint8), _ptr(adv),
+                                    _ptr(ret), rewards.numel(), gamma, lam, _stream()))
 
 
 def welford_scratch_bytes(T, O):

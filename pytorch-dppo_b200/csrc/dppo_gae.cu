@@ -212,3 +212,60 @@ extern "C" int dppo_gae_scan(const float* rewards, const float* values, const fl
     DPPO_LAUNCH_CHECK();
     return 0;
 }
+
+// ---------------------------------------------------------------------------
+// dppo_gae_scan_noalloc - the same scan for callers that cannot hand us scratch.
+//
+// dppo_gae_scan needs a few bytes per 2048-step tile for the look-back chain, and
+// it expects the caller to allocate them.  Some callers cannot: a host program
+// that was given a fixed set of device buffers by someone else's allocator and
+// has no allocator of its own; a control loop that must not call cudaMalloc
+// because cudaMalloc synchronises the whole device and may fail late; code that
+// runs after the application has frozen its memory pool.  For them the chain
+// lives in the array below, which is part of the library image: every GPU that
+// loads libdppo_b200.so keeps these ~24 KB resident until the process exits.
+//
+// Limits and rules
+//   * T <= DPPO_GAE_NOALLOC_MAX_T (4 194 304 steps); longer buffers are refused
+//     with DPPO_E_NOALLOC_LIMIT - use dppo_gae_scan with your own scratch.
+//   * The first call on each device looks up the device address of the array
+//     (cudaGetSymbolAddress, with that device current) and caches it.  Make that
+//     first call outside of any stream capture.
+//   * Nothing is allocated or freed, here or in anything this calls.
+//   * All calls on a device share the one array.  The flags that must start at
+//     zero are cleared on `stream` at the start of every call; everything else is
+//     overwritten before it is read.  Two calls that can overlap on the GPU
+//     (different streams, no dependency between them) race on it - serialise them.
+// ---------------------------------------------------------------------------
+#define DPPO_GAE_NOALLOC_MAX_TILES ((DPPO_GAE_NOALLOC_MAX_T + GAE_TILE - 1) / GAE_TILE)
+#define DPPO_GAE_NOALLOC_FLAG_BYTES ((sizeof(int) * (1 + DPPO_GAE_NOALLOC_MAX_TILES) + 15) / 16 * 16)
+#define DPPO_GAE_NOALLOC_BYTES (DPPO_GAE_NOALLOC_FLAG_BYTES + sizeof(float2) * DPPO_GAE_NOALLOC_MAX_TILES)
+
+static __device__ __align__(256) unsigned char g_gae_noalloc_scratch[DPPO_GAE_NOALLOC_BYTES];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+void* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};      // device address of the array, per device
+}  // namespace
+
+extern "C" int dppo_gae_scan_noalloc(const float* rewards, const float* values, const float* boot,
+                                     const uint8_t* seg_end, float* adv, float* ret, int64_t T, double gamma,
+                                     double lam, void* stream) {
+    if (T < 0) return DPPO_E_BADARG;
+    if (T > (int64_t)DPPO_GAE_NOALLOC_MAX_T) return DPPO_E_NOALLOC_LIMIT;
+    if (T == 0) return 0;
+    int dev = -1;
+    DPPO_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return DPPO_E_BADARG;
+    if (g_noalloc_ptr[dev] == nullptr) {
+        // In host code `g_gae_noalloc_scratch` is only a handle for the symbol, not an address the
+        // GPU can use: ask the runtime where the array lives on THIS device.
+        void* p = nullptr;
+        DPPO_CUDA_TRY(cudaGetSymbolAddress(&p, g_gae_noalloc_scratch));
+        if (p == nullptr) return DPPO_E_BADARG;
+        g_noalloc_ptr[dev] = p;
+    }
+    static_assert(DPPO_GAE_NOALLOC_MAX_T % GAE_TILE == 0, "maximum must be a whole number of tiles");
+    return dppo_gae_scan(rewards, values, boot, seg_end, adv, ret, T, gamma, lam, g_noalloc_ptr[dev],
+                         (size_t)DPPO_GAE_NOALLOC_BYTES, stream);
+}

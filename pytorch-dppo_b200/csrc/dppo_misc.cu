@@ -11,6 +11,9 @@ extern "C" const char* dppo_error_string(int code) {
         case DPPO_E_SCRATCH: return "dppo: scratch buffer too small (see *_scratch_bytes)";
         case DPPO_E_ALIGN: return "dppo: pointer not 16-byte aligned";
         case DPPO_E_COMM: return "dppo: communicator misuse";
+        case DPPO_E_NOALLOC_LIMIT:
+            return "dppo: size exceeds the built-in scratch of this *_noalloc entry point (dppo_gae_scan_noalloc: "
+                   "T <= 4194304 steps); call the variant that takes caller-provided scratch";
         default: break;
     }
     if (code > 0) return cudaGetErrorString((cudaError_t)code);
