@@ -19,13 +19,24 @@
 // dimension; rows are interleaved over threads and leading dimensions are odd
 // multiples of 16 B so the quarter-warp phases are bank-conflict free.
 #include <math.h>
+#include <stdio.h>
 #include "common.cuh"
+
+// per-phase clock64() stamps of CTA 0 (tools/k2clock.py); compiled in with -DDPPO_K2_TIMING only
+#ifdef DPPO_K2_TIMING
+__device__ long long g_k2_clock[64];
+#define K2_TICK(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_k2_clock[i] = clock64(); } while (0)
+#else
+#define K2_TICK(i) do { } while (0)
+#endif
 
 namespace {
 
 constexpr int UPD_THREADS = 256;
 constexpr int UPD_TM_MAX = 32;
-constexpr int UPD_STAGE = 5120;             // floats per weight staging buffer (20 KB)
+constexpr int UPD_STAGE_MAX = 10240;        // floats per weight staging buffer (40 KB), two buffers
+constexpr int UPD_STAGE_MIN = 4096;
+constexpr int UPD_ROWS = 32;                // sample rows per CTA tile (TM <= 32 of them are real)
 constexpr int UPD_MAX_A = 64;
 constexpr int UPD_MAX_WIDTH = 1024;
 
@@ -60,6 +71,8 @@ struct UpdArgs {
     int ldO, ldH1, ldH2, ldG1, ldG2, ldA;
     int o_x, o_h1, o_h2, o_g1, o_g2, o_act, o_mu, o_muo, o_dmu, o_v, o_vo, o_dv, o_adv, o_ret, o_lpo, o_red, o_stage;
     int smem_floats;
+    int SF;                                     // floats per weight staging buffer
+    int o_zero_end, o_heads, head_floats, o_bars;
 };
 
 __device__ __forceinline__ Net net_of(const float* t, const Layout& L) {
@@ -78,104 +91,266 @@ __device__ __forceinline__ GradOut grad_of(float* t, const Layout& L) {
 }
 
 // ---------------------------------------------------------------------------
-// forward layer: out[m][n] = act(sum_k in[m][k] W[n][k] + b[n]),  m < TM, n < N
-// in: smem [TM][ldin] (zero beyond K); W: global row-major [N][K]; out: smem [TM][ldout]
+// TMA bulk copies (cp.async.bulk, global -> shared, completion on an mbarrier): one
+// instruction moves a whole weight row (or a whole block of rows), so staging costs no
+// address arithmetic per element.  bar_phase[b] tracks the parity of stage buffer b.
 // ---------------------------------------------------------------------------
-template <bool TANH>
-__device__ void fwd_layer(const float* __restrict__ W, const float* __restrict__ bias, int N, int K,
-                          const float* in, int ldin, float* out, int ldout, int TM, float* stage) {
-    const int MG = TM >> 2;                                  // row groups (TM is a multiple of 4)
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, unsigned parity) {
+    unsigned ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"((unsigned)__cvta_generic_to_shared(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+#ifdef DPPO_K2_SPINTRAP
+    long long spin = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spin > 4000000) { printf("mbar_wait stuck: block %d thread %d parity %u\n", blockIdx.x, threadIdx.x, parity); __trap(); }
+    }
+#else
+    while (!mbar_try_wait(bar, parity)) { }
+#endif
+}
+__device__ __forceinline__ void bulk_g2s(float* smem, const float* gmem, unsigned bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     (unsigned)__cvta_generic_to_shared(smem)),
+                 "l"(gmem), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar))
+                 : "memory");
+}
+
+// rows [n0, n0+nrows) x columns [k0, k0+kc) of W[N][K] -> dst[nn][lds]; K % 4 == 0, k0 % 4 == 0,
+// W 16-byte aligned.  Rows >= N and columns >= K are NOT written (callers never let them reach a
+// kept accumulator).  One bulk copy per row, issued by as many threads as there are rows.
+__device__ __forceinline__ void stage_rows_bulk(float* dst, int lds, const float* __restrict__ W, int N, int K, int n0,
+                                                int nrows, int k0, int kc, uint64_t* bar) {
+    const int vr = min(nrows, N - n0);
+    const int cols = min(kc, K - k0);
+    if (vr <= 0 || cols <= 0) { if (threadIdx.x == 0) mbar_expect_tx(bar, 0); return; }
+    if (threadIdx.x == 0) mbar_expect_tx(bar, (unsigned)(vr * cols * 4));
+    for (int r = threadIdx.x; r < vr; r += UPD_THREADS)
+        bulk_g2s(dst + r * lds, W + (size_t)(n0 + r) * K + k0, (unsigned)(cols * 4), bar);
+}
+// nfloats contiguous floats (multiple of 4, 16-byte aligned source) -> dst, one bulk copy
+__device__ __forceinline__ void stage_flat_bulk(float* dst, const float* __restrict__ src, int nfloats, uint64_t* bar) {
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(bar, (unsigned)(nfloats * 4));
+        if (nfloats > 0) bulk_g2s(dst, src, (unsigned)(nfloats * 4), bar);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// forward layer: out[m][n] = act(sum_k in[m][k] W[n][k] + b[n]),  m < 32, n < N
+// in: smem [32][ldin] (finite beyond K); W: global row-major [N][K]; out: smem [32][ldout]
+//
+// Warp tile: 32 rows x 4*CN columns; lanes are 8 (rows) x 4 (columns), a thread owns rows
+// mi+8i and columns c0+ni+4j, so per 4-deep k step a warp issues 4 + CN 128-bit shared loads
+// (one wavefront each: 8 resp. 4 distinct 16-byte rows) for 16*CN FFMAs.  The 8 warps form
+// NW column blocks x KW k-splits; k-split partners are summed through shared memory.
+// ---------------------------------------------------------------------------
+template <int CN, bool TANH>
+__device__ __noinline__ unsigned fwd_layer_t(const float* __restrict__ W, const float* __restrict__ bias, int N, int K, const float* in,
+                            int ldin, float* out, int ldout, float* stage, int SF, uint64_t* bars, unsigned ph) {
+    constexpr int NWARPS = UPD_THREADS / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int mi = lane >> 2, ni = lane & 3;
     const int Kp = (K + 3) & ~3;
-    const bool vecW = ((K & 3) == 0) && aligned16_dev(W);
-    // column chunk: as many 4-column groups as threads allow, bounded by the stage
-    int NGmax = UPD_THREADS / MG;
-    for (int n0 = 0; n0 < N; n0 += 4 * NGmax) {
-        const int NCH = min(N - n0, 4 * NGmax);
-        const int NG = (NCH + 3) >> 2;
-        const int NCHp = NG * 4;
-        int KC = Kp;                                         // k-chunk so that NCHp*ld(KC) fits the stage
-        while (NCHp * ld_of(KC) > UPD_STAGE) KC = ((KC >> 1) + 3) & ~3;
-        const int ni = threadIdx.x % NG, mi = threadIdx.x / NG;
-        const bool active = mi < MG;
-        float acc[4][4];
+    const bool vecW = (K & 3) == 0;                          // buckets are 16-byte aligned by construction
+    int NW = (N + 4 * CN - 1) / (4 * CN);                     // column blocks needed
+    if (NW > NWARPS) NW = NWARPS;
+    int KW = 1;                                               // k-splits: largest power of two with NW*KW <= 8
+    while (NW * KW * 2 <= NWARPS && (Kp >> 2) >= KW * 2) KW *= 2;
+    const int cw = warp % NW, kw = warp / NW;
+    const bool wactive = kw < KW;
+    const int colsPerPass = NW * 4 * CN;
+    for (int n0 = 0; n0 < N; n0 += colsPerPass) {
+        const int nrows = min(colsPerPass, ((N - n0 + 4 * CN - 1) / (4 * CN)) * 4 * CN);
+        // k-chunk: multiple of 4*KW, stage rows padded to an odd number of 16-byte units.
+        // flat mode (K % 4 != 0, first layers): the whole row block is one contiguous piece of W,
+        // copied as is (row stride K) and read with scalar loads.
+        int KC = (SF / nrows - 4) & ~(4 * KW - 1);
+        if (KC > ((Kp + 4 * KW - 1) / (4 * KW)) * 4 * KW) KC = ((Kp + 4 * KW - 1) / (4 * KW)) * 4 * KW;
+        const bool flat = !vecW;
+        const int vr = min(nrows, N - n0);
+        if (flat) KC = Kp;
+        const int lds = flat ? K : ld_of(KC);
+        const int nchunks = flat ? 1 : (Kp + KC - 1) / KC;
+        float acc[4][CN];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-        for (int k0 = 0; k0 < Kp; k0 += KC) {
-            const int kc = min(KC, Kp - k0);
-            const int lds = ld_of(kc);
-            __syncthreads();                                 // previous chunk fully consumed
-            // stage W[n0 .. n0+NCHp)[k0 .. k0+kc) -> stage[nn][lds], zero-filled outside (N,K)
-            const int q = kc >> 2;
-            for (int e = threadIdx.x; e < NCHp * q; e += UPD_THREADS) {
-                const int nn = e / q, kq = e - nn * q;
-                const int n = n0 + nn, k = k0 + 4 * kq;
-                float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (n < N) {
-                    const float* src = W + (size_t)n * K + k;
-                    if (vecW) w = __ldg(reinterpret_cast<const float4*>(src));
-                    else {
-                        if (k + 0 < K) w.x = __ldg(src + 0);
-                        if (k + 1 < K) w.y = __ldg(src + 1);
-                        if (k + 2 < K) w.z = __ldg(src + 2);
-                        if (k + 3 < K) w.w = __ldg(src + 3);
+            for (int j = 0; j < CN; ++j) acc[i][j] = 0.f;
+        float bb[CN];
+#pragma unroll
+        for (int j = 0; j < CN; ++j) {
+            const int n = n0 + cw * 4 * CN + ni + 4 * j;
+            bb[j] = (wactive && kw == 0 && n < N) ? __ldg(bias + n) : 0.f;
+        }
+        __syncthreads();                                      // stage buffers free, `in` complete, barriers ready
+        if (flat) {
+            const int nfl = vr * K;
+            stage_flat_bulk(stage, W + (size_t)n0 * K, nfl & ~3, &bars[0]);
+            if (threadIdx.x == 32)
+                for (int e = nfl & ~3; e < nfl; ++e) stage[e] = __ldg(W + (size_t)n0 * K + e);
+        } else {
+            stage_rows_bulk(stage, lds, W, N, K, n0, nrows, 0, KC, &bars[0]);
+        }
+        for (int c = 0; c < nchunks; ++c) {
+            mbar_wait(&bars[c & 1], (ph >> (c & 1)) & 1u);    // chunk c has landed
+            ph ^= 1u << (c & 1);
+            __syncthreads();                                  // everyone is done with chunk c-1
+            if (c + 1 < nchunks)
+                stage_rows_bulk(stage + ((c + 1) & 1) * SF, lds, W, N, K, n0, nrows, (c + 1) * KC, KC, &bars[(c + 1) & 1]);
+            if (wactive && cw * 4 * CN < nrows) {
+                if (flat) {
+                    // rows beyond N were not staged: clamp them (their accumulators are dropped)
+                    const float* sbj[CN];
+#pragma unroll
+                    for (int j = 0; j < CN; ++j) sbj[j] = stage + min(cw * 4 * CN + ni + 4 * j, vr - 1) * K;
+                    const int ksub = (K + KW - 1) / KW;
+                    const int kend = min(kw * ksub + ksub, K);
+                    const float* a0 = in + mi * ldin;
+                    for (int k = kw * ksub; k < kend; ++k) {
+                        float a[4], b[CN];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) a[i] = a0[(8 * i) * ldin + k];
+#pragma unroll
+                        for (int j = 0; j < CN; ++j) b[j] = sbj[j][k];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+#pragma unroll
+                            for (int j = 0; j < CN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
                     }
-                }
-                *reinterpret_cast<float4*>(stage + nn * lds + 4 * kq) = w;
-            }
-            __syncthreads();
-            if (active) {
-                const float* a0 = in + mi * ldin + k0;
-                const float* b0 = stage + ni * lds;
-                for (int kk = 0; kk < kc; kk += 4) {
-                    float4 a[4], b[4];
+                } else {
+                    const float* sb = stage + (c & 1) * SF + (cw * 4 * CN + ni) * lds;
+                    const int ksub = KC / KW;                 // this warp's slice of the chunk
+                    const int kbeg = kw * ksub;
+                    const int kend = min(kbeg + ksub, Kp - c * KC);
+                    const float* a0 = in + mi * ldin + c * KC;
+                    for (int kk = kbeg; kk < kend; kk += 4) {
+                        float4 a[4], b[CN];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(a0 + (i * MG) * ldin + kk);
+                        for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(a0 + (8 * i) * ldin + kk);
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) b[j] = *reinterpret_cast<const float4*>(b0 + (j * NG) * lds + kk);
+                        for (int j = 0; j < CN; ++j) b[j] = *reinterpret_cast<const float4*>(sb + (4 * j) * lds + kk);
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
+                        for (int i = 0; i < 4; ++i)
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            acc[i][j] = fmaf(a[i].x, b[j].x, acc[i][j]);
-                            acc[i][j] = fmaf(a[i].y, b[j].y, acc[i][j]);
-                            acc[i][j] = fmaf(a[i].z, b[j].z, acc[i][j]);
-                            acc[i][j] = fmaf(a[i].w, b[j].w, acc[i][j]);
-                        }
+                            for (int j = 0; j < CN; ++j) {
+                                acc[i][j] = fmaf(a[i].x, b[j].x, acc[i][j]);
+                                acc[i][j] = fmaf(a[i].y, b[j].y, acc[i][j]);
+                                acc[i][j] = fmaf(a[i].z, b[j].z, acc[i][j]);
+                                acc[i][j] = fmaf(a[i].w, b[j].w, acc[i][j]);
+                            }
+                    }
                 }
             }
         }
-        if (active) {
+        // k-split partners: kw = KW-1 .. 1 hand their partial tiles over through shared memory
+        for (int r = KW - 1; r >= 1; --r) {
+            __syncthreads();                                  // stage buffers no longer read / previous round consumed
+            if (wactive && kw == r) {
+                float* sc = stage + (cw * 32) * (4 * CN);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int n = n0 + ni + j * NG;
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < CN; ++j) sc[(mi + 8 * i) * (4 * CN) + ni + 4 * j] = acc[i][j];
+            }
+            __syncthreads();
+            if (wactive && kw == 0) {
+                const float* sc = stage + (cw * 32) * (4 * CN);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < CN; ++j) acc[i][j] += sc[(mi + 8 * i) * (4 * CN) + ni + 4 * j];
+            }
+        }
+        if (wactive && kw == 0) {
+#pragma unroll
+            for (int j = 0; j < CN; ++j) {
+                const int n = n0 + cw * 4 * CN + ni + 4 * j;
                 if (n < N) {
-                    const float bb = __ldg(bias + n);
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
-                        float y = acc[i][j] + bb;
+                        float y = acc[i][j] + bb[j];
                         if (TANH) y = tanhf(y);
-                        out[(mi + i * MG) * ldout + n] = y;
+                        out[(mi + 8 * i) * ldout + n] = y;
                     }
                 }
             }
         }
     }
     __syncthreads();
+    return ph;
 }
 
-// tiny head (N <= A or 1): one warp per output, lanes over k
-__device__ void head_fwd(const float* __restrict__ W, const float* __restrict__ bias, int N, int K, const float* in,
-                         int ldin, float* out, int ldout, int TM) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int o = warp; o < TM * N; o += UPD_THREADS / 32) {
-        const int m = o / N, n = o - m * N;
-        float s = 0.f;
-        for (int k = lane; k < K; k += 32) s = fmaf(in[m * ldin + k], __ldg(W + (size_t)n * K + k), s);
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
-        if (lane == 0) out[m * ldout + n] = s + __ldg(bias + n);
+template <bool TANH>
+__device__ __forceinline__ unsigned fwd_layer(const float* __restrict__ W, const float* __restrict__ bias, int N, int K,
+                                          const float* in, int ldin, float* out, int ldout, float* stage, int SF,
+                                          uint64_t* bars, unsigned ph) {
+    // 4*CN columns per warp: 28 fits N = 100 (reference widths) in four blocks, 32 otherwise
+    const int blocks32 = (N + 31) / 32;
+    if (N > 28 * (blocks32 - 1) && N <= 28 * blocks32 && blocks32 <= 8)
+        return fwd_layer_t<7, TANH>(W, bias, N, K, in, ldin, out, ldout, stage, SF, bars, ph);
+    return fwd_layer_t<8, TANH>(W, bias, N, K, in, ldin, out, ldout, stage, SF, bars, ph);
+}
+
+// head weights (mu: [A][ldH2] + bias[A], v: [ldG2] + bias) of one network, resident in shared
+// memory for the whole kernel (they are tiny and every tile needs them four times)
+struct HeadS { const float *Wmu, *bmu, *Wv, *bv; };
+
+__device__ __forceinline__ void load_heads(float* dst, const Net& nw, const UpdArgs& P) {
+    const dppo_dims& d = P.d;
+    for (int e = threadIdx.x; e < d.A * d.H2; e += UPD_THREADS) {
+        const int n = e / d.H2, k = e - n * d.H2;
+        dst[n * P.ldH2 + k] = __ldg(nw.Wmu + e);
+    }
+    float* b = dst + d.A * P.ldH2;
+    for (int e = threadIdx.x; e < d.A; e += UPD_THREADS) b[e] = __ldg(nw.bmu + e);
+    float* wv = b + ((d.A + 3) & ~3);
+    for (int e = threadIdx.x; e < d.G2; e += UPD_THREADS) wv[e] = __ldg(nw.Wv + e);
+    if (threadIdx.x == 0) wv[P.ldG2] = __ldg(nw.bv);
+}
+__device__ __forceinline__ HeadS heads_at(const float* base, const UpdArgs& P) {
+    HeadS h;
+    h.Wmu = base;
+    h.bmu = base + P.d.A * P.ldH2;
+    h.Wv = h.bmu + ((P.d.A + 3) & ~3);
+    h.bv = h.Wv + P.ldG2;
+    return h;
+}
+
+// both heads of one network in one pass: thread (m, n) does one dot product from shared memory
+//   n < A : mu[m][n] = h2[m] . Wmu[n] + bmu[n]         n == A : v[m] = g2[m] . Wv + bv
+__device__ __noinline__ void heads_fwd(HeadS hs, int A, int H2, int G2, const float* h2, int ldh2, const float* g2,
+                                       int ldg2, float* mu_out, int ldA, float* v_out) {
+    for (int o = threadIdx.x; o < UPD_ROWS * (A + 1); o += UPD_THREADS) {
+        const int m = o / (A + 1), n = o - m * (A + 1);
+        const bool isv = n == A;
+        const float* x = isv ? g2 + m * ldg2 : h2 + m * ldh2;
+        const float* w = isv ? hs.Wv : hs.Wmu + n * ldh2;
+        const int K4 = ((isv ? G2 : H2) + 3) >> 2;          // pad columns: activations finite, weights 0
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        for (int k = 0; k < K4; ++k) {
+            const float4 a = *reinterpret_cast<const float4*>(x + 4 * k);
+            const float4 b = *reinterpret_cast<const float4*>(w + 4 * k);
+            s0 = fmaf(a.x, b.x, s0); s1 = fmaf(a.y, b.y, s1); s2 = fmaf(a.z, b.z, s2); s3 = fmaf(a.w, b.w, s3);
+        }
+        const float s = (s0 + s1) + (s2 + s3);
+        if (isv) v_out[m] = s + hs.bv[0];
+        else mu_out[m * ldA + n] = s + hs.bmu[n];
     }
     __syncthreads();
 }
@@ -183,60 +358,69 @@ __device__ void head_fwd(const float* __restrict__ W, const float* __restrict__ 
 // ---------------------------------------------------------------------------
 // dX through a tanh layer, in place:
 //   act[m][k] <- (sum_n dOut[m][n] W[n][k]) * (1 - act[m][k]^2),  k < K
-// dOut: smem [TM][ldd] (zero beyond N); W global [N][K]
+// dOut: smem [32][ldd] (zero beyond N); W global [N][K]; W rows stream through the stage.
+// Lanes are 8 (rows) x 4 (k-quads); a thread owns rows mi+8i and quads q0+ki+4j (j < KT).
 // ---------------------------------------------------------------------------
-constexpr int DX_KT = 4;                                     // k-quads per thread
-__device__ void dx_layer(const float* __restrict__ W, int N, int K, const float* dOut, int ldd, float* act, int lda,
-                         int TM, float* stage) {
-    const int MG = TM >> 2;
-    const int KQ = (K + 3) >> 2;                             // k-quads
-    const int Kp = KQ * 4;
-    const bool vecW = ((K & 3) == 0) && aligned16_dev(W);
-    const int KGL = UPD_THREADS / MG;                        // quad lanes per row group
+// rows [n0, n0+nc) of W[N][K] -> dst[nn][Kp] for the dX pass.  K % 4 == 0: the rows are one
+// contiguous block (one bulk copy); otherwise element-wise.  Rows >= N are zero-filled (they meet
+// dOut's zero padding; garbage there could be NaN).
+__device__ __forceinline__ void dx_stage(float* dst, const float* __restrict__ W, int N, int K, int Kp, int n0, int nc,
+                                         bool vec, uint64_t* bar) {
+    const int vr = max(0, min(nc, N - n0));
+    for (int e = vr * Kp + threadIdx.x; e < nc * Kp; e += UPD_THREADS) dst[e] = 0.f;
+    if (vec) {
+        stage_flat_bulk(dst, W + (size_t)n0 * K, vr * K, bar);
+    } else {
+        for (int e = threadIdx.x; e < vr * Kp; e += UPD_THREADS) {
+            const int r = e / Kp, k = e - r * Kp;
+            dst[e] = k < K ? __ldg(W + (size_t)(n0 + r) * K + k) : 0.f;
+        }
+        if (threadIdx.x == 0) mbar_expect_tx(bar, 0);
+    }
+}
+
+template <int KT>
+__device__ __noinline__ unsigned dx_layer_t(const float* __restrict__ W, int N, int K, const float* dOut, int ldd, float* act, int lda,
+                           float* stage, int SF, uint64_t* bars, unsigned ph) {
+    constexpr int NWARPS = UPD_THREADS / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int mi = lane >> 2, ki = lane & 3;
+    const int KQ = (K + 3) >> 2, Kp = KQ * 4;
+    const bool vecW = (K & 3) == 0;
     const int Np = (N + 3) & ~3;
-    int NC = (UPD_STAGE / Kp) & ~3;                          // rows of W per chunk
+    int NC = (SF / Kp) & ~3;                                 // rows of W per chunk
     if (NC > Np) NC = Np;
-    const int ki = threadIdx.x % KGL, mi = threadIdx.x / KGL;
-    const bool active = mi < MG;
-    for (int kq0 = 0; kq0 < KQ; kq0 += KGL * DX_KT) {        // usually a single pass
-        float acc[4][DX_KT][4];
+    const int nchunks = (Np + NC - 1) / NC;
+    for (int q0 = 0; q0 < KQ; q0 += NWARPS * 4 * KT) {       // usually a single pass
+        const int qb = q0 + warp * 4 * KT + ki;
+        float acc[4][KT][4];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int j = 0; j < DX_KT; ++j)
+            for (int j = 0; j < KT; ++j)
 #pragma unroll
                 for (int c = 0; c < 4; ++c) acc[i][j][c] = 0.f;
-        for (int n0 = 0; n0 < Np; n0 += NC) {
+        __syncthreads();
+        dx_stage(stage, W, N, K, Kp, 0, NC, vecW, &bars[0]);
+        for (int c = 0; c < nchunks; ++c) {
+            mbar_wait(&bars[c & 1], (ph >> (c & 1)) & 1u);
+            ph ^= 1u << (c & 1);
+            __syncthreads();
+            if (c + 1 < nchunks) dx_stage(stage + ((c + 1) & 1) * SF, W, N, K, Kp, (c + 1) * NC, NC, vecW, &bars[(c + 1) & 1]);
+            const int n0 = c * NC;
             const int nc = min(NC, Np - n0);
-            __syncthreads();
-            for (int e = threadIdx.x; e < nc * KQ; e += UPD_THREADS) {
-                const int nn = e / KQ, kq = e - nn * KQ;
-                const int n = n0 + nn, k = 4 * kq;
-                float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (n < N) {
-                    const float* src = W + (size_t)n * K + k;
-                    if (vecW) w = __ldg(reinterpret_cast<const float4*>(src));
-                    else {
-                        if (k + 0 < K) w.x = __ldg(src + 0);
-                        if (k + 1 < K) w.y = __ldg(src + 1);
-                        if (k + 2 < K) w.z = __ldg(src + 2);
-                        if (k + 3 < K) w.w = __ldg(src + 3);
-                    }
-                }
-                *reinterpret_cast<float4*>(stage + nn * Kp + 4 * kq) = w;
-            }
-            __syncthreads();
-            if (active) {
+            const float* sw = stage + (c & 1) * SF;
+            if (qb < KQ) {
                 for (int nn = 0; nn < nc; nn += 4) {
                     float4 a[4];
 #pragma unroll
                     for (int i = 0; i < 4; ++i)
-                        a[i] = *reinterpret_cast<const float4*>(dOut + (mi + i * MG) * ldd + n0 + nn);
+                        a[i] = *reinterpret_cast<const float4*>(dOut + (mi + 8 * i) * ldd + n0 + nn);
 #pragma unroll
-                    for (int j = 0; j < DX_KT; ++j) {
-                        const int kq = kq0 + ki + j * KGL;
+                    for (int j = 0; j < KT; ++j) {
+                        const int kq = qb + 4 * j;
                         if (kq < KQ) {
-                            const float* wp = stage + nn * Kp + 4 * kq;
+                            const float* wp = sw + nn * Kp + 4 * kq;
                             const float4 w0 = *reinterpret_cast<const float4*>(wp);
                             const float4 w1 = *reinterpret_cast<const float4*>(wp + Kp);
                             const float4 w2 = *reinterpret_cast<const float4*>(wp + 2 * Kp);
@@ -265,95 +449,208 @@ __device__ void dx_layer(const float* __restrict__ W, int N, int K, const float*
                 }
             }
         }
-        if (active) {
 #pragma unroll
-            for (int j = 0; j < DX_KT; ++j) {
-                const int kq = kq0 + ki + j * KGL;
-                if (kq < KQ) {
+        for (int j = 0; j < KT; ++j) {
+            const int kq = qb + 4 * j;
+            if (kq < KQ) {
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        float* ap = act + (mi + i * MG) * lda + 4 * kq;
-                        float4 h = *reinterpret_cast<float4*>(ap);
-                        h.x = acc[i][j][0] * (1.f - h.x * h.x);
-                        h.y = acc[i][j][1] * (1.f - h.y * h.y);
-                        h.z = acc[i][j][2] * (1.f - h.z * h.z);
-                        h.w = acc[i][j][3] * (1.f - h.w * h.w);
-                        // columns k >= K hold act = 0 and W = 0, so they stay 0
-                        *reinterpret_cast<float4*>(ap) = h;
-                    }
+                for (int i = 0; i < 4; ++i) {
+                    float* ap = act + (mi + 8 * i) * lda + 4 * kq;
+                    float4 h = *reinterpret_cast<float4*>(ap);
+                    h.x = acc[i][j][0] * (1.f - h.x * h.x);
+                    h.y = acc[i][j][1] * (1.f - h.y * h.y);
+                    h.z = acc[i][j][2] * (1.f - h.z * h.z);
+                    h.w = acc[i][j][3] * (1.f - h.w * h.w);
+                    // columns k >= K see W = 0 (zero-filled stage), so they stay finite
+                    *reinterpret_cast<float4*>(ap) = h;
                 }
             }
         }
     }
     __syncthreads();
+    return ph;
 }
 
-// dX through a tiny head (N small): act[m][k] <- (sum_n dOut[m][n] W[n][k]) (1 - act^2)
-__device__ void head_dx(const float* __restrict__ W, int N, int K, const float* dOut, int ldd, float* act, int lda,
-                        int TM) {
-    for (int e = threadIdx.x; e < TM * K; e += UPD_THREADS) {
-        const int m = e / K, k = e - m * K;
-        float s = 0.f;
-        for (int n = 0; n < N; ++n) s = fmaf(dOut[m * ldd + n], __ldg(W + (size_t)n * K + k), s);
-        const float h = act[m * lda + k];
-        act[m * lda + k] = s * (1.f - h * h);
+__device__ __forceinline__ unsigned dx_layer(const float* __restrict__ W, int N, int K, const float* dOut, int ldd,
+                                         float* act, int lda, float* stage, int SF, uint64_t* bars, unsigned ph) {
+    const int KQ = (K + 3) >> 2;
+    if (KQ > 64) return dx_layer_t<4>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
+    if (KQ > 32) return dx_layer_t<2>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
+    return dx_layer_t<1>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
+}
+
+// dX through a tiny head (N small), weights in shared memory [N][ldw] (zero beyond K):
+//   act[m][k] <- (sum_n dOut[m][n] W[n][k]) (1 - act[m][k]^2), four k per thread
+__device__ __noinline__ void head_dx(const float* Ws, int ldw, int N, int K, const float* dOut, int ldd, float* act,
+                                     int lda) {
+    const int KQ = (K + 3) >> 2;
+    for (int e = threadIdx.x; e < UPD_ROWS * KQ; e += UPD_THREADS) {
+        const int m = e / KQ, kq = e - m * KQ;
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int n = 0; n < N; ++n) {
+            const float dd = dOut[m * ldd + n];
+            const float4 w = *reinterpret_cast<const float4*>(Ws + n * ldw + 4 * kq);
+            s.x = fmaf(dd, w.x, s.x); s.y = fmaf(dd, w.y, s.y); s.z = fmaf(dd, w.z, s.z); s.w = fmaf(dd, w.w, s.w);
+        }
+        float4 h = *reinterpret_cast<float4*>(act + m * lda + 4 * kq);
+        h.x = s.x * (1.f - h.x * h.x); h.y = s.y * (1.f - h.y * h.y);
+        h.z = s.z * (1.f - h.z * h.z); h.w = s.w * (1.f - h.w * h.w);
+        *reinterpret_cast<float4*>(act + m * lda + 4 * kq) = h;
     }
     __syncthreads();
 }
 
 // ---------------------------------------------------------------------------
-// dW[n][k] (+)= sum_m dOut[m][n] in[m][k];  db[n] (+)= sum_m dOut[m][n]
-// written to this CTA's partial bucket (global).  m ascending: fixed order.
+// dW[n][k] (+)= sum_m dOut[m][n] in[m][k];  db[n] (+)= sum_m dOut[m][n]   (m < 32, ascending:
+// fixed order) written to this CTA's partial bucket (global).
+// Warp tile 16 n x 64 k; lanes are 4 (n-quads) x 8 (k-quads), a thread owns one n-quad and two
+// k-quads: 3 shared loads (one wavefront each) per 32 FFMAs.
 // ---------------------------------------------------------------------------
-__device__ void dw_layer(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut, int ldd,
-                         const float* in, int ldin, int TM, bool accumulate) {
+__device__ __noinline__ void dw_layer(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut, int ldd,
+                         const float* in, int ldin, bool accumulate) {
+    constexpr int NWARPS = UPD_THREADS / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nql = lane >> 3, kql = lane & 7;
     const int NQ = (N + 3) >> 2, KQ = (K + 3) >> 2;
+    const int NB = (NQ + 3) >> 2, KB = (KQ + 15) >> 4;
     const bool vecG = ((K & 3) == 0) && aligned16_dev(gW);
-    for (int t = threadIdx.x; t < NQ * KQ; t += UPD_THREADS) {
-        const int nq = t / KQ, kq = t - nq * KQ;
-        float acc[4][4];
+    for (int t = warp; t < NB * KB; t += NWARPS) {
+        const int nb = t / KB, kb = t - nb * KB;
+        const int nq = nb * 4 + nql;
+        const int kq0 = kb * 16 + kql, kq1 = kq0 + 8;
+        // clamp the read positions of out-of-range tiles (their results are dropped)
+        const float* dp = dOut + 4 * min(nq, NQ - 1);
+        const float* ip0 = in + 4 * min(kq0, KQ - 1);
+        const float* ip1 = in + 4 * min(kq1, KQ - 1);
+        float acc[4][8];
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-        const float* dp = dOut + 4 * nq;
-        const float* ip = in + 4 * kq;
+            for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
 #pragma unroll 4
-        for (int m = 0; m < TM; ++m) {
+        for (int m = 0; m < 32; ++m) {
             const float4 a = *reinterpret_cast<const float4*>(dp + m * ldd);
-            const float4 b = *reinterpret_cast<const float4*>(ip + m * ldin);
-            acc[0][0] = fmaf(a.x, b.x, acc[0][0]); acc[0][1] = fmaf(a.x, b.y, acc[0][1]);
-            acc[0][2] = fmaf(a.x, b.z, acc[0][2]); acc[0][3] = fmaf(a.x, b.w, acc[0][3]);
-            acc[1][0] = fmaf(a.y, b.x, acc[1][0]); acc[1][1] = fmaf(a.y, b.y, acc[1][1]);
-            acc[1][2] = fmaf(a.y, b.z, acc[1][2]); acc[1][3] = fmaf(a.y, b.w, acc[1][3]);
-            acc[2][0] = fmaf(a.z, b.x, acc[2][0]); acc[2][1] = fmaf(a.z, b.y, acc[2][1]);
-            acc[2][2] = fmaf(a.z, b.z, acc[2][2]); acc[2][3] = fmaf(a.z, b.w, acc[2][3]);
-            acc[3][0] = fmaf(a.w, b.x, acc[3][0]); acc[3][1] = fmaf(a.w, b.y, acc[3][1]);
-            acc[3][2] = fmaf(a.w, b.z, acc[3][2]); acc[3][3] = fmaf(a.w, b.w, acc[3][3]);
+            const float4 b0 = *reinterpret_cast<const float4*>(ip0 + m * ldin);
+            const float4 b1 = *reinterpret_cast<const float4*>(ip1 + m * ldin);
+            const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                acc[i][0] = fmaf(av[i], b0.x, acc[i][0]); acc[i][1] = fmaf(av[i], b0.y, acc[i][1]);
+                acc[i][2] = fmaf(av[i], b0.z, acc[i][2]); acc[i][3] = fmaf(av[i], b0.w, acc[i][3]);
+                acc[i][4] = fmaf(av[i], b1.x, acc[i][4]); acc[i][5] = fmaf(av[i], b1.y, acc[i][5]);
+                acc[i][6] = fmaf(av[i], b1.z, acc[i][6]); acc[i][7] = fmaf(av[i], b1.w, acc[i][7]);
+            }
         }
+        if (nq < NQ) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int n = 4 * nq + i;
-            if (n < N) {
-                float* dst = gW + (size_t)n * K + 4 * kq;
-                if (vecG) {
-                    float4 o = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
-                    if (accumulate) {
-                        const float4 p = *reinterpret_cast<const float4*>(dst);
-                        o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+            for (int h = 0; h < 2; ++h) {
+                const int kq = h ? kq1 : kq0;
+                if (kq >= KQ) continue;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int n = 4 * nq + i;
+                    if (n < N) {
+                        float* dst = gW + (size_t)n * K + 4 * kq;
+                        if (vecG) {
+                            float4 o = make_float4(acc[i][4 * h], acc[i][4 * h + 1], acc[i][4 * h + 2], acc[i][4 * h + 3]);
+                            if (accumulate) {
+                                const float4 p = *reinterpret_cast<const float4*>(dst);
+                                o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+                            }
+                            *reinterpret_cast<float4*>(dst) = o;
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                if (4 * kq + j < K) dst[j] = accumulate ? dst[j] + acc[i][4 * h + j] : acc[i][4 * h + j];
+                        }
                     }
-                    *reinterpret_cast<float4*>(dst) = o;
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        if (4 * kq + j < K) dst[j] = accumulate ? dst[j] + acc[i][j] : acc[i][j];
                 }
             }
         }
     }
     for (int n = threadIdx.x; n < N; n += UPD_THREADS) {
         float s = 0.f;
-        for (int m = 0; m < TM; ++m) s += dOut[m * ldd + n];
+        for (int m = 0; m < 32; ++m) s += dOut[m * ldd + n];
+        gb[n] = accumulate ? gb[n] + s : s;
+    }
+    __syncthreads();
+}
+
+// dW for a narrow input (K <= 24, first layers): lanes are 16 (n-quads) x 2 (k-groups), a thread owns
+// one n-quad and the k-quads g*KH .. g*KH+KH-1 (KH = ceil(KQ/2) <= 3), so nothing is padded to 64 columns.
+__device__ __noinline__ void dw_layer_smallk(float* __restrict__ gW, float* __restrict__ gb, int N, int K,
+                                             const float* dOut, int ldd, const float* in, int ldin, bool accumulate,
+                                             float* img) {
+    constexpr int NWARPS = UPD_THREADS / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nql = lane >> 1, g = lane & 1;
+    const int NQ = (N + 3) >> 2, KQ = (K + 3) >> 2;
+    const int KH = (KQ + 1) >> 1;
+    for (int nq0 = warp * 16; nq0 < NQ; nq0 += NWARPS * 16) {
+        const int nq = nq0 + nql;
+        const float* dp = dOut + 4 * min(nq, NQ - 1);
+        float acc[4][12];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 12; ++j) acc[i][j] = 0.f;
+#pragma unroll 2
+        for (int m = 0; m < 32; ++m) {
+            const float4 a = *reinterpret_cast<const float4*>(dp + m * ldd);
+            const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+            for (int h = 0; h < 3; ++h) {
+                if (h < KH) {
+                    const int kq = min(g * KH + h, KQ - 1);
+                    const float4 b = *reinterpret_cast<const float4*>(in + m * ldin + 4 * kq);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        acc[i][4 * h + 0] = fmaf(av[i], b.x, acc[i][4 * h + 0]);
+                        acc[i][4 * h + 1] = fmaf(av[i], b.y, acc[i][4 * h + 1]);
+                        acc[i][4 * h + 2] = fmaf(av[i], b.z, acc[i][4 * h + 2]);
+                        acc[i][4 * h + 3] = fmaf(av[i], b.w, acc[i][4 * h + 3]);
+                    }
+                }
+            }
+        }
+        // the tile goes to a flat [N][K] image in shared memory first: the tensor is contiguous in
+        // the bucket, so the flush below is fully coalesced (rows of 17 floats are not, one by one)
+        if (nq < NQ) {
+#pragma unroll
+            for (int h = 0; h < 3; ++h) {
+                const int kq = g * KH + h;
+                if (h < KH && kq < KQ) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int n = 4 * nq + i;
+                        if (n < N) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const int k = 4 * kq + j;
+                                if (k < K) img[n * K + k] = acc[i][4 * h + j];
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int tot = N * K;
+    if ((tot & 3) == 0) {
+        float4* g4 = reinterpret_cast<float4*>(gW);
+        const float4* s4 = reinterpret_cast<const float4*>(img);
+        for (int e = threadIdx.x; e < (tot >> 2); e += UPD_THREADS) {
+            float4 o = s4[e];
+            if (accumulate) { const float4 p = g4[e]; o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
+            g4[e] = o;
+        }
+    } else {
+        for (int e = threadIdx.x; e < tot; e += UPD_THREADS) gW[e] = accumulate ? gW[e] + img[e] : img[e];
+    }
+    for (int n = threadIdx.x; n < N; n += UPD_THREADS) {
+        float s = 0.f;
+        for (int m = 0; m < 32; ++m) s += dOut[m * ldd + n];
         gb[n] = accumulate ? gb[n] + s : s;
     }
     __syncthreads();
@@ -362,15 +659,22 @@ __device__ void dw_layer(float* __restrict__ gW, float* __restrict__ gb, int N, 
 // ---------------------------------------------------------------------------
 // whole forward of one network on the tile (model.py:35-45)
 // ---------------------------------------------------------------------------
-__device__ void net_forward(const Net& nw, const UpdArgs& P, float* S, float* mu_out, float* v_out) {
+__device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, const UpdArgs& P, float* S, float* mu_out,
+                                            float* v_out, int tick, unsigned ph) {
     const dppo_dims& d = P.d;
     float* stage = S + P.o_stage;
-    fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, P.TM, stage);
-    fwd_layer<true>(nw.W2, nw.b2, d.H2, d.H1, S + P.o_h1, P.ldH1, S + P.o_h2, P.ldH2, P.TM, stage);
-    head_fwd(nw.Wmu, nw.bmu, d.A, d.H2, S + P.o_h2, P.ldH2, mu_out, P.ldA, P.TM);
-    fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, P.TM, stage);
-    fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, P.TM, stage);
-    head_fwd(nw.Wv, nw.bv, 1, d.G2, S + P.o_g2, P.ldG2, v_out, 1, P.TM);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
+    ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph);
+    K2_TICK(tick + 0);
+    ph = fwd_layer<true>(nw.W2, nw.b2, d.H2, d.H1, S + P.o_h1, P.ldH1, S + P.o_h2, P.ldH2, stage, P.SF, bars, ph);
+    K2_TICK(tick + 1);
+    ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph);
+    K2_TICK(tick + 2);
+    ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph);
+    K2_TICK(tick + 3);
+    heads_fwd(hs, d.A, d.H2, d.G2, S + P.o_h2, P.ldH2, S + P.o_g2, P.ldG2, mu_out, P.ldA, v_out);
+    K2_TICK(tick + 4);
+    return ph;
 }
 
 // deterministic block sum (fixed tree), result broadcast
@@ -395,6 +699,21 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
     float* part = P.partials + (size_t)blockIdx.x * P.lay.P_pad;
     const GradOut go = grad_of(part, P.lay);
     float* red = S + P.o_red;
+    // the two stage-buffer mbarriers are initialised ONCE; `ph` carries their phase parities
+    if (threadIdx.x == 0) {
+        uint64_t* b = reinterpret_cast<uint64_t*>(S + P.o_bars);
+        mbar_init(&b[0], 1);
+        mbar_init(&b[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    unsigned ph = 0;
+    // head weights of both networks stay in shared memory for the whole kernel
+    for (int i = threadIdx.x; i < 2 * P.head_floats; i += UPD_THREADS) S[P.o_heads + i] = 0.f;
+    __syncthreads();
+    load_heads(S + P.o_heads, nw, P);
+    if (P.flavour == DPPO_FLAVOUR_DPPO) load_heads(S + P.o_heads + P.head_floats, net_of(P.theta_old, P.lay), P);
+    K2_TICK(0);
+    const HeadS hs_new = heads_at(S + P.o_heads, P), hs_old = heads_at(S + P.o_heads + P.head_floats, P);
     if (threadIdx.x < DPPO_N_PARAMS)                                   // padding floats of the bucket stay 0
         for (int j = P.lay.size[threadIdx.x]; j < ((P.lay.size[threadIdx.x] + 3) & ~3); ++j)
             part[P.lay.off[threadIdx.x] + j] = 0.f;
@@ -402,10 +721,11 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
     bool first = true;
 
     for (int tile = blockIdx.x; tile < P.ntiles; tile += gridDim.x, first = false) {
+        K2_TICK(1);
         const int b0 = tile * TM;
         const int valid = min(TM, P.B - b0);
         // ---- zero the activation area (pads must read as 0), then gather --------------------
-        for (int i = threadIdx.x; i < P.o_stage; i += UPD_THREADS) S[i] = 0.f;
+        for (int i = threadIdx.x; i < P.o_zero_end; i += UPD_THREADS) S[i] = 0.f;
         __syncthreads();
         for (int e = threadIdx.x; e < valid * d.O; e += UPD_THREADS) {
             const int m = e / d.O, k = e - m * d.O;
@@ -423,12 +743,13 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         }
         __syncthreads();
 
+        K2_TICK(2);
         // ---- forward(s) -----------------------------------------------------------------------
         if (P.flavour == DPPO_FLAVOUR_DPPO) {
             const Net no = net_of(P.theta_old, P.lay);
-            net_forward(no, P, S, S + P.o_muo, S + P.o_vo);              // train.py:142
+            ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph);              // train.py:142
         }
-        net_forward(nw, P, S, S + P.o_mu, S + P.o_v);                    // train.py:145 / ppo.py:148
+        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph);                    // train.py:145 / ppo.py:148
 
         // ---- losses and their derivatives w.r.t. mu, v, log_std ---------------------------------
         const float lo = 1.f - P.clip, hi = 1.f + P.clip;               // clamp bounds (train.py:151)
@@ -436,7 +757,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
             const float g0 = -1.f / ((float)P.B * (float)d.A);          // d loss_clip / d min(.,.)
             const float ge = -P.ent_coeff / ((float)P.B * (float)d.A);
             const Net no = net_of(P.theta_old, P.lay);
-            for (int e = threadIdx.x; e < TM * d.A; e += UPD_THREADS) {
+            for (int e = threadIdx.x; e < UPD_ROWS * d.A; e += UPD_THREADS) {
                 const int m = e / d.A, a = e - m * d.A;
                 float dmu = 0.f, dls = 0.f;
                 if (m < valid) {
@@ -486,7 +807,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
                 S[P.o_muo + m * P.ldA + a] = dls;                        // mu_old no longer needed: reuse for dls
             }
             const float gv = 0.5f / (float)P.B;                          // train.py:157
-            for (int m = threadIdx.x; m < TM; m += UPD_THREADS) {
+            for (int m = threadIdx.x; m < UPD_ROWS; m += UPD_THREADS) {
                 float dv = 0.f;
                 if (m < valid) {
                     const float v = S[P.o_v + m], vo = S[P.o_vo + m], R = S[P.o_ret + m];
@@ -510,7 +831,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
             const float g0 = -1.f / (float)P.B;                          // ppo.py:161
             const float gv = 1.f / (float)P.B;                           // ppo.py:164
             const float half_log_2pi = 0.918938533204672742f;            // 0.5*math.log(2*math.pi)
-            for (int m = threadIdx.x; m < TM; m += UPD_THREADS) {
+            for (int m = threadIdx.x; m < UPD_ROWS; m += UPD_THREADS) {
                 float dv = 0.f, dlogp = 0.f;
                 if (m < valid) {
                     float logp = 0.f;
@@ -551,31 +872,47 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
             }
         }
         __syncthreads();
+        K2_TICK(13);
         // d log_std[a] = sum over the tile's samples (ascending m)
         for (int a = threadIdx.x; a < d.A; a += UPD_THREADS) {
             float s = 0.f;
-            for (int m = 0; m < TM; ++m) s += S[P.o_muo + m * P.ldA + a];
+            for (int m = 0; m < UPD_ROWS; ++m) s += S[P.o_muo + m * P.ldA + a];
             if (P.flavour == DPPO_FLAVOUR_PPO && blockIdx.x == 0 && first) s -= P.ent_coeff;   // ppo.py:152-153,167
             go.ls[a] = first ? s : go.ls[a] + s;
         }
         __syncthreads();
 
+        K2_TICK(14);
         // ---- backward, policy trunk -------------------------------------------------------------
         const bool acc = !first;
         float* stage = S + P.o_stage;
-        dw_layer(go.Wmu, go.bmu, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2, TM, acc);
-        head_dx(nw.Wmu, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2, TM);          // h2 <- dz2
-        dw_layer(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, TM, acc);
-        dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, TM, stage);  // h1 <- dz1
-        dw_layer(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, TM, acc);
+        uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
+        dw_layer(go.Wmu, go.bmu, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2, acc);
+        K2_TICK(15);
+        head_dx(hs_new.Wmu, P.ldH2, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2);          // h2 <- dz2
+        K2_TICK(16);
+        dw_layer(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc);
+        K2_TICK(17);
+        ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph);  // h1 <- dz1
+        K2_TICK(18);
+        if (d.O <= 24 && d.H1 >= 256 && d.H1 * d.O <= P.SF) dw_layer_smallk(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage);
+        else dw_layer(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc);
+        K2_TICK(19);
         // ---- backward, value trunk --------------------------------------------------------------
-        dw_layer(go.Wv, go.bv, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2, TM, acc);
-        head_dx(nw.Wv, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2, TM);
-        dw_layer(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, TM, acc);
-        dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, TM, stage);
-        dw_layer(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, TM, acc);
+        dw_layer(go.Wv, go.bv, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2, acc);
+        K2_TICK(20);
+        head_dx(hs_new.Wv, P.ldG2, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);
+        K2_TICK(21);
+        dw_layer(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc);
+        K2_TICK(22);
+        ph = dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph);
+        K2_TICK(23);
+        if (d.O <= 24 && d.G1 >= 256 && d.G1 * d.O <= P.SF) dw_layer_smallk(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage);
+        else dw_layer(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc);
+        K2_TICK(24);
     }
 
+    K2_TICK(25);
     // ---- per-CTA loss sums (scaled so that K3 only has to add them) -----------------------------
     const float sc = block_sum(lsum_clip, red);
     const float sv = block_sum(lsum_val, red);
@@ -636,7 +973,7 @@ int plan(UpdArgs& P) {
     const dppo_dims& d = P.d;
     P.ldO = ld_of(d.O); P.ldH1 = ld_of(d.H1); P.ldH2 = ld_of(d.H2); P.ldG1 = ld_of(d.G1); P.ldG2 = ld_of(d.G2);
     P.ldA = ld_of(d.A);
-    const int TM = P.TM;
+    const int TM = UPD_ROWS;                    // tiles always hold 32 rows; P.TM of them are samples
     int o = 0;
     auto take = [&](int n) { int r = o; o += (n + 3) & ~3; return r; };
     P.o_x = take(TM * P.ldO);
@@ -654,9 +991,17 @@ int plan(UpdArgs& P) {
     P.o_adv = take(TM);
     P.o_ret = take(TM);
     P.o_lpo = take(TM);
-    P.o_stage = o;                              // everything before the stage is zeroed per tile
-    o += UPD_STAGE;
+    P.o_zero_end = o;                           // everything before this is zeroed per tile
     P.o_red = take(UPD_THREADS);
+    P.o_bars = take(4);                         // two mbarriers (8 bytes each, 16-byte aligned)
+    P.head_floats = (d.A * P.ldH2 + ((d.A + 3) & ~3) + P.ldG2 + 4 + 3) & ~3;
+    P.o_heads = take(2 * P.head_floats);
+    P.o_stage = o;                              // everything before the stage is zeroed per tile
+    // two weight staging buffers from what is left of the 227 KB
+    int sf = ((227 * 1024 / 4 - o) / 2) & ~127;
+    if (sf > UPD_STAGE_MAX) sf = UPD_STAGE_MAX;
+    P.SF = sf;
+    o += 2 * (sf > 0 ? sf : 0);
     P.smem_floats = o;
     return o;
 }
@@ -728,7 +1073,7 @@ extern "C" int dppo_update_fused(int flavour, const dppo_dims* d, const float* o
     P.partials = partials; P.loss_partials = loss_partials;
     plan(P);
     const size_t smem = sizeof(float) * (size_t)P.smem_floats;
-    if (smem > 227 * 1024) return DPPO_E_TOOLARGE;
+    if (smem > 227 * 1024 || P.SF < UPD_STAGE_MIN) return DPPO_E_TOOLARGE;
     static size_t smem_set = 0;
     if (smem > smem_set) {
         DPPO_CUDA_TRY(cudaFuncSetAttribute(update_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -738,3 +1083,9 @@ extern "C" int dppo_update_fused(int flavour, const dppo_dims* d, const float* o
     DPPO_LAUNCH_CHECK();
     return 0;
 }
+
+#ifdef DPPO_K2_TIMING
+extern "C" int dppo_debug_k2_clocks(long long* out64_host) {
+    return (int)cudaMemcpyFromSymbol(out64_host, g_k2_clock, sizeof(long long) * 64);
+}
+#endif
