@@ -51,6 +51,87 @@ __device__ __forceinline__ void reduce_losses(const float* __restrict__ loss_par
     }
 }
 
+// ---- many partials (one per K2 CTA): 8 warps of a block each sum every 8th partial for the
+// same 32 float4 columns, then the eight group sums are added in fixed order.  8x more loads in
+// flight and 8x more blocks than one thread per column walking all partials.
+constexpr int RG = 8;                      // partial groups (= warps per block)
+constexpr int RQ = 32;                     // float4 columns per block
+
+__device__ __forceinline__ float4 sum_partials_grouped(const float4* __restrict__ partials, int nparts, int n4, int i,
+                                                       const float4* __restrict__ gshared, float4 (*red)[RQ]) {
+    const int q = threadIdx.x & 31, g = threadIdx.x >> 5;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < n4) {
+#pragma unroll 6
+        for (int p = g; p < nparts; p += RG) {
+            const float4 x = __ldcs(&partials[(size_t)p * n4 + i]);
+            a.x = __fadd_rn(a.x, x.x); a.y = __fadd_rn(a.y, x.y); a.z = __fadd_rn(a.z, x.z); a.w = __fadd_rn(a.w, x.w);
+        }
+    }
+    red[g][q] = a;
+    __syncthreads();
+    float4 G = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (g == 0 && i < n4) {
+        G = gshared ? gshared[i] : G;
+#pragma unroll
+        for (int r = 0; r < RG; ++r) {
+            const float4 x = red[r][q];
+            G.x = __fadd_rn(G.x, x.x); G.y = __fadd_rn(G.y, x.y); G.z = __fadd_rn(G.z, x.z); G.w = __fadd_rn(G.w, x.w);
+        }
+    }
+    return G;
+}
+
+__global__ void __launch_bounds__(RG * 32)
+reduce_adam_grouped_kernel(const float4* __restrict__ partials, int nparts, float4* __restrict__ gshared,
+                           float4* __restrict__ theta, float4* __restrict__ theta_prev, float4* __restrict__ m,
+                           float4* __restrict__ v, int n4, AdamScalars s, const AdamScalars* __restrict__ sdev,
+                           float4* __restrict__ grad_out, const float* __restrict__ loss_partials,
+                           float* __restrict__ loss_out) {
+    __shared__ float4 red[RG][RQ];
+    if (sdev) s = *sdev;
+    reduce_losses(loss_partials, nparts, loss_out);
+    const int i = blockIdx.x * RQ + (threadIdx.x & 31);
+    const float4 G = sum_partials_grouped(partials, nparts, n4, i, gshared, red);
+    if ((threadIdx.x >> 5) != 0 || i >= n4) return;
+    float4 p = theta[i], mm = m[i], vv = v[i];
+    if (theta_prev) theta_prev[i] = p;
+    adam_one(G.x, p.x, mm.x, vv.x, s);
+    adam_one(G.y, p.y, mm.y, vv.y, s);
+    adam_one(G.z, p.z, mm.z, vv.z, s);
+    adam_one(G.w, p.w, mm.w, vv.w, s);
+    theta[i] = p; m[i] = mm; v[i] = vv;
+    if (grad_out) grad_out[i] = G;
+    if (gshared) gshared[i] = make_float4(0.f, 0.f, 0.f, 0.f);          // chief.py:19
+}
+
+// clipping, pass 1 (grouped): G -> gtmp, per-block sum of squares (fp64, fixed order)
+__global__ void __launch_bounds__(RG * 32)
+reduce_sumsq_grouped_kernel(const float4* __restrict__ partials, int nparts, float4* __restrict__ gshared, int n4,
+                            float4* __restrict__ gtmp, double* __restrict__ blocksums,
+                            const float* __restrict__ loss_partials, float* __restrict__ loss_out) {
+    __shared__ float4 red[RG][RQ];
+    __shared__ double sq[RQ];
+    reduce_losses(loss_partials, nparts, loss_out);
+    const int i = blockIdx.x * RQ + (threadIdx.x & 31);
+    const float4 G = sum_partials_grouped(partials, nparts, n4, i, gshared, red);
+    if ((threadIdx.x >> 5) == 0) {
+        double ss = 0.0;
+        if (i < n4) {
+            gtmp[i] = G;
+            if (gshared) gshared[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            ss = (double)G.x * G.x + (double)G.y * G.y + (double)G.z * G.z + (double)G.w * G.w;
+        }
+        sq[threadIdx.x] = ss;
+        __syncwarp();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int k = 0; k < RQ; ++k) t += sq[k];
+            blocksums[blockIdx.x] = t;
+        }
+    }
+}
+
 // no clipping: everything in one kernel
 __global__ void __launch_bounds__(ADAM_THREADS)
 reduce_adam_kernel(const float4* __restrict__ partials, int nparts, float4* __restrict__ gshared,
@@ -137,7 +218,7 @@ clip_adam_kernel(const float4* __restrict__ gtmp, const double* __restrict__ blo
 // scratch: float gtmp[P_pad]; double blocksums[nblocks]; float norm
 extern "C" size_t dppo_reduce_adam_scratch_bytes(int P_pad) {
     if (P_pad <= 0) return 16;
-    const int nblocks = ceil_div(P_pad / 4, ADAM_THREADS);
+    const int nblocks = ceil_div(P_pad / 4, RQ);                 // the grouped grid is the larger one
     return align_up(sizeof(float) * (size_t)P_pad, 16) + sizeof(double) * (size_t)nblocks + 16;
 }
 
@@ -176,19 +257,33 @@ extern "C" int dppo_reduce_adam(const float* partials, int nparts, float* gshare
     const int n4 = P_pad / 4;
     const int nblocks = ceil_div(n4, ADAM_THREADS);
     const AdamScalars s = dppo_adam_scalars(step < 1 ? 1 : step, lr, beta1, beta2, eps);
+    const bool grouped = nparts > 2;                          // many K2 partials: spread them over 8 warps
+    const int gblocks = ceil_div(n4, RQ);
     if (max_grad_norm > 0.0) {
         if (!scratch || scratch_bytes < dppo_reduce_adam_scratch_bytes(P_pad)) return DPPO_E_SCRATCH;
         if (!aligned16(scratch)) return DPPO_E_ALIGN;
         float4* gtmp = (float4*)scratch;
         double* blocksums = (double*)((char*)scratch + align_up(sizeof(float) * (size_t)P_pad, 16));
-        float* norm = (float*)(blocksums + nblocks);
-        reduce_sumsq_kernel<<<nblocks, ADAM_THREADS, 0, stream>>>((const float4*)partials, nparts, (float4*)gshared, n4,
-                                                                   gtmp, blocksums, loss_partials, loss_out);
+        const int nsums = grouped ? gblocks : nblocks;
+        float* norm = (float*)(blocksums + gblocks);
+        if (grouped)
+            reduce_sumsq_grouped_kernel<<<gblocks, RG * 32, 0, stream>>>((const float4*)partials, nparts,
+                                                                         (float4*)gshared, n4, gtmp, blocksums,
+                                                                         loss_partials, loss_out);
+        else
+            reduce_sumsq_kernel<<<nblocks, ADAM_THREADS, 0, stream>>>((const float4*)partials, nparts, (float4*)gshared,
+                                                                       n4, gtmp, blocksums, loss_partials, loss_out);
         DPPO_LAUNCH_CHECK();
-        clip_adam_kernel<<<nblocks, ADAM_THREADS, 0, stream>>>(gtmp, blocksums, nblocks, (float)max_grad_norm,
+        clip_adam_kernel<<<nblocks, ADAM_THREADS, 0, stream>>>(gtmp, blocksums, nsums, (float)max_grad_norm,
                                                                 (float4*)theta, (float4*)theta_prev, (float4*)m,
                                                                 (float4*)v, n4, s, (const AdamScalars*)scalars_dev,
                                                                 (float4*)grad_out, norm);
+        DPPO_LAUNCH_CHECK();
+    } else if (grouped) {
+        reduce_adam_grouped_kernel<<<gblocks, RG * 32, 0, stream>>>((const float4*)partials, nparts, (float4*)gshared,
+                                                                    (float4*)theta, (float4*)theta_prev, (float4*)m,
+                                                                    (float4*)v, n4, s, (const AdamScalars*)scalars_dev,
+                                                                    (float4*)grad_out, loss_partials, loss_out);
         DPPO_LAUNCH_CHECK();
     } else {
         reduce_adam_kernel<<<nblocks, ADAM_THREADS, 0, stream>>>((const float4*)partials, nparts, (float4*)gshared,

@@ -202,10 +202,13 @@ def test_reduce_adam_vs_oracle(nv, nparts, clipnorm):
         torch.cuda.synchronize()
         assert torch.equal(prev.cpu(), before)
         assert float(gsh.abs().max()) == 0.0                           # chief.py:19
-        assert_close_scaled(gout.cpu(), G, 1e-6, "G step %d" % step)
-        assert_close_scaled(th_d.cpu(), theta, 1e-6, "theta step %d" % step)
-        assert_close_scaled(m_d.cpu(), m, 1e-6, "m")
-        assert_close_scaled(v_d.cpu(), v, 1e-6, "v")
+        # the partials are summed in a fixed but different order than the oracle's loop (8 interleaved
+        # groups, then the groups): an fp32 re-association, bounded by the suite's 1e-5
+        tol = 1e-6 if nparts <= 2 else 1e-5
+        assert_close_scaled(gout.cpu(), G, tol, "G step %d" % step)
+        assert_close_scaled(th_d.cpu(), theta, tol, "theta step %d" % step)
+        assert_close_scaled(m_d.cpu(), m, tol, "m")
+        assert_close_scaled(v_d.cpu(), v, tol, "v")
         # keep the two trajectories from drifting apart through the (non-IEEE) torch sqrt
         theta.copy_(th_d.cpu()); m.copy_(m_d.cpu()); v.copy_(v_d.cpu())
 
