@@ -149,6 +149,39 @@ int dppo_reduce_adam(const float* partials, int nparts, float* gshared,
                      const float* loss_partials, float* loss_out,
                      void* scratch, size_t scratch_bytes, void* stream);
 
+/* ---- K3 across GPUs: gradient SUM over workers + Adam in one kernel over NVLink -------
+ * Replaces, for W workers on W GPUs of one node, the shared-memory gradient bucket that
+ * every worker adds into (model.py:53-55), the Counter/TrafficLight barrier (utils.py:4-39,
+ * train.py:171-175, chief.py:9-13) and the chief's Adam step + reset (chief.py:15-20).
+ * One process per GPU.  Every rank calls dppo_allreduce_adam once per epoch with its own K2
+ * partials; the kernel pushes the rank's summed slice into every peer's receive buffer
+ * (peer-mapped memory), waits for all ranks' slices and applies
+ *     G = gshared + sum_{r=0..W-1} g_r   (rank order),  Adam(G),  gshared = 0
+ * so all replicas stay bit-identical.  Arguments as dppo_reduce_adam (no norm clipping).
+ * Life cycle: dppo_comm_create allocates the peer-visible buffer (the only allocation the
+ * library makes), dppo_comm_local_handle exports it (dppo_comm_handle_bytes() bytes, to be
+ * all-gathered by the host, e.g. torch.distributed), dppo_comm_open_peers maps the others.
+ * The *_loopback pair runs W virtual ranks on ONE GPU in a cooperative launch (tests).
+ * dppo_reduce_partials only sums the K2 partials (used by the NCCL baseline path). */
+typedef struct dppo_comm dppo_comm;
+int dppo_comm_create(int rank, int world, int P_pad, dppo_comm** out);
+int dppo_comm_handle_bytes(void);
+int dppo_comm_local_handle(dppo_comm* c, void* handle_host);
+int dppo_comm_open_peers(dppo_comm* c, const void* handles_host);
+int dppo_comm_create_loopback(int world, int P_pad, dppo_comm** out_array);
+int dppo_comm_destroy(dppo_comm* c);
+int dppo_allreduce_adam(dppo_comm* c, const float* partials, int nparts, float* gshared,
+                        float* theta, float* theta_prev, float* m, float* v, int P_pad,
+                        int step, double lr, double beta1, double beta2, double eps,
+                        const float* scalars_dev, float* grad_out,
+                        const float* loss_partials, float* loss_out, void* stream);
+int dppo_allreduce_adam_loopback(dppo_comm** comms, int world, const float* const* partials, const int* nparts,
+                                 float* const* gshared, float* const* theta, float* const* theta_prev,
+                                 float* const* m, float* const* v, int P_pad,
+                                 int step, double lr, double beta1, double beta2, double eps,
+                                 float* const* grad_out, void* stream);
+int dppo_reduce_partials(const float* partials, int nparts, float* out, int P_pad, void* stream);
+
 /* ---- a4: minibatch positions (HOST function, no GPU work) ------------------
  * Replaces ``random.sample(self.memory, batch_size)`` (train.py:31-33 /
  * ppo.py:58-60): `rounds` consecutive samples of k distinct positions out of

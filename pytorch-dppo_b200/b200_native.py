@@ -64,6 +64,17 @@ def _load():
         "dppo_update_partials_bytes": (sz, [dp, i32]),
         "dppo_update_fused": (i32, [i32, dp, vp, vp, vp, vp, vp, vp, i32, vp, vp, flt, flt, vp, vp, vp]),
         "dppo_reduce_adam_scratch_bytes": (sz, [i32]),
+        "dppo_comm_create": (i32, [i32, i32, i32, c.POINTER(vp)]),
+        "dppo_comm_handle_bytes": (i32, []),
+        "dppo_comm_local_handle": (i32, [vp, vp]),
+        "dppo_comm_open_peers": (i32, [vp, vp]),
+        "dppo_comm_create_loopback": (i32, [i32, i32, c.POINTER(vp)]),
+        "dppo_comm_destroy": (i32, [vp]),
+        "dppo_allreduce_adam": (i32, [vp, vp, i32, vp, vp, vp, vp, vp, i32, i32, dbl, dbl, dbl, dbl, vp, vp, vp, vp, vp]),
+        "dppo_allreduce_adam_loopback": (i32, [c.POINTER(vp), i32, c.POINTER(vp), c.POINTER(i32), c.POINTER(vp),
+                                               c.POINTER(vp), c.POINTER(vp), c.POINTER(vp), c.POINTER(vp), i32, i32,
+                                               dbl, dbl, dbl, dbl, c.POINTER(vp), vp]),
+        "dppo_reduce_partials": (i32, [vp, i32, vp, i32, vp]),
         "dppo_sample_indices_host": (i32, [c.POINTER(c.c_uint32), c.POINTER(i32), i64, i32, i32, c.POINTER(c.c_int32)]),
         "dppo_fp32_probe": (i32, [i32, vp, c.POINTER(dbl), vp]),
         "dppo_adam_scalars_host": (i32, [i32, dbl, dbl, dbl, dbl, c.POINTER(flt)]),
@@ -217,3 +228,62 @@ def fp32_probe(iters=4096):
         e1.synchronize()
         best = max(best, flops.value / (e0.elapsed_time(e1) * 1e-3) / 1e12)
     return best
+
+
+# ---- multi-GPU exchange (csrc/dppo_comm.cu) -----------------------------------------------------
+def comm_create(rank, world, P_pad):
+    h = ctypes.c_void_p()
+    check(lib.dppo_comm_create(rank, world, P_pad, ctypes.byref(h)))
+    return h
+
+
+def comm_local_handle(comm):
+    buf = ctypes.create_string_buffer(lib.dppo_comm_handle_bytes())
+    check(lib.dppo_comm_local_handle(comm, buf))
+    return bytes(buf.raw)
+
+
+def comm_open_peers(comm, handles):
+    blob = b"".join(handles)
+    check(lib.dppo_comm_open_peers(comm, ctypes.c_char_p(blob)))
+
+
+def comm_destroy(comm):
+    lib.dppo_comm_destroy(comm)
+
+
+def allreduce_adam(comm, partials, nparts, gshared, theta, theta_prev, m, v, step, lr, beta1=0.9, beta2=0.999,
+                   eps=1e-8, grad_out=None, loss_partials=None, loss_out=None, scalars_dev=None):
+    check(lib.dppo_allreduce_adam(comm, _ptr(partials, allow_none=True), nparts, _ptr(gshared, allow_none=True),
+                                  _ptr(theta), _ptr(theta_prev, allow_none=True), _ptr(m), _ptr(v), theta.numel(), step,
+                                  lr, beta1, beta2, eps, _ptr(scalars_dev, allow_none=True),
+                                  _ptr(grad_out, allow_none=True), _ptr(loss_partials, allow_none=True),
+                                  _ptr(loss_out, allow_none=True), _stream()))
+
+
+def comm_create_loopback(world, P_pad):
+    arr = (ctypes.c_void_p * world)()
+    check(lib.dppo_comm_create_loopback(world, P_pad, arr))
+    return [ctypes.c_void_p(arr[r]) for r in range(world)]
+
+
+def allreduce_adam_loopback(comms, partials, gshared, theta, theta_prev, m, v, step, lr, grad_out=None,
+                            beta1=0.9, beta2=0.999, eps=1e-8):
+    """W virtual ranks on one GPU (test helper): every argument is a list indexed by rank."""
+    W = len(comms)
+    vp = ctypes.c_void_p
+
+    def arr(ts):
+        if ts is None:
+            return None
+        return (vp * W)(*[_ptr(t, allow_none=True) for t in ts])
+
+    cc = (vp * W)(*[c.value for c in comms])
+    np_ = (ctypes.c_int * W)(*[p.shape[0] for p in partials])
+    check(lib.dppo_allreduce_adam_loopback(cc, W, arr(partials), np_, arr(gshared), arr(theta), arr(theta_prev), arr(m),
+                                           arr(v), theta[0].numel(), step, lr, beta1, beta2, eps, arr(grad_out),
+                                           _stream()))
+
+
+def reduce_partials(partials, nparts, out):
+    check(lib.dppo_reduce_partials(_ptr(partials), nparts, _ptr(out), out.numel(), _stream()))

@@ -72,11 +72,16 @@ __device__ __forceinline__ float4 sum_partials_grouped(const float4* __restrict_
     __syncthreads();
     float4 G = make_float4(0.f, 0.f, 0.f, 0.f);
     if (g == 0 && i < n4) {
-        G = gshared ? gshared[i] : G;
+        // this GPU's gradient first, the shared bucket's content on top of it: the same association as
+        // the multi-GPU kernel with one rank (dppo_comm.cu), so W = 1 is bit-identical to this path
 #pragma unroll
         for (int r = 0; r < RG; ++r) {
             const float4 x = red[r][q];
             G.x = __fadd_rn(G.x, x.x); G.y = __fadd_rn(G.y, x.y); G.z = __fadd_rn(G.z, x.z); G.w = __fadd_rn(G.w, x.w);
+        }
+        if (gshared) {
+            const float4 s0 = gshared[i];
+            G.x = __fadd_rn(s0.x, G.x); G.y = __fadd_rn(s0.y, G.y); G.z = __fadd_rn(s0.z, G.z); G.w = __fadd_rn(s0.w, G.w);
         }
     }
     return G;
