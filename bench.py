@@ -205,7 +205,7 @@ def main():
     engine = UpdateEngine(model, nv.FLAVOUR_DPPO, wl["B"], wl["E"], wl["lr"], comm=comm)
     host, devbuf = make_rollout(model, stats, wl["T"], seed=1 + rank, flavour=nv.FLAVOUR_DPPO)
     rng = random.Random(1 + rank)
-    use_graph = not args.no_graph
+    use_graph = not args.no_graph and not (comm is not None and comm.mode == "nccl")   # NCCL baseline: plain launches
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     stats0 = [t.clone() for t in (stats.n, stats.mean, stats.mean_diff, stats.var)]
 
@@ -361,6 +361,9 @@ def kernel_times(nv, engine, stats, buf, sgb, wl, flush):
                         engine.theta, old, engine.clip, engine.ent_coeff, engine.partials, engine.loss_partials)
 
     def k3():
+        if engine.comm is not None:                        # every rank runs this the same number of times
+            engine.comm.allreduce_adam(engine, 0, None)
+            return
         nv.reduce_adam(engine.partials, engine.nparts, None, engine.theta, old, engine.m, engine.v, 0, engine.lr,
                        grad_out=engine.grad, loss_partials=engine.loss_partials, loss_out=engine.loss_out[0],
                        scalars_dev=engine.scalars_dev[0])

@@ -140,7 +140,7 @@ class UpdateEngine:
         if not indices_staged:
             self.idx_dev.copy_(self.idx_host, non_blocking=True)
         self._stage_scalars()
-        if not use_graph:
+        if not use_graph or (self.comm is not None and self.comm.mode == "nccl"):
             self.launches_per_cycle = self._launch_epochs(buf, gshared)
         else:
             key = (id(buf), None if gshared is None else gshared.data_ptr())

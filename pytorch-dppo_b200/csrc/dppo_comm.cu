@@ -9,20 +9,21 @@
 //
 //   each CTA owns 32 float4 columns of the bucket:
 //     1. sum this GPU's K2 partials for those columns (8 warps, as in dppo_adam.cu)
-//     2. PUSH the 512-byte slice into slot [parity][rank] of EVERY GPU's receive buffer
-//        (peer stores over NVLink), fence.sys, then stamp the epoch number into every GPU's
-//        flag word for (rank, column block)
-//     3. wait until the flag words of all ranks for this column block carry this epoch, add
-//        the W slices in RANK ORDER on top of the shared bucket's content (ones before the
-//        first update, model.py:51) - identical values in identical order on every GPU, so
-//        the replicas stay bit-identical - and run Adam on the columns.
-//   The flag exchange is the barrier that Counter + TrafficLight + sleep(1) implement in the
-//   reference.  Receive slots are double-buffered by epoch parity; a slot is rewritten two
-//   epochs later, after its reader has signalled the epoch in between.
+//     2. PUSH the slice into slot [parity][rank] of EVERY GPU's receive buffer with peer stores
+//        over NVLink.  Every 8-byte word carries 4 bytes of payload and the 4-byte epoch number
+//        (the "LL" idea of NCCL's low-latency protocol): 8-byte stores are single-copy atomic, so
+//        a reader that sees the epoch in a word also sees its payload - no fence, no separate flag.
+//     3. poll the W slots of this column block until every word carries this epoch, add the W
+//        slices in RANK ORDER on top of the shared bucket's content (ones before the first update,
+//        model.py:51) - identical values in identical order on every GPU, so the replicas stay
+//        bit-identical - and run Adam on the columns.
+//   Waiting for the words is the barrier that Counter + TrafficLight + sleep(1) implement in the
+//   reference.  Receive slots are double-buffered by epoch parity; a slot is rewritten two epochs
+//   later, after its reader has pushed the epoch in between (which it does after reading).
 //
-// CTAs are persistent and walk the column blocks in index order on every GPU, so a CTA only
-// ever waits for the SAME column block of its peers, which never waits on anything else: no
-// deadlock regardless of how many CTAs are resident.
+// CTAs walk the column blocks in index order on every GPU and push ALL their blocks before they
+// poll any, so a poll only ever waits for pushes that depend on nothing: no deadlock regardless
+// of how many CTAs are resident.
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
@@ -38,8 +39,7 @@ struct AdamScalars { float w1, b2, a2, bc2_sqrt, eps, alpha; };
 
 struct CommDev {                            // everything a kernel needs, by value
     int rank, world, n4, gblocks;
-    float4* recv[CM_MAX_WORLD];             // recv[r]: base of rank r's receive buffer [2][world][n4] (peer-mapped)
-    unsigned* flags[CM_MAX_WORLD];          // flags[r]: rank r's flag words [world][gblocks]
+    uint4* recv[CM_MAX_WORLD];              // recv[r]: rank r's receive buffer [2][world][n4][2] LL words (peer-mapped)
     unsigned* epoch;                        // this rank: completed epochs
     unsigned* done;                         // this rank: CTAs finished in the current launch
 };
@@ -56,12 +56,15 @@ struct dppo_comm {
 
 namespace {
 
-__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+__device__ __forceinline__ void st_ll(uint4* p, float d0, float d1, unsigned flag) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(__float_as_uint(d0)), "r"(flag),
+                 "r"(__float_as_uint(d1)), "r"(flag)
+                 : "memory");
 }
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
-    unsigned v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ uint4 ld_ll(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p)
+                 : "memory");
     return v;
 }
 
@@ -105,9 +108,9 @@ __global__ void __launch_bounds__(CM_THREADS) allreduce_adam_kernel(const Launch
         for (int p = 0; p < A.nparts; ++p) t = __fadd_rn(t, A.loss_partials[p * 4 + threadIdx.x]);
         A.loss_out[threadIdx.x] = t;
     }
+    // ---- phase 1: sum my partials per column block and push the slices to every rank ------------
     for (int jb = blockIdx.x; jb < C.gblocks; jb += gridDim.x) {
         const int i = jb * CM_RQ + lane;
-        // 1. this rank's partials, 8 interleaved groups then the groups in order
         float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
         if (i < n4) {
 #pragma unroll 6
@@ -119,34 +122,37 @@ __global__ void __launch_bounds__(CM_THREADS) allreduce_adam_kernel(const Launch
         __syncthreads();                                  // red[] of the previous column block consumed
         red[g][lane] = a;
         __syncthreads();
-        if (g != 0) continue;                             // warp 0 does the exchange and Adam
-        float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
+        // warps 0..world-1: warp w pushes to rank w (all warps hold the same sum)
+        if (g < C.world && i < n4) {
+            float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int r = 0; r < CM_THREADS / 32; ++r) {
-            const float4 x = red[r][lane];
-            mine.x = __fadd_rn(mine.x, x.x); mine.y = __fadd_rn(mine.y, x.y);
-            mine.z = __fadd_rn(mine.z, x.z); mine.w = __fadd_rn(mine.w, x.w);
+            for (int r = 0; r < CM_THREADS / 32; ++r) {
+                const float4 x = red[r][lane];
+                mine.x = __fadd_rn(mine.x, x.x); mine.y = __fadd_rn(mine.y, x.y);
+                mine.z = __fadd_rn(mine.z, x.z); mine.w = __fadd_rn(mine.w, x.w);
+            }
+            uint4* dst = C.recv[g] + (((size_t)par * C.world + C.rank) * n4 + i) * 2;
+            st_ll(dst, mine.x, mine.y, epoch);
+            st_ll(dst + 1, mine.z, mine.w, epoch);
         }
-        // 2. push my slice into everybody's slot [par][rank], then publish the epoch
-        if (i < n4) {
-            for (int r = 0; r < C.world; ++r)
-                C.recv[r][((size_t)par * C.world + C.rank) * n4 + i] = mine;
-        }
-        __threadfence_system();
-        __syncwarp();
-        if (lane < C.world) st_release_sys(C.flags[lane] + (size_t)C.rank * C.gblocks + jb, epoch);
-        // 3. wait for every rank's slice of this column block, then sum in rank order
-        if (lane < C.world) {
-            const unsigned* f = C.flags[C.rank] + (size_t)lane * C.gblocks + jb;
-            while ((int)(ld_acquire_sys(f) - epoch) < 0) { }
-        }
-        __syncwarp();
-        if (i < n4) {
-        float4 G = A.gshared ? A.gshared[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-        const float4* slot = C.recv[C.rank] + (size_t)par * C.world * n4 + i;
+    }
+    // ---- phase 2: poll every rank's slice, sum in rank order, Adam -----------------------------------
+    for (int jb = blockIdx.x; jb < C.gblocks; jb += gridDim.x) {
+        const int i = jb * CM_RQ + lane;
+        if (g != 0 || i >= n4) continue;                  // no block-wide barrier below this line
+        float4 G = make_float4(0.f, 0.f, 0.f, 0.f);
+        const uint4* slot = C.recv[C.rank] + ((size_t)par * C.world * n4 + i) * 2;
         for (int r = 0; r < C.world; ++r) {
-            const float4 x = __ldcg(slot + (size_t)r * n4);       // L2: peers wrote it, L1 may be stale
-            G.x = __fadd_rn(G.x, x.x); G.y = __fadd_rn(G.y, x.y); G.z = __fadd_rn(G.z, x.z); G.w = __fadd_rn(G.w, x.w);
+            const uint4* q = slot + (size_t)r * n4 * 2;
+            uint4 lo, hi;
+            do { lo = ld_ll(q); } while (lo.y != epoch || lo.w != epoch);
+            do { hi = ld_ll(q + 1); } while (hi.y != epoch || hi.w != epoch);
+            G.x = __fadd_rn(G.x, __uint_as_float(lo.x)); G.y = __fadd_rn(G.y, __uint_as_float(lo.z));
+            G.z = __fadd_rn(G.z, __uint_as_float(hi.x)); G.w = __fadd_rn(G.w, __uint_as_float(hi.z));
+        }
+        if (A.gshared) {                                  // shared bucket content on top (as dppo_adam.cu)
+            const float4 s0 = A.gshared[i];
+            G.x = __fadd_rn(s0.x, G.x); G.y = __fadd_rn(s0.y, G.y); G.z = __fadd_rn(s0.z, G.z); G.w = __fadd_rn(s0.w, G.w);
         }
         float4 p = A.theta[i], mm = A.m[i], vv = A.v[i];
         if (A.theta_prev) A.theta_prev[i] = p;
@@ -157,7 +163,6 @@ __global__ void __launch_bounds__(CM_THREADS) allreduce_adam_kernel(const Launch
         A.theta[i] = p; A.m[i] = mm; A.v[i] = vv;
         if (A.grad_out) A.grad_out[i] = G;
         if (A.gshared) A.gshared[i] = make_float4(0.f, 0.f, 0.f, 0.f);      // chief.py:19
-        }
     }
     // the last CTA of this rank to finish closes the epoch (every CTA read it at its start)
     __syncthreads();
@@ -186,23 +191,22 @@ AdamScalars make_scalars(int step, double lr, double beta1, double beta2, double
 }
 
 size_t layout(dppo_comm* c) {
-    c->recv_bytes = align_up(sizeof(float4) * 2 * (size_t)c->world * c->n4, 256);
-    c->flag_bytes = align_up(sizeof(unsigned) * (size_t)c->world * c->gblocks, 256);
+    c->recv_bytes = align_up(sizeof(uint4) * 2 * 2 * (size_t)c->world * c->n4, 256);    // LL: 2x the payload
+    c->flag_bytes = 0;
     return c->recv_bytes + c->flag_bytes + 256;
 }
 
 void fill_dev(dppo_comm* c) {
     c->dev.rank = c->rank; c->dev.world = c->world; c->dev.n4 = c->n4; c->dev.gblocks = c->gblocks;
     for (int r = 0; r < c->world; ++r) {
-        c->dev.recv[r] = (float4*)c->peer_base[r];
-        c->dev.flags[r] = (unsigned*)((char*)c->peer_base[r] + c->recv_bytes);
+        c->dev.recv[r] = (uint4*)c->peer_base[r];
     }
     c->dev.epoch = (unsigned*)((char*)c->base + c->recv_bytes + c->flag_bytes);
     c->dev.done = c->dev.epoch + 1;
 }
 
 int grid_for(const dppo_comm* c) {
-    const int cap = dppo_sm_count() * 2;
+    const int cap = dppo_sm_count() * 4;
     return c->gblocks < cap ? c->gblocks : cap;
 }
 
