@@ -260,7 +260,8 @@ def main():
     h2d = d2h = 0
     for _ in range(2):
         reset_stats()
-        engine.update_from_host(host, devbuf, obs_stats=stats, rng=rng, use_graph=use_graph, gshared=sgb.flat)
+        engine.update_from_host(host, devbuf, obs_stats=stats, rng=rng, use_graph=use_graph, gshared=sgb.flat,
+                                prefetch_next=True)
     barrier()
     n_e2e = max(3, min(args.steps, 100))
     for _ in range(n_e2e):
@@ -270,7 +271,7 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         _, h2d, d2h = engine.update_from_host(host, devbuf, obs_stats=stats, rng=rng, use_graph=use_graph,
-                                              gshared=sgb.flat)
+                                              gshared=sgb.flat, prefetch_next=True)
         e1.record()
         e2e_evs.append((e0, e1))
     barrier()

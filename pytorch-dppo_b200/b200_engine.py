@@ -80,6 +80,8 @@ class UpdateEngine:
         model.flat_grad = self.grad
         self.idx_dev = torch.zeros(self.E, self.B, dtype=torch.int32, device=dev)
         self.idx_host = torch.zeros(self.E, self.B, dtype=torch.int32, pin_memory=True)
+        self._idx_next = torch.zeros(self.E, self.B, dtype=torch.int32, pin_memory=True)
+        self._prefetched = None                  # (T, id(rng)) of the positions already drawn into _idx_next
         self.scalars_dev = torch.zeros(self.E, 8, device=dev)
         self.scalars_host = torch.zeros(self.E, 8, pin_memory=True)
         self.loss_host = torch.zeros(self.E, 4, pin_memory=True)
@@ -167,21 +169,32 @@ class UpdateEngine:
         return self.loss_out
 
     # ---- whole outer iteration from a host rollout (the end-to-end call) ----------------------
-    def update_from_host(self, host, dev, obs_stats=None, rng=random, use_graph=True, gshared=None):
+    def update_from_host(self, host, dev, obs_stats=None, rng=random, use_graph=True, gshared=None,
+                         prefetch_next=False):
         """H2D copy of one rollout (pinned ``host`` buffer -> ``dev``), K4 (if obs_stats),
         K1, E x (K2,K3), D2H copy of the per-epoch losses.  Returns (loss_host, h2d_bytes,
-        d2h_bytes)."""
+        d2h_bytes).  With ``prefetch_next`` the minibatch positions of the NEXT call are drawn
+        from ``rng`` while the GPU works on this one (same ``random.sample`` stream, drawn
+        earlier); the next call must then use the same ``rng`` and rollout length."""
         fields = ["act", "rew", "val", "boot", "seg_end"] + (["raw_obs"] if obs_stats is not None else ["obs"])
         if self.flavour == nv.FLAVOUR_PPO:
             fields.append("logp")
         h2d = dev.copy_from(host, fields)
-        self.draw_indices(dev.T, rng)
-        self.idx_dev.copy_(self.idx_host, non_blocking=True)
-        h2d += self.idx_host.numel() * 4 + self.scalars_host.numel() * 4
         if obs_stats is not None:
             obs_stats.observes_batch(dev.raw_obs, out=dev.obs)
         self.gae(dev)
+        # the host draws the minibatch positions while the GPU is busy with the copies, K4 and K1
+        if self._prefetched == (dev.T, id(rng)):
+            self.idx_host, self._idx_next = self._idx_next, self.idx_host
+        else:
+            self.draw_indices(dev.T, rng)
+        self._prefetched = None
+        self.idx_dev.copy_(self.idx_host, non_blocking=True)
+        h2d += self.idx_host.numel() * 4 + self.scalars_host.numel() * 4
         self.run_epochs(dev, gshared=gshared, use_graph=use_graph, indices_staged=True)
         self.loss_host.copy_(self.loss_out, non_blocking=True)
+        if prefetch_next:
+            nv.sample_indices(dev.T, self.B, self.E, rng=rng, out=self._idx_next)
+            self._prefetched = (dev.T, id(rng))
         torch.cuda.current_stream().synchronize()
         return self.loss_host, h2d, self.loss_host.numel() * 4

@@ -87,32 +87,56 @@ extern "C" int dppo_sample_indices_host(uint32_t* mt_state624_host, int* mt_inde
         }
         free(pool);
     } else {
-        // set branch: rejection of already selected positions (open-addressing hash set)
-        size_t cap = 16;
-        while (cap < (size_t)k * 2 + 2) cap <<= 1;
-        int32_t* tab = (int32_t*)malloc(sizeof(int32_t) * cap);
-        if (!tab) return DPPO_E_BADARG;
+        // set branch: rejection of already selected positions.  Membership is a bitmap of n bits
+        // while that stays cache-sized (8 KB for a 65536-step rollout), else an open-addressing set.
         const int bits = bit_length(un);
-        for (int r = 0; r < rounds; ++r) {
-            memset(tab, 0xff, sizeof(int32_t) * cap);
-            int32_t* out = out_host + (size_t)r * k;
-            for (int i = 0; i < k; ++i) {
-                for (;;) {
-                    const uint32_t j = mt.below(un, bits);
-                    size_t h = ((size_t)j * 2654435761u) & (cap - 1);
-                    bool seen = false;
-                    while (tab[h] != -1) {
-                        if ((uint32_t)tab[h] == j) { seen = true; break; }
-                        h = (h + 1) & (cap - 1);
+        if (n <= (int64_t)1 << 24) {
+            const size_t words = ((size_t)n + 63) / 64;
+            uint64_t* bm = (uint64_t*)malloc(sizeof(uint64_t) * words);
+            if (!bm) return DPPO_E_BADARG;
+            for (int r = 0; r < rounds; ++r) {
+                memset(bm, 0, sizeof(uint64_t) * words);
+                int32_t* out = out_host + (size_t)r * k;
+                for (int i = 0; i < k; ++i) {
+                    uint32_t j;
+                    for (;;) {
+                        j = mt.below(un, bits);
+                        uint64_t& w = bm[j >> 6];
+                        const uint64_t bit = (uint64_t)1 << (j & 63);
+                        if (w & bit) continue;
+                        w |= bit;
+                        break;
                     }
-                    if (seen) continue;
-                    tab[h] = (int32_t)j;
                     out[i] = (int32_t)j;
-                    break;
                 }
             }
+            free(bm);
+        } else {
+            size_t cap = 16;
+            while (cap < (size_t)k * 2 + 2) cap <<= 1;
+            int32_t* tab = (int32_t*)malloc(sizeof(int32_t) * cap);
+            if (!tab) return DPPO_E_BADARG;
+            for (int r = 0; r < rounds; ++r) {
+                memset(tab, 0xff, sizeof(int32_t) * cap);
+                int32_t* out = out_host + (size_t)r * k;
+                for (int i = 0; i < k; ++i) {
+                    for (;;) {
+                        const uint32_t j = mt.below(un, bits);
+                        size_t h = ((size_t)j * 2654435761u) & (cap - 1);
+                        bool seen = false;
+                        while (tab[h] != -1) {
+                            if ((uint32_t)tab[h] == j) { seen = true; break; }
+                            h = (h + 1) & (cap - 1);
+                        }
+                        if (seen) continue;
+                        tab[h] = (int32_t)j;
+                        out[i] = (int32_t)j;
+                        break;
+                    }
+                }
+            }
+            free(tab);
         }
-        free(tab);
     }
     *mt_index_host = mt.idx;
     return 0;

@@ -216,3 +216,24 @@ def test_engine_vs_oracle_c2_shape_ten_epochs():
         assert float(loss[k, 1]) == pytest.approx(terms[k]["loss_value"], rel=1e-4)
     assert_close_scaled(unpadded(m.flat, m.offsets, m.sizes), orc.flatten(p), 1e-5, "theta after 10 epochs")
     assert eng.step == E
+
+
+def test_prefetched_indices_are_the_same_stream():
+    """update_from_host(prefetch_next=True) draws the next call's positions early; the stream of
+    random.sample results must be exactly the one Python would have produced."""
+    import b200_native as nv
+    from b200_engine import UpdateEngine
+    from model import Model, Shared_obs_stats
+    from synthetic import make_rollout
+    torch.manual_seed(1)
+    m = Model(4, 2, device=DEV)
+    stats = Shared_obs_stats(4)
+    T, B, E = 512, 64, 3
+    host, dev = make_rollout(m, stats, T, seed=1, flavour=nv.FLAVOUR_DPPO, seg_len=200)
+    eng = UpdateEngine(m, nv.FLAVOUR_DPPO, B, E, 3e-4)
+    rng = random.Random(9)
+    ref = random.Random(9)
+    for call in range(3):
+        eng.update_from_host(host, dev, obs_stats=None, rng=rng, prefetch_next=True)
+        want = [ref.sample(range(T), B) for _ in range(E)]
+        assert eng.idx_host.tolist() == want, call
