@@ -75,7 +75,7 @@ int dppo_gae_scan(const float* rewards, const float* values, const float* boot, 
 /* dppo_gae_scan for callers that cannot allocate scratch (no counterpart in the
  * reference; added for host programs that own no device allocator or must not call
  * cudaMalloc while running).  Same inputs, outputs and results as dppo_gae_scan; the
- * look-back chain lives in a ~24 KB array inside the library image, resident on every
+ * look-back chain lives in a ~12 KB array inside the library image, resident on every
  * GPU that loads the library.  T <= DPPO_GAE_NOALLOC_MAX_T, otherwise
  * DPPO_E_NOALLOC_LIMIT.  The first call on a device resolves the array's device address:
  * make it before any stream capture.  Allocates and frees nothing.  All calls on a

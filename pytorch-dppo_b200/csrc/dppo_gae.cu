@@ -18,11 +18,12 @@
 // normally ends after one hop.  With its carry known, each thread REPLAYS its
 // 8 steps with the reference's exact fp32 operation order (no FMA), so the
 // only rounding difference to the sequential loop sits in the carries.
+#include <math.h>
 #include "common.cuh"
 
 namespace {
 
-constexpr int GAE_THREADS = 256;
+constexpr int GAE_THREADS = 512;
 constexpr int GAE_K = 8;                          // steps per thread
 constexpr int GAE_TILE = GAE_THREADS * GAE_K;     // 2048 steps per CTA
 
@@ -38,20 +39,35 @@ __device__ __forceinline__ Aff compose(Aff f, Aff g) {
 // scratch layout: int ticket; int status[ntiles]; float2 ab[ntiles]
 // status: 0 = nothing, 1 = ab is the tile-local composition, 2 = ab.b is the
 // resolved A at the tile's first step (ab.a = 0)
-template <bool VEC>
+// HALO > 0: the tile's window is GAE_TILE steps of which the last HALO are a read-only look-ahead:
+// |gamma*lam|^HALO is below 2^-40, so the advantage entering the window from the right cannot change
+// any fp32 result in the first GAE_TILE-HALO steps and the tiles become independent (no ticket, no
+// look-back, no inter-CTA traffic).  HALO == 0: chained tiles with decoupled look-back (exact for
+// any gamma*lam, used when the decay is too slow for a halo).
+template <bool VEC, bool HALO>
 __global__ void __launch_bounds__(GAE_THREADS)
 gae_scan_kernel(const float* __restrict__ rew, const float* __restrict__ val, const float* __restrict__ boot,
                 const uint8_t* __restrict__ seg_end, float* __restrict__ adv, float* __restrict__ ret,
-                int64_t T, float g, float gl, int ntiles, int* __restrict__ ticket, int* __restrict__ status,
+                int64_t T, float g, float gl, int ntiles, int halo, int* __restrict__ ticket, int* __restrict__ status,
                 float2* __restrict__ ab) {
     __shared__ int s_tile;
     __shared__ Aff s_warp[GAE_THREADS / 32];
     __shared__ float s_carry;
 
-    if (threadIdx.x == 0) s_tile = ntiles - 1 - atomicAdd(ticket, 1);   // right-most tile first
-    __syncthreads();
-    const int tile = s_tile;
-    const int64_t base = (int64_t)tile * GAE_TILE + (int64_t)threadIdx.x * GAE_K;
+    int tile;
+    int64_t tile_base, out_end;
+    if (HALO) {
+        tile = blockIdx.x;
+        tile_base = (int64_t)tile * (GAE_TILE - halo);
+        out_end = tile_base + (GAE_TILE - halo);          // steps >= out_end belong to the next tile
+    } else {
+        if (threadIdx.x == 0) s_tile = ntiles - 1 - atomicAdd(ticket, 1);   // right-most tile first
+        __syncthreads();
+        tile = s_tile;
+        tile_base = (int64_t)tile * GAE_TILE;
+        out_end = tile_base + GAE_TILE;
+    }
+    const int64_t base = tile_base + (int64_t)threadIdx.x * GAE_K;
 
     float r[GAE_K], v[GAE_K + 1], bt[GAE_K];
     uint8_t se[GAE_K];
@@ -119,7 +135,9 @@ gae_scan_kernel(const float* __restrict__ rew, const float* __restrict__ val, co
         if (w > warp) right = compose(right, s_warp[w]);
 
     // tile aggregate and look-back (thread 0)
-    if (threadIdx.x == 0) {
+    if (HALO) {
+        if (threadIdx.x == 0) s_carry = 0.f;              // what enters from beyond the halo has decayed away
+    } else if (threadIdx.x == 0) {
         Aff agg = compose(loc, right);
         float carry = 0.f;
         if (tile == ntiles - 1) {
@@ -160,6 +178,7 @@ gae_scan_kernel(const float* __restrict__ rew, const float* __restrict__ val, co
         oa[k] = A;
         orr[k] = __fadd_rn(A, v[k]);
     }
+    if (HALO && base >= out_end) return;                  // look-ahead steps are not written (out_end % 8 == 0)
     if (VEC && base + GAE_K <= T) {
         float4* a4 = reinterpret_cast<float4*>(adv + base);
         float4* q4 = reinterpret_cast<float4*>(ret + base);
@@ -176,6 +195,16 @@ gae_scan_kernel(const float* __restrict__ rew, const float* __restrict__ val, co
 
 }  // namespace
 
+// look-ahead length for the independent-tile mode, 0 if the decay is too slow
+static int gae_halo(float gl) {
+    const double a = fabs((double)gl);
+    if (a == 0.0) return 8;
+    if (a >= 1.0) return 0;
+    const double h = ceil(40.0 * log(2.0) / -log(a));
+    if (h > GAE_TILE / 2) return 0;
+    return ((int)h + 7) & ~7;
+}
+
 extern "C" size_t dppo_gae_scratch_bytes(int64_t T) {
     if (T <= 0) return 16;
     const int64_t ntiles = ceil_div64(T, GAE_TILE);
@@ -188,27 +217,40 @@ extern "C" int dppo_gae_scan(const float* rewards, const float* values, const fl
     if (T < 0) return DPPO_E_BADARG;
     if (T == 0) return 0;
     if (!rewards || !values || !boot || !seg_end || !adv || !ret || !scratch) return DPPO_E_BADARG;
-    if (ceil_div64(T, GAE_TILE) > 0x7fffffff) return DPPO_E_TOOLARGE;
+    if (ceil_div64(T, GAE_TILE / 2) > 0x7fffffff) return DPPO_E_TOOLARGE;
     if (scratch_bytes < dppo_gae_scratch_bytes(T)) return DPPO_E_SCRATCH;
     if (!aligned16(scratch)) return DPPO_E_ALIGN;
     cudaStream_t stream = (cudaStream_t)stream_;
+    // gamma multiplies a 0-dim fp32 tensor, gamma*lam is a Python double product
+    // that multiplies an fp32 tensor (train.py:118-119): both end up as fp32 scalars
+    const float g = (float)gamma, gl = (float)(gamma * lam);
+    const bool vec = aligned16(rewards) && aligned16(values) && aligned16(boot) && aligned16(adv) && aligned16(ret) &&
+                     ((reinterpret_cast<uintptr_t>(seg_end) & 7u) == 0);
+    const int halo = gae_halo(gl);
+    if (halo > 0) {
+        const int step = GAE_TILE - halo;
+        const int ntiles = (int)ceil_div64(T, step);
+        if (vec)
+            gae_scan_kernel<true, true><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T,
+                                                                             g, gl, ntiles, halo, nullptr, nullptr, nullptr);
+        else
+            gae_scan_kernel<false, true><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T,
+                                                                              g, gl, ntiles, halo, nullptr, nullptr, nullptr);
+        DPPO_LAUNCH_CHECK();
+        return 0;
+    }
     const int ntiles = (int)ceil_div64(T, GAE_TILE);
     const size_t flag_bytes = align_up(sizeof(int) * (size_t)(1 + ntiles), 16);
     int* ticket = (int*)scratch;
     int* status = ticket + 1;
     float2* ab = (float2*)((char*)scratch + flag_bytes);
     DPPO_CUDA_TRY(cudaMemsetAsync(scratch, 0, flag_bytes, stream));
-    // gamma multiplies a 0-dim fp32 tensor, gamma*lam is a Python double product
-    // that multiplies an fp32 tensor (train.py:118-119): both end up as fp32 scalars
-    const float g = (float)gamma, gl = (float)(gamma * lam);
-    const bool vec = aligned16(rewards) && aligned16(values) && aligned16(boot) && aligned16(adv) && aligned16(ret) &&
-                     ((reinterpret_cast<uintptr_t>(seg_end) & 7u) == 0);
     if (vec)
-        gae_scan_kernel<true><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T, g, gl,
-                                                                   ntiles, ticket, status, ab);
+        gae_scan_kernel<true, false><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T, g,
+                                                                          gl, ntiles, 0, ticket, status, ab);
     else
-        gae_scan_kernel<false><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T, g, gl,
-                                                                    ntiles, ticket, status, ab);
+        gae_scan_kernel<false, false><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T, g,
+                                                                           gl, ntiles, 0, ticket, status, ab);
     DPPO_LAUNCH_CHECK();
     return 0;
 }
@@ -223,7 +265,7 @@ extern "C" int dppo_gae_scan(const float* rewards, const float* values, const fl
 // because cudaMalloc synchronises the whole device and may fail late; code that
 // runs after the application has frozen its memory pool.  For them the chain
 // lives in the array below, which is part of the library image: every GPU that
-// loads libdppo_b200.so keeps these ~24 KB resident until the process exits.
+// loads libdppo_b200.so keeps these ~12 KB resident until the process exits.
 //
 // Limits and rules
 //   * T <= DPPO_GAE_NOALLOC_MAX_T (4 194 304 steps); longer buffers are refused

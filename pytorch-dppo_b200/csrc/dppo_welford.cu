@@ -13,16 +13,16 @@
 // sums are carried in fp64, mean_t / M2_t are rounded to fp32 and the
 // normalisation is the reference's fp32 arithmetic.
 //
-// Three launches over row tiles: (a) per-tile column sums, (b) exclusive scan
-// of the tile sums per column + new state, (c) per-row prefix + normalise.
-// HBM traffic: obs is read in (a) and (c) (the second read is an L2 hit while
-// the rollout is smaller than L2) and out is written once.
+// Three launches: (a) per-tile column sums, (b) exclusive scan of the tile sums per column + new
+// state, (c) per-row prefix + normalise.  obs is read in (a) and (c): the second read is an L2 hit
+// while the rollout is smaller than L2 (every named config), else HBM sees 12*O B/row.
 #include "common.cuh"
 
 namespace {
 
 constexpr int WF_THREADS = 256;
-constexpr int WF_TILE_ELEMS = 8192;                 // 32 KB of fp32 per CTA
+constexpr int WF_TILE_ELEMS = 8192;                 // 32 KB of fp32 per CTA (16 KB and 64 KB were slower)
+constexpr int64_t WF_CHUNK_BYTES = (int64_t)1 << 40;  // rows per launch group (chunking for L2 reuse did not pay: see DESIGN.md)
 
 struct WfGeom {
     int O, R, G, RPG;                               // rows per tile, row groups per tile, rows per group
@@ -32,14 +32,17 @@ struct WfGeom {
 
 __host__ __device__ inline int wf_rows_per_tile(int O) {
     int R = (WF_TILE_ELEMS / O) & ~3;               // multiple of 4 rows keeps tiles 16-byte aligned
+    if (R > 2048) R = 2048;                         // bounds the per-row reciprocal tables
     return R < 4 ? 4 : R;
 }
 
+// KEEP: the aggregate pass leaves the rows in L2 for the apply pass (which streams them out)
+template <bool KEEP>
 __device__ __forceinline__ void wf_load_tile(float* s, const float* __restrict__ g, int64_t off, int n, bool vec) {
     if (vec && (n & 3) == 0) {
         const float4* g4 = reinterpret_cast<const float4*>(g + off);
         float4* s4 = reinterpret_cast<float4*>(s);
-        for (int i = threadIdx.x; i < n / 4; i += WF_THREADS) s4[i] = __ldcs(&g4[i]);
+        for (int i = threadIdx.x; i < n / 4; i += WF_THREADS) s4[i] = KEEP ? __ldg(&g4[i]) : __ldcs(&g4[i]);
     } else {
         for (int i = threadIdx.x; i < n; i += WF_THREADS) s[i] = g[off + i];
     }
@@ -83,7 +86,7 @@ wf_aggregate_kernel(const float* __restrict__ obs, WfGeom q, const float* __rest
             if (c == 0) state0[2 * q.O] = n[0];
         }
     }
-    wf_load_tile(s, obs, row0 * q.O, rows * q.O, vec);
+    wf_load_tile<true>(s, obs, row0 * q.O, rows * q.O, vec);
     __syncthreads();
     wf_group_sums(s, s_p, q, rows, s_g1, s_g2);
     __syncthreads();
@@ -151,7 +154,7 @@ wf_apply_kernel(const float* __restrict__ obs, float* __restrict__ out, WfGeom q
     const int64_t row0 = (int64_t)tile * q.R;
     const int rows = (int)min((int64_t)q.R, q.T - row0);
     for (int c = threadIdx.x; c < q.O; c += WF_THREADS) s_p[c] = state0[c];
-    wf_load_tile(s, obs, row0 * q.O, rows * q.O, vec);
+    wf_load_tile<false>(s, obs, row0 * q.O, rows * q.O, vec);
     __syncthreads();
     wf_group_sums(s, s_p, q, rows, s_g1, s_g2);
     __syncthreads();
@@ -166,6 +169,17 @@ wf_apply_kernel(const float* __restrict__ obs, float* __restrict__ out, WfGeom q
     }
     __syncthreads();
     const double n0 = (double)state0[2 * q.O];
+    // per-row 1/n_t (fp64 and fp32), once per row instead of once per element: the int->fp64 and
+    // fp64->fp32 conversions run at 1/8 of the FP32 rate and were the bottleneck of this kernel
+    double* s_inv = s_g2 + q.G * q.O;
+    float* s_nf = reinterpret_cast<float*>(s_inv + q.R);
+    for (int r = threadIdx.x; r < rows; r += WF_THREADS) {
+        const double nt = n0 + (double)(row0 + r + 1);
+        const double r0 = (double)__frcp_rn((float)nt);       // fp32 reciprocal + one Newton step in fp64
+        s_inv[r] = r0 * (2.0 - nt * r0);
+        s_nf[r] = (float)s_inv[r];                             // 1/n_t in fp32
+    }
+    __syncthreads();
     for (int it = threadIdx.x; it < q.G * q.O; it += WF_THREADS) {
         const int g = it / q.O, c = it - g * q.O;
         const float p = s_p[c];
@@ -177,13 +191,13 @@ wf_apply_kernel(const float* __restrict__ obs, float* __restrict__ out, WfGeom q
             const double d = (double)__fsub_rn(x, p);
             a1 += d;
             a2 = fma(d, d, a2);
-            const double nt = n0 + (double)(row0 + r + 1);
-            const double inv = 1.0 / nt;
-            const double t = a1 * inv;
+            const double t = a1 * s_inv[r];
             const float mean_t = (float)((double)p + t);
             const float md_t = (float)(M0 + a2 - a1 * t);
-            const float var_t = fmaxf(__fdiv_rn(md_t, (float)nt), 1e-2f);                   // model.py:75
-            const float xh = __fdiv_rn(__fsub_rn(x, mean_t), __fsqrt_rn(var_t));            // model.py:77-80
+            // var = max(M2/n, 1e-2), xhat = (x-mean)/sqrt(var) (model.py:75-80) as multiply-by-reciprocal and
+            // rsqrt: within 2 ulp of the divide/sqrt form, an order of magnitude fewer instructions
+            const float var_t = fmaxf(md_t * s_nf[r], 1e-2f);
+            const float xh = __fsub_rn(x, mean_t) * rsqrtf(var_t);
             s[r * q.O + c] = fminf(fmaxf(xh, -5.f), 5.f);
         }
     }
@@ -212,7 +226,8 @@ WfGeom wf_geom(int64_t T, int O) {
 }
 
 size_t wf_smem_bytes(const WfGeom& q) {
-    return sizeof(float) * ((size_t)q.R * q.O + ((q.O + 3) & ~3)) + 2 * sizeof(double) * (size_t)q.G * q.O;
+    return sizeof(float) * ((size_t)q.R * q.O + ((q.O + 3) & ~3)) + 2 * sizeof(double) * (size_t)q.G * q.O +
+           (sizeof(double) + sizeof(float)) * (size_t)q.R + 16;            // + per-row 1/n (fp64) and n (fp32)
 }
 
 }  // namespace
@@ -229,25 +244,35 @@ extern "C" int dppo_welford(const float* obs, float* out, int64_t T, int O, floa
     if (T < 0 || O <= 0) return DPPO_E_BADARG;
     if (T == 0) return 0;
     if (!obs || !out || !n || !mean || !mean_diff || !var || !scratch) return DPPO_E_BADARG;
-    if (O > 2048) return DPPO_E_TOOLARGE;
+    if (O > 4096) return DPPO_E_TOOLARGE;
     if (ceil_div64(T, wf_rows_per_tile(O)) > 0x7fffffff) return DPPO_E_TOOLARGE;
     if (scratch_bytes < dppo_welford_scratch_bytes(T, O)) return DPPO_E_SCRATCH;
     if (!aligned16(scratch)) return DPPO_E_ALIGN;
     cudaStream_t stream = (cudaStream_t)stream_;
-    const WfGeom q = wf_geom(T, O);
     float* state0 = (float*)scratch;
     double* agg = (double*)((char*)scratch + align_up(sizeof(float) * (size_t)(2 * O + 1), 16));
-    const size_t smem = wf_smem_bytes(q);
     const bool vec = aligned16(obs) && aligned16(out);
-    if (smem > 48 * 1024) {
-        DPPO_CUDA_TRY(cudaFuncSetAttribute(wf_aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        DPPO_CUDA_TRY(cudaFuncSetAttribute(wf_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // Row chunks (WF_CHUNK_BYTES each; one chunk in practice).  The running state is carried from chunk
+    // to chunk exactly as between two calls.
+    const int R = wf_rows_per_tile(O);
+    int64_t chunk_rows = ((int64_t)WF_CHUNK_BYTES / ((int64_t)O * 4) / R) * R;
+    if (chunk_rows < R) chunk_rows = R;
+    for (int64_t t0 = 0; t0 < T; t0 += chunk_rows) {
+        const int64_t tc = (T - t0 < chunk_rows) ? T - t0 : chunk_rows;
+        const WfGeom q = wf_geom(tc, O);
+        const size_t smem = wf_smem_bytes(q);
+        if (smem > 48 * 1024 && t0 == 0) {
+            DPPO_CUDA_TRY(cudaFuncSetAttribute(wf_aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            DPPO_CUDA_TRY(cudaFuncSetAttribute(wf_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        }
+        const float* in = obs + t0 * O;
+        float* o = out + t0 * O;
+        wf_aggregate_kernel<<<q.ntiles, WF_THREADS, smem, stream>>>(in, q, n, mean, mean_diff, state0, agg, vec);
+        DPPO_LAUNCH_CHECK();
+        wf_scan_kernel<<<O, WF_THREADS, 0, stream>>>(q, agg, state0, n, mean, mean_diff, var);
+        DPPO_LAUNCH_CHECK();
+        wf_apply_kernel<<<q.ntiles, WF_THREADS, smem, stream>>>(in, o, q, state0, agg, vec);
+        DPPO_LAUNCH_CHECK();
     }
-    wf_aggregate_kernel<<<q.ntiles, WF_THREADS, smem, stream>>>(obs, q, n, mean, mean_diff, state0, agg, vec);
-    DPPO_LAUNCH_CHECK();
-    wf_scan_kernel<<<O, WF_THREADS, 0, stream>>>(q, agg, state0, n, mean, mean_diff, var);
-    DPPO_LAUNCH_CHECK();
-    wf_apply_kernel<<<q.ntiles, WF_THREADS, smem, stream>>>(obs, out, q, state0, agg, vec);
-    DPPO_LAUNCH_CHECK();
     return 0;
 }
