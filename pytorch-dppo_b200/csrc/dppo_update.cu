@@ -26,15 +26,21 @@
 #ifdef DPPO_K2_TIMING
 __device__ long long g_k2_clock[64];
 #define K2_TICK(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_k2_clock[i] = clock64(); } while (0)
+#define K2_ACC_DECL long long acc_t0 = 0
+#define K2_ACC_T0 acc_t0 = clock64()
+#define K2_ACC(i) do { if (blockIdx.x == 0 && (threadIdx.x == 0 || threadIdx.x == 32)) { long long t = clock64(); g_k2_clock[i] += t - acc_t0; acc_t0 = t; } } while (0)
 #else
 #define K2_TICK(i) do { } while (0)
+#define K2_ACC_DECL
+#define K2_ACC_T0
+#define K2_ACC(i) do { } while (0)
 #endif
 
 namespace {
 
 constexpr int UPD_THREADS = 256;
 constexpr int UPD_TM_MAX = 32;
-constexpr int UPD_STAGE_MAX = 10240;        // floats per weight staging buffer (40 KB), two buffers
+constexpr int UPD_STAGE_MAX = 11520;        // floats per staging buffer (45 KB: one tensor-core k-block), two buffers
 constexpr int UPD_STAGE_MIN = 4096;
 constexpr int UPD_ROWS = 32;                // sample rows per CTA tile (TM <= 32 of them are real)
 constexpr int UPD_MAX_A = 64;
@@ -296,10 +302,255 @@ __device__ __noinline__ unsigned fwd_layer_t(const float* __restrict__ W, const 
     return ph;
 }
 
+
+// ---------------------------------------------------------------------------
+// Tensor-core forward layer (tcgen05, sm_100a) for the wide GEMM-shaped layers:
+//   out[m][n] = tanh(sum_k in[m][k] W[n][k] + b[n]),  N <= 128, K % 4 == 0
+// computed transposed on the 5th-generation tensor cores as  D[n][m] = W[n][:] . in[m][:]
+// (M = 128 weight rows, N = 32 samples, K in blocks of 32) with 3xTF32: every fp32 operand is split
+// into hi = rn_tf32(x) and lo = rn_tf32(x - hi) and hi*hi + lo*hi + hi*lo is accumulated in fp32 in
+// tensor memory.  The tensor core truncates when it adds into an accumulator, so the k-blocks go round
+// robin into four 64-column TMEM accumulators ([hi*hi | hi*lo], one N = 64 MMA) and lo*hi into a fifth;
+// they are added in registers in the epilogue.  Measured (tools/tc_probe.cu): max error 6.8e-6 at K = 500 against
+// 2.3e-5 for the fp32 FMA loop.
+//
+// Operands are staged by all threads (global/L2 -> registers -> split -> shared memory) into the
+// canonical K-major no-swizzle UMMA layout: 16-byte chunk (row r, chunk kc) at
+// (r/8)*SBO + kc*LBO + (r%8)*16 with LBO = 144 B (padded so the chunk stores are bank-conflict
+// free).  Two stage buffers; one thread issues the MMAs and commits them to an mbarrier that frees
+// the stage.  The epilogue reads TMEM with tcgen05.ld (lane = output feature, columns = samples).
+// ---------------------------------------------------------------------------
+constexpr int TC_KB = 32;                                   // k-block: 32 floats = 8 chunks
+constexpr int TC_LBO = 144, TC_SBO = (TC_KB / 4) * TC_LBO;  // bytes
+constexpr int TC_A_BYTES = 16 * TC_SBO, TC_B_BYTES = 4 * TC_SBO;
+constexpr int TC_STAGE_FLOATS = (2 * TC_A_BYTES + 2 * TC_B_BYTES) / 4;      // 11520
+constexpr int TC_NACC = 4;                                  // 64-column accumulators [hi*hi | hi*lo] (+1 for lo*hi)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t tc_off(int r, int kc) { return (r >> 3) * TC_SBO + kc * TC_LBO + (r & 7) * 16; }
+__device__ __forceinline__ uint64_t tc_desc(uint32_t saddr) {
+    return (uint64_t)((saddr >> 4) & 0x3fff) | ((uint64_t)(TC_LBO >> 4) << 16) | ((uint64_t)(TC_SBO >> 4) << 32) |
+           ((uint64_t)1 << 46);                             // version 1, SWIZZLE_NONE, K-major
+}
+// round-to-nearest (ties away) split of an fp32 number into two tf32 numbers with integer ALU ops:
+// cvt.rna.tf32.f32 gives the same result but runs on the conversion pipe at 1/8 of the ALU rate, and
+// the split is the inner loop of the operand staging (checked against cvt.rna in tools/tc_probe.cu)
+__device__ __forceinline__ float tc_rn_tf32(float x) {
+    return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
+__device__ __forceinline__ void tc_split(float x, float& hi, float& lo) {
+    hi = tc_rn_tf32(x);
+    lo = tc_rn_tf32(x - hi);
+}
+__device__ __forceinline__ void tc_store_split(char* hi_tile, char* lo_tile, int r, int kc, float4 x) {
+    float4 h, l;
+    tc_split(x.x, h.x, l.x); tc_split(x.y, h.y, l.y); tc_split(x.z, h.z, l.z); tc_split(x.w, h.w, l.w);
+    const uint32_t o = tc_off(r, kc);
+    *reinterpret_cast<float4*>(hi_tile + o) = h;
+    *reinterpret_cast<float4*>(lo_tile + o) = l;
+}
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}"
+        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(0), "r"(0), "r"(0), "r"(0)
+        : "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+
+// Warp 0 only issues the MMAs (one elected thread, as tcgen05 wants); warps 1-7 are producers that
+// split and stage the operands.  No block-wide barrier inside the k loop: producers signal a filled
+// stage on full[s] (one arrival per warp), the issuer waits for it, issues 12 MMAs and commits them to
+// empty[s], which producers wait on before they overwrite the stage two k-blocks later.
+constexpr int TC_PRODUCERS = UPD_THREADS - 32;
+
+template <bool TANH>
+__device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const float* __restrict__ bias, int N, int K,
+                                              const float* in, int ldin, float* out, int ldout, float* stage, int SF,
+                                              uint64_t* bars, unsigned ph, uint32_t tmem) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nkb = (K + TC_KB - 1) / TC_KB;
+    uint64_t* empty = bars + 2;                             // MMAs of a stage done   (ph bits 2, 3)
+    uint64_t* full = bars + 4;                              // stage filled            (ph bits 4, 5)
+    // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 32, M = 128
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    __syncthreads();                                        // previous users of the stage buffers are done
+    if (warp == 0) {
+        // ---------------- MMA issuer ----------------
+        K2_ACC_DECL;
+        // descriptors of the four operand tiles of both stages, built once: inside the loop a k-step only
+        // adds a constant to the start-address field (one thread issues everything, so every instruction
+        // in this loop is on the critical path)
+        uint64_t dAh[2], dAl[2], dBh[2], dBl[2];
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            const uint32_t base = smem_u32(stage + (size_t)s * SF);
+            dAh[s] = tc_desc(base);
+            dAl[s] = tc_desc(base + TC_A_BYTES);
+            dBh[s] = tc_desc(base + 2 * TC_A_BYTES);
+            dBl[s] = tc_desc(base + 2 * TC_A_BYTES + TC_B_BYTES);
+        }
+        constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;       // start-address increment per 8 tf32
+        const uint32_t tcross = tmem + 64 * TC_NACC;
+        const uint32_t idesc64 = (idesc & ~(0x3fu << 17)) | ((uint32_t)(64 >> 3) << 17);
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb & 1;
+            K2_ACC_T0;
+            mbar_wait(&full[s], (ph >> (4 + s)) & 1u);
+            ph ^= 1u << (4 + s);
+            K2_ACC(40);
+            if (lane == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                // B_hi and B_lo tiles are adjacent, so ONE N = 64 MMA with A_hi produces hi*hi (columns
+                // 0-31) and hi*lo (columns 32-63): A_hi is read from shared memory once for both terms
+                const uint64_t ah = dAh[s], al = dAl[s], bb = dBh[s];
+                const uint32_t tmain = tmem + 64 * (kb % TC_NACC);
+                tc_mma(tmain, ah, bb, idesc64, kb >= TC_NACC ? 1u : 0u);
+                tc_mma(tcross, al, bb, idesc, kb ? 1u : 0u);
+#pragma unroll
+                for (int ks = 1; ks < TC_KB / 8; ++ks) {    // one MMA covers 8 tf32 = two chunks
+                    tc_mma(tmain, ah + ks * KSTEP, bb + ks * KSTEP, idesc64, 1u);
+                    tc_mma(tcross, al + ks * KSTEP, bb + ks * KSTEP, idesc, 1u);
+                }
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                 smem_u32(&empty[s]))
+                             : "memory");
+            }
+            __syncwarp();
+            K2_ACC(41);
+        }
+        // bring the issuer's view of the empty barriers up to date (phases the producers consumed in the
+        // loop), then wait for the last commit of each stage like everybody else: `ph` ends up uniform
+        for (int kb = 2; kb < nkb; ++kb) ph ^= 1u << (2 + (kb & 1));
+        for (int kb = (nkb > 2 ? nkb - 2 : 0); kb < nkb; ++kb) {
+            const int s = kb & 1;
+            mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
+            ph ^= 1u << (2 + s);
+        }
+    } else {
+        // ---------------- producers ----------------
+        const int pt = tid - 32;                            // 0..223
+        K2_ACC_DECL;
+        constexpr int NCH = (1024 + TC_PRODUCERS - 1) / TC_PRODUCERS;     // A chunks per producer (5)
+        // per-thread constants of the staging loop: source pointer and tile offset of each chunk
+        const float* gp[NCH];
+        uint32_t so[NCH];
+        int kc4[NCH];
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
+            const int e = pt + TC_PRODUCERS * i, r = e >> 3, kc = e & 7;
+            const bool ok = e < 1024 && r < N;
+            gp[i] = ok ? W + (size_t)r * K + 4 * kc : nullptr;
+            so[i] = tc_off(r & 127, kc);
+            kc4[i] = e < 1024 ? 4 * kc : K;                 // chunks beyond the tile are never stored
+        }
+        const int bm = pt >> 3, bkc = pt & 7;               // B: chunk pt (and pt + 224 for pt < 32)
+        // weight chunks are fetched TWO k-blocks ahead (two register sets): one block of lead did not
+        // cover the L2 latency
+        float4 preA[NCH], preB[NCH];
+        auto prefetch = [&](float4 (&pre)[NCH], int kb) {
+#pragma unroll
+            for (int i = 0; i < NCH; ++i)
+                pre[i] = (gp[i] != nullptr && kb * TC_KB + kc4[i] < K) ? __ldg(reinterpret_cast<const float4*>(gp[i] + kb * TC_KB))
+                                                                        : make_float4(0.f, 0.f, 0.f, 0.f);
+        };
+        prefetch(preA, 0);
+        if (nkb > 1) prefetch(preB, 1);
+#pragma unroll 2
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb & 1;
+            float4 (&pre)[NCH] = (kb & 1) ? preB : preA;
+            char* base = reinterpret_cast<char*>(stage + (size_t)s * SF);
+            char *Ah = base, *Al = base + TC_A_BYTES, *Bh = base + 2 * TC_A_BYTES, *Bl = Bh + TC_B_BYTES;
+            K2_ACC_T0;
+            if (kb >= 2) {                                  // the MMAs of k-block kb-2 have read this stage
+                mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
+                ph ^= 1u << (2 + s);
+            }
+            K2_ACC(42);
+#pragma unroll
+            for (int i = 0; i < NCH; ++i) {
+                if (i < NCH - 1 || pt + TC_PRODUCERS * i < 1024) {
+                    float4 h, l;
+                    tc_split(pre[i].x, h.x, l.x); tc_split(pre[i].y, h.y, l.y);
+                    tc_split(pre[i].z, h.z, l.z); tc_split(pre[i].w, h.w, l.w);
+                    *reinterpret_cast<float4*>(Ah + so[i]) = h;
+                    *reinterpret_cast<float4*>(Al + so[i]) = l;
+                }
+            }
+            {
+                const int k = kb * TC_KB + 4 * bkc;
+                const float4 x = (k < K) ? *reinterpret_cast<const float4*>(in + bm * ldin + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                tc_store_split(Bh, Bl, bm, bkc, x);
+                if (pt < 32) {                              // the remaining 32 of the 256 B chunks
+                    const int m2 = (pt + TC_PRODUCERS) >> 3;
+                    const float4 y = (k < K) ? *reinterpret_cast<const float4*>(in + m2 * ldin + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    tc_store_split(Bh, Bl, m2, bkc, y);
+                }
+            }
+            K2_ACC(43);
+            if (kb + 2 < nkb) prefetch(pre, kb + 2);        // lands while the next block is staged
+            K2_ACC(44);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> tensor-core reads
+            K2_ACC(45);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full[s]);           // one arrival per producer warp
+            K2_ACC(46);
+        }
+        // drain: wait for the last commits (they cover every MMA issued), keeps `ph` equal to the issuer's
+        for (int kb = (nkb > 2 ? nkb - 2 : 0); kb < nkb; ++kb) {
+            const int s = kb & 1;
+            mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
+            ph ^= 1u << (2 + s);
+        }
+        for (int kb = 0; kb < nkb; ++kb) ph ^= 1u << (4 + (kb & 1));       // phases the issuer consumed
+    }
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    // epilogue: warp w owns TMEM lanes 32*(w%4)..+31 (= output features), warps 0-3 samples 0-15, 4-7 samples 16-31
+    {
+        const int n = 32 * (warp & 3) + lane, c0 = (warp >> 2) * 16;
+        float sum[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) sum[j] = 0.f;
+        const int nacc = nkb < TC_NACC ? nkb : TC_NACC;
+        // small terms first: lo*hi, then the hi*lo halves, then the hi*hi halves of the accumulators
+        for (int t = 0; t < 1 + 2 * nacc; ++t) {
+            const uint32_t col = (t == 0) ? 64 * TC_NACC : (t <= nacc ? 64 * (t - 1) + 32 : 64 * (t - 1 - nacc));
+            uint32_t v[16];
+            const uint32_t taddr = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + col + c0;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                         : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < 16; ++j) sum[j] += __uint_as_float(v[j]);
+        }
+        if (n < N) {
+            const float bb = __ldg(bias + n);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                float y = sum[j] + bb;
+                if (TANH) y = tanhf(y);
+                out[(c0 + j) * ldout + n] = y;
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    return ph;
+}
+
 template <bool TANH>
 __device__ __forceinline__ unsigned fwd_layer(const float* __restrict__ W, const float* __restrict__ bias, int N, int K,
                                           const float* in, int ldin, float* out, int ldout, float* stage, int SF,
-                                          uint64_t* bars, unsigned ph) {
+                                          uint64_t* bars, unsigned ph, uint32_t tmem) {
+    // wide GEMM-shaped layers go to the tensor cores (tcgen05), the rest stays on the FP32 pipe
+    if (N <= 128 && N >= 32 && K >= 128 && (K & 3) == 0 && SF >= TC_STAGE_FLOATS)
+        return fwd_layer_tc<TANH>(W, bias, N, K, in, ldin, out, ldout, stage, SF, bars, ph, tmem);
     // 4*CN columns per warp: 28 fits N = 100 (reference widths) in four blocks, 32 otherwise
     const int blocks32 = (N + 31) / 32;
     if (N > 28 * (blocks32 - 1) && N <= 28 * blocks32 && blocks32 <= 8)
@@ -660,17 +911,17 @@ __device__ __noinline__ void dw_layer_smallk(float* __restrict__ gW, float* __re
 // whole forward of one network on the tile (model.py:35-45)
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, const UpdArgs& P, float* S, float* mu_out,
-                                            float* v_out, int tick, unsigned ph) {
+                                            float* v_out, int tick, unsigned ph, uint32_t tmem) {
     const dppo_dims& d = P.d;
     float* stage = S + P.o_stage;
     uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
-    ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph);
+    ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, tmem);
     K2_TICK(tick + 0);
-    ph = fwd_layer<true>(nw.W2, nw.b2, d.H2, d.H1, S + P.o_h1, P.ldH1, S + P.o_h2, P.ldH2, stage, P.SF, bars, ph);
+    ph = fwd_layer<true>(nw.W2, nw.b2, d.H2, d.H1, S + P.o_h1, P.ldH1, S + P.o_h2, P.ldH2, stage, P.SF, bars, ph, tmem);
     K2_TICK(tick + 1);
-    ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph);
+    ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, tmem);
     K2_TICK(tick + 2);
-    ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph);
+    ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph, tmem);
     K2_TICK(tick + 3);
     heads_fwd(hs, d.A, d.H2, d.G2, S + P.o_h2, P.ldH2, S + P.o_g2, P.ldG2, mu_out, P.ldA, v_out);
     K2_TICK(tick + 4);
@@ -702,10 +953,24 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
     // the two stage-buffer mbarriers are initialised ONCE; `ph` carries their phase parities
     if (threadIdx.x == 0) {
         uint64_t* b = reinterpret_cast<uint64_t*>(S + P.o_bars);
-        mbar_init(&b[0], 1);
+        mbar_init(&b[0], 1);                               // weight stage buffers (TMA bulk copies)
         mbar_init(&b[1], 1);
+        mbar_init(&b[2], 1);                               // tensor-core stages: MMAs done (tcgen05.commit)
+        mbar_init(&b[3], 1);
+        mbar_init(&b[4], UPD_THREADS / 32 - 1);            // tensor-core stages: filled, one arrival per producer warp
+        mbar_init(&b[5], UPD_THREADS / 32 - 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    // tensor memory: all 512 columns (one CTA per SM), 9 accumulators of 32 columns are used
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(S + P.o_bars + 12);
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = *tmem_slot;
     unsigned ph = 0;
     // head weights of both networks stay in shared memory for the whole kernel
     for (int i = threadIdx.x; i < 2 * P.head_floats; i += UPD_THREADS) S[P.o_heads + i] = 0.f;
@@ -747,9 +1012,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         // ---- forward(s) -----------------------------------------------------------------------
         if (P.flavour == DPPO_FLAVOUR_DPPO) {
             const Net no = net_of(P.theta_old, P.lay);
-            ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph);              // train.py:142
+            ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem);              // train.py:142
         }
-        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph);                    // train.py:145 / ppo.py:148
+        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem);                    // train.py:145 / ppo.py:148
 
         // ---- losses and their derivatives w.r.t. mu, v, log_std ---------------------------------
         const float lo = 1.f - P.clip, hi = 1.f + P.clip;               // clamp bounds (train.py:151)
@@ -934,6 +1199,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         }
         lp[3] = 0.f;
     }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x < 32)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
 }
 
 int fill_layout(const dppo_dims& d, Layout& L) {
@@ -993,9 +1262,10 @@ int plan(UpdArgs& P) {
     P.o_lpo = take(TM);
     P.o_zero_end = o;                           // everything before this is zeroed per tile
     P.o_red = take(UPD_THREADS);
-    P.o_bars = take(4);                         // two mbarriers (8 bytes each, 16-byte aligned)
+    P.o_bars = take(16);                        // six mbarriers (8 bytes each) + the TMEM base address
     P.head_floats = (d.A * P.ldH2 + ((d.A + 3) & ~3) + P.ldG2 + 4 + 3) & ~3;
     P.o_heads = take(2 * P.head_floats);
+    o = (o + 31) & ~31;                         // 128-byte aligned stage buffers (UMMA descriptors)
     P.o_stage = o;                              // everything before the stage is zeroed per tile
     // two weight staging buffers from what is left of the 227 KB
     int sf = ((227 * 1024 / 4 - o) / 2) & ~127;
