@@ -565,7 +565,7 @@ __device__ __forceinline__ unsigned fwd_layer(const float* __restrict__ W, const
                                           const float* in, int ldin, float* out, int ldout, float* stage, int SF,
                                           uint64_t* bars, unsigned ph, uint32_t tmem) {
     // wide GEMM-shaped layers go to the tensor cores (tcgen05), the rest stays on the FP32 pipe
-    if (N <= 128 && N >= 32 && K >= 128 && (K & 3) == 0 && SF >= TC_STAGE_FLOATS)
+    if (N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0 && SF >= TC_STAGE_FLOATS)
         return fwd_layer_tc<TANH>(W, bias, N, K, in, ldin, out, ldout, stage, SF, bars, ph, tmem);
     // 4*CN columns per warp: 28 fits N = 100 (reference widths) in four blocks, 32 otherwise
     const int blocks32 = (N + 31) / 32;
@@ -923,6 +923,126 @@ __device__ __noinline__ void dw_layer_smallk(float* __restrict__ gW, float* __re
     __syncthreads();
 }
 
+
+// ---------------------------------------------------------------------------
+// Tensor-core dW (tcgen05) for the wide layers:  dW[n][k] = sum_s dOut[s][n] in[s][k],  s < 32 samples.
+//   D_t[128 n][128 k] = A[n][s] . B_t[k][s]^T,  K_mma = 32 samples = four k-steps, 3xTF32 into ONE
+// 128-column accumulator per k-tile (only 12 accumulations, so a single accumulator is accurate);
+// up to four k-tiles live in the 512 TMEM columns at once and are drained in one epilogue.
+// Both operands are TRANSPOSED activations, gathered from shared memory (4 scalar loads per chunk)
+// by the producer warps: A = dOut^T (staged once), B_t = in^T tile (staged per tile, single buffer).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void tc_stage_transposed(char* hi_tile, char* lo_tile, const float* src, int ld, int col0,
+                                                    int ncols, int pt) {
+    // 128 rows (columns col0..col0+127 of src) x 8 chunks (samples 4kc..4kc+3); rows >= ncols are zero
+    for (int e = pt; e < 1024; e += TC_PRODUCERS) {
+        const int r = e & 127, kc = e >> 7;                 // consecutive lanes -> consecutive columns of src
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (col0 + r < ncols) {
+            const float* p = src + (4 * kc) * ld + col0 + r;
+            x = make_float4(p[0], p[ld], p[2 * ld], p[3 * ld]);
+        }
+        tc_store_split(hi_tile, lo_tile, r, kc, x);
+    }
+}
+
+__device__ __noinline__ unsigned dw_layer_tc(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut,
+                                             int ldd, const float* in, int ldin, bool accumulate, float* stage, int SF,
+                                             uint64_t* bars, unsigned ph, uint32_t tmem) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    uint64_t* empty = bars + 2;                             // stage 0's pair of barriers is enough here
+    uint64_t* full = bars + 4;
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    char* Abase = reinterpret_cast<char*>(stage);
+    char* Bbase = reinterpret_cast<char*>(stage + SF);
+    const int ntiles = (K + 127) >> 7;
+    __syncthreads();                                        // stage buffers free, dOut / in complete
+    for (int t0 = 0; t0 < ntiles; t0 += 4) {                // groups of four k-tiles = 512 TMEM columns
+        const int nt = min(4, ntiles - t0);
+        if (warp == 0) {
+            uint32_t adA = smem_u32(Abase), adB = smem_u32(Bbase);
+            const uint64_t ah = tc_desc(adA), al = tc_desc(adA + TC_A_BYTES);
+            const uint64_t bh = tc_desc(adB), bl = tc_desc(adB + TC_A_BYTES);
+            constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
+            for (int t = 0; t < nt; ++t) {
+                mbar_wait(&full[0], (ph >> 4) & 1u);
+                ph ^= 1u << 4;
+                if (lane == 0) {
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t d = tmem + 128 * t;
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        tc_mma(d, al + ks * KSTEP, bh + ks * KSTEP, idesc, ks ? 1u : 0u);
+                        tc_mma(d, ah + ks * KSTEP, bl + ks * KSTEP, idesc, 1u);
+                        tc_mma(d, ah + ks * KSTEP, bh + ks * KSTEP, idesc, 1u);
+                    }
+                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                     smem_u32(&empty[0]))
+                                 : "memory");
+                }
+                __syncwarp();
+            }
+            for (int t = 1; t < nt; ++t) ph ^= 1u << 2;     // empty phases the producers consumed in their loop
+            mbar_wait(&empty[0], (ph >> 2) & 1u);           // last commit: everything is in TMEM
+            ph ^= 1u << 2;
+        } else {
+            const int pt = tid - 32;
+            for (int t = 0; t < nt; ++t) {
+                if (t == 0) {
+                    if (t0 == 0) tc_stage_transposed(Abase, Abase + TC_A_BYTES, dOut, ldd, 0, N, pt);
+                } else {
+                    mbar_wait(&empty[0], (ph >> 2) & 1u);   // MMAs of the previous tile have read the B buffer
+                    ph ^= 1u << 2;
+                }
+                tc_stage_transposed(Bbase, Bbase + TC_A_BYTES, in, ldin, 128 * (t0 + t), K, pt);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&full[0]);
+            }
+            mbar_wait(&empty[0], (ph >> 2) & 1u);
+            ph ^= 1u << 2;
+            for (int t = 0; t < nt; ++t) ph ^= 1u << 4;     // full phases the issuer consumed
+        }
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        // epilogue: lane = n; warps 0-3 take columns 0..255 of the group, warps 4-7 columns 256..511
+        {
+            const int n = 32 * (warp & 3) + lane;
+            const int cbeg = (warp >> 2) * 256;
+            for (int c0 = cbeg; c0 < cbeg + 256 && c0 < nt * 128; c0 += 16) {
+                uint32_t v[16];
+                const uint32_t taddr = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + c0;
+                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                             : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                               "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                             : "r"(taddr));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                const int k0 = 128 * t0 + c0;
+                if (n < N) {
+#pragma unroll
+                    for (int j = 0; j < 16; j += 4) {
+                        if (k0 + j < K) {                   // K % 4 == 0
+                            float4 o = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                                   __uint_as_float(v[j + 3]));
+                            float4* dst = reinterpret_cast<float4*>(gW + (size_t)n * K + k0 + j);
+                            if (accumulate) { const float4 p = *dst; o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
+                            *dst = o;
+                        }
+                    }
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();                                    // TMEM and the B buffer are free for the next group
+    }
+    for (int n = tid; n < N; n += UPD_THREADS) {
+        float sb = 0.f;
+        for (int m = 0; m < 32; ++m) sb += dOut[m * ldd + n];
+        gb[n] = accumulate ? gb[n] + sb : sb;
+    }
+    __syncthreads();
+    return ph;
+}
+
 // ---------------------------------------------------------------------------
 // whole forward of one network on the tile (model.py:35-45)
 // ---------------------------------------------------------------------------
@@ -1172,7 +1292,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         K2_TICK(15);
         head_dx(hs_new.Wmu, P.ldH2, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2);          // h2 <- dz2
         K2_TICK(16);
-        dw_layer(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc);
+        if (d.H2 <= 128 && d.H2 >= 32 && d.H1 >= 64 && (d.H1 & 3) == 0 && P.SF >= TC_STAGE_FLOATS)
+            ph = dw_layer_tc(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc, stage, P.SF, bars, ph, tmem);
+        else
+            dw_layer(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc);
         K2_TICK(17);
         ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph);  // h1 <- dz1
         K2_TICK(18);
@@ -1184,7 +1307,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         K2_TICK(20);
         head_dx(hs_new.Wv, P.ldG2, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);
         K2_TICK(21);
-        dw_layer(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc);
+        if (d.G2 <= 128 && d.G2 >= 32 && d.G1 >= 64 && (d.G1 & 3) == 0 && P.SF >= TC_STAGE_FLOATS)
+            ph = dw_layer_tc(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc, stage, P.SF, bars, ph, tmem);
+        else
+            dw_layer(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc);
         K2_TICK(22);
         ph = dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph);
         K2_TICK(23);
