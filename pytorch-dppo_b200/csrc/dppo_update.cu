@@ -1043,6 +1043,40 @@ __device__ __noinline__ unsigned dw_layer_tc(float* __restrict__ gW, float* __re
     return ph;
 }
 
+
+// dW / db of both heads in one pass, one thread per output element (A*H2 + G2 weights, A + 1 biases):
+//   dWmu[n][k] = sum_s dmu[s][n] h2[s][k],   dWv[k] = sum_s dv[s] g2[s][k]    (s ascending: fixed order)
+__device__ __noinline__ void heads_dw(float* __restrict__ gWmu, float* __restrict__ gbmu, float* __restrict__ gWv,
+                                      float* __restrict__ gbv, int A, int H2, int G2, const float* dmu, int ldA,
+                                      const float* dv4, const float* h2, int ldh2, const float* g2, int ldg2,
+                                      bool accumulate) {
+    const int nmu = A * H2;
+    for (int o = threadIdx.x; o < nmu + G2 + A + 1; o += UPD_THREADS) {
+        float s = 0.f;
+        float* dst;
+        if (o < nmu) {
+            const int n = o / H2, k = o - n * H2;
+#pragma unroll 8
+            for (int m = 0; m < UPD_ROWS; ++m) s = fmaf(dmu[m * ldA + n], h2[m * ldh2 + k], s);
+            dst = gWmu + o;
+        } else if (o < nmu + G2) {
+            const int k = o - nmu;
+#pragma unroll 8
+            for (int m = 0; m < UPD_ROWS; ++m) s = fmaf(dv4[4 * m], g2[m * ldg2 + k], s);
+            dst = gWv + k;
+        } else if (o < nmu + G2 + A) {
+            const int n = o - nmu - G2;
+            for (int m = 0; m < UPD_ROWS; ++m) s += dmu[m * ldA + n];
+            dst = gbmu + n;
+        } else {
+            for (int m = 0; m < UPD_ROWS; ++m) s += dv4[4 * m];
+            dst = gbv;
+        }
+        *dst = accumulate ? *dst + s : s;
+    }
+    __syncthreads();
+}
+
 // ---------------------------------------------------------------------------
 // whole forward of one network on the tile (model.py:35-45)
 // ---------------------------------------------------------------------------
@@ -1288,7 +1322,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         const bool acc = !first;
         float* stage = S + P.o_stage;
         uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
-        dw_layer(go.Wmu, go.bmu, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2, acc);
+        heads_dw(go.Wmu, go.bmu, go.Wv, go.bv, d.A, d.H2, d.G2, S + P.o_dmu, P.ldA, S + P.o_dv, S + P.o_h2, P.ldH2,
+                 S + P.o_g2, P.ldG2, acc);
         K2_TICK(15);
         head_dx(hs_new.Wmu, P.ldH2, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2);          // h2 <- dz2
         K2_TICK(16);
@@ -1303,7 +1338,6 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         else dw_layer(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc);
         K2_TICK(19);
         // ---- backward, value trunk --------------------------------------------------------------
-        dw_layer(go.Wv, go.bv, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2, acc);
         K2_TICK(20);
         head_dx(hs_new.Wv, P.ldG2, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);
         K2_TICK(21);
