@@ -94,7 +94,7 @@ struct UpdArgs {
     int o_x, o_h1, o_h2, o_g1, o_g2, o_act, o_mu, o_muo, o_dmu, o_v, o_vo, o_dv, o_adv, o_ret, o_lpo, o_red, o_stage;
     int smem_floats;
     int SF;                                     // floats per weight staging buffer
-    int o_zero_end, o_heads, head_floats, o_bars;
+    int o_zero_end, o_heads, head_floats, o_bars, heads_in_smem;
 };
 
 __device__ __forceinline__ Net net_of(const float* t, const Layout& L) {
@@ -576,7 +576,7 @@ __device__ __forceinline__ unsigned fwd_layer(const float* __restrict__ W, const
 
 // head weights (mu: [A][ldH2] + bias[A], v: [ldG2] + bias) of one network, resident in shared
 // memory for the whole kernel (they are tiny and every tile needs them four times)
-struct HeadS { const float *Wmu, *bmu, *Wv, *bv; };
+struct HeadS { const float *Wmu, *bmu, *Wv, *bv; int ldw; };   // ldw: row stride of Wmu
 
 __device__ __forceinline__ void load_heads(float* dst, const Net& nw, const UpdArgs& P) {
     const dppo_dims& d = P.d;
@@ -592,6 +592,7 @@ __device__ __forceinline__ void load_heads(float* dst, const Net& nw, const UpdA
 }
 __device__ __forceinline__ HeadS heads_at(const float* base, const UpdArgs& P) {
     HeadS h;
+    h.ldw = P.ldH2;
     h.Wmu = base;
     h.bmu = base + P.d.A * P.ldH2;
     h.Wv = h.bmu + ((P.d.A + 3) & ~3);
@@ -607,7 +608,7 @@ __device__ __noinline__ void heads_fwd(HeadS hs, int A, int H2, int G2, const fl
         const int m = o / (A + 1), n = o - m * (A + 1);
         const bool isv = n == A;
         const float* x = isv ? g2 + m * ldg2 : h2 + m * ldh2;
-        const float* w = isv ? hs.Wv : hs.Wmu + n * ldh2;
+        const float* w = isv ? hs.Wv : hs.Wmu + n * hs.ldw;
         const int K4 = ((isv ? G2 : H2) + 3) >> 2;          // pad columns: activations finite, weights 0
         float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
         for (int k = 0; k < K4; ++k) {
@@ -1143,12 +1144,22 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
     const uint32_t tmem = *tmem_slot;
     unsigned ph = 0;
     // head weights of both networks stay in shared memory for the whole kernel
-    for (int i = threadIdx.x; i < 2 * P.head_floats; i += UPD_THREADS) S[P.o_heads + i] = 0.f;
-    __syncthreads();
-    load_heads(S + P.o_heads, nw, P);
-    if (P.flavour == DPPO_FLAVOUR_DPPO) load_heads(S + P.o_heads + P.head_floats, net_of(P.theta_old, P.lay), P);
+    // (when shared memory is tight - Humanoid with 256-wide nets - they are read from global memory instead)
+    if (P.heads_in_smem) {
+        for (int i = threadIdx.x; i < 2 * P.head_floats; i += UPD_THREADS) S[P.o_heads + i] = 0.f;
+        __syncthreads();
+        load_heads(S + P.o_heads, nw, P);
+        if (P.flavour == DPPO_FLAVOUR_DPPO) load_heads(S + P.o_heads + P.head_floats, net_of(P.theta_old, P.lay), P);
+    }
     K2_TICK(0);
-    const HeadS hs_new = heads_at(S + P.o_heads, P), hs_old = heads_at(S + P.o_heads + P.head_floats, P);
+    HeadS hs_new = heads_at(S + P.o_heads, P), hs_old = heads_at(S + P.o_heads + P.head_floats, P);
+    if (!P.heads_in_smem) {
+        hs_new.Wmu = nw.Wmu; hs_new.bmu = nw.bmu; hs_new.Wv = nw.Wv; hs_new.bv = nw.bv; hs_new.ldw = d.H2;
+        if (P.flavour == DPPO_FLAVOUR_DPPO) {
+            const Net no = net_of(P.theta_old, P.lay);
+            hs_old.Wmu = no.Wmu; hs_old.bmu = no.bmu; hs_old.Wv = no.Wv; hs_old.bv = no.bv; hs_old.ldw = d.H2;
+        }
+    }
     if (threadIdx.x < DPPO_N_PARAMS)                                   // padding floats of the bucket stay 0
         for (int j = P.lay.size[threadIdx.x]; j < ((P.lay.size[threadIdx.x] + 3) & ~3); ++j)
             part[P.lay.off[threadIdx.x] + j] = 0.f;
@@ -1325,7 +1336,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         heads_dw(go.Wmu, go.bmu, go.Wv, go.bv, d.A, d.H2, d.G2, S + P.o_dmu, P.ldA, S + P.o_dv, S + P.o_h2, P.ldH2,
                  S + P.o_g2, P.ldG2, acc);
         K2_TICK(15);
-        head_dx(hs_new.Wmu, P.ldH2, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2);          // h2 <- dz2
+        head_dx(hs_new.Wmu, hs_new.ldw, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2);          // h2 <- dz2
         K2_TICK(16);
         if (d.H2 <= 128 && d.H2 >= 32 && d.H1 >= 64 && (d.H1 & 3) == 0 && P.SF >= TC_STAGE_FLOATS)
             ph = dw_layer_tc(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc, stage, P.SF, bars, ph, tmem);
@@ -1339,7 +1350,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         K2_TICK(19);
         // ---- backward, value trunk --------------------------------------------------------------
         K2_TICK(20);
-        head_dx(hs_new.Wv, P.ldG2, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);
+        head_dx(hs_new.Wv, 0, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);
         K2_TICK(21);
         if (d.G2 <= 128 && d.G2 >= 32 && d.G1 >= 64 && (d.G1 & 3) == 0 && P.SF >= TC_STAGE_FLOATS)
             ph = dw_layer_tc(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc, stage, P.SF, bars, ph, tmem);
@@ -1440,7 +1451,12 @@ int plan(UpdArgs& P) {
     P.o_red = take(UPD_THREADS);
     P.o_bars = take(16);                        // six mbarriers (8 bytes each) + the TMEM base address
     P.head_floats = (d.A * P.ldH2 + ((d.A + 3) & ~3) + P.ldG2 + 4 + 3) & ~3;
-    P.o_heads = take(2 * P.head_floats);
+    // head weights resident in shared memory unless that would squeeze the stage buffers below their
+    // minimum (then they are read from global memory, which needs 16-byte aligned rows)
+    P.heads_in_smem = 1;
+    if ((227 * 1024 / 4 - o - 2 * P.head_floats - 64) / 2 < UPD_STAGE_MIN && (d.H2 & 3) == 0 && (d.G2 & 3) == 0)
+        P.heads_in_smem = 0;
+    P.o_heads = take(P.heads_in_smem ? 2 * P.head_floats : 4);
     o = (o + 31) & ~31;                         // 128-byte aligned stage buffers (UMMA descriptors)
     P.o_stage = o;                              // everything before the stage is zeroed per tile
     // two weight staging buffers from what is left of the 227 KB

@@ -277,6 +277,9 @@ CASES = [
     (3, 2, (8, 12, 20, 4), 100, 37),                   # ragged: B not a multiple of the tile
     (17, 6, (100, 100, 500, 100), 8192, 6000),         # more tiles than SMs: CTAs loop and accumulate
     (33, 5, (256, 256, 256, 256), 600, 300),           # wide
+    (376, 17, (256, 256, 256, 256), 700, 512),         # C5: Humanoid shape, 256x256 nets
+    (15, 3, (100, 100, 500, 100), 2048, 2048),         # C3: HopperBullet shape
+    (17, 6, (128, 128, 128, 128), 1024, 1024),         # 128-wide: every hidden layer on the tcgen05 path
 ]
 
 
