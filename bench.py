@@ -216,9 +216,8 @@ def main():
     def step_resident():
         """inputs already in HBM: K4 -> K1 -> E x (K2 -> K3).  (minibatch positions are host
         data by nature - random.sample - and are staged before the timed events.)"""
-        stats.observes_batch(devbuf.raw_obs, out=devbuf.obs)
-        engine.gae(devbuf)
-        engine.run_epochs(devbuf, gshared=sgb.flat, use_graph=use_graph, indices_staged=True)
+        engine.run_epochs(devbuf, gshared=sgb.flat, use_graph=use_graph, indices_staged=True, obs_stats=stats,
+                          with_gae=True)
 
     def barrier():
         if dist is not None:
@@ -231,7 +230,7 @@ def main():
         engine.draw_indices(wl["T"], rng)
         engine.idx_dev.copy_(engine.idx_host, non_blocking=True)
         step_resident()
-    launches_per_step = 3 + 1 + engine.launches_per_cycle - (1 if engine.flavour == nv.FLAVOUR_DPPO else 0)
+    launches_per_step = engine.launches_per_cycle - (1 if engine.flavour == nv.FLAVOUR_DPPO else 0)
     barrier()
 
     # ---- timed region: K steps, device-resident inputs -------------------------------------
@@ -255,27 +254,24 @@ def main():
     sampler.join()
 
     # ---- end to end: host rollouts through the public call, copies inside the timed region --
+    # engine.update_stream is the call a training loop makes: every step uploads its rollout from pinned
+    # host memory and downloads its losses; the upload of step i+1 and the host-side index sampling overlap
+    # the kernels of step i (two device buffers, copy stream).
+    from b200_engine import RolloutBuffer
+    devbuf2 = RolloutBuffer(wl["T"], wl["O"], wl["A"], dev)
+    devs2 = [devbuf, devbuf2]
     reset_stats()
-    e2e_evs = []
-    h2d = d2h = 0
-    for _ in range(2):
-        reset_stats()
-        engine.update_from_host(host, devbuf, obs_stats=stats, rng=rng, use_graph=use_graph, gshared=sgb.flat,
-                                prefetch_next=True)
+    engine.update_stream([host], devs2, 3, obs_stats=stats, rng=rng, gshared=sgb.flat, on_step=None)
     barrier()
     n_e2e = max(3, min(args.steps, 100))
-    for _ in range(n_e2e):
-        flush.fill_(1)
-        reset_stats()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        _, h2d, d2h = engine.update_from_host(host, devbuf, obs_stats=stats, rng=rng, use_graph=use_graph,
-                                              gshared=sgb.flat, prefetch_next=True)
-        e1.record()
-        e2e_evs.append((e0, e1))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reset_stats()
+    e0.record()
+    _, h2d, d2h = engine.update_stream([host], devs2, n_e2e, obs_stats=stats, rng=rng, gshared=sgb.flat,
+                                       on_step=lambda i: reset_stats() if i % 64 == 63 else None)
+    e1.record()
     barrier()
-    e2e_ms = sum(a.elapsed_time(b) for a, b in e2e_evs)
+    e2e_ms = e0.elapsed_time(e1)
 
     # ---- per-kernel durations (instrumented pass, plain launches, same data) ----------------
     kt = kernel_times(nv, engine, stats, devbuf, sgb, wl, flush)

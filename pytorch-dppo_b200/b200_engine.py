@@ -107,8 +107,14 @@ class UpdateEngine:
         return self.idx_host
 
     # ---- E x (K2 -> K3) -----------------------------------------------------------------------
-    def _launch_epochs(self, buf, gshared):
+    def _launch_epochs(self, buf, gshared, obs_stats=None, with_gae=False):
         n = 0
+        if obs_stats is not None:                              # K4: raw observations -> normalised states
+            obs_stats.observes_batch(buf.raw_obs, out=buf.obs)
+            n += 3
+        if with_gae:                                           # K1
+            self.gae(buf)
+            n += 1
         if self.flavour == nv.FLAVOUR_DPPO:
             self.theta_old.copy_(self.theta)                       # model_old = copy of model, train.py:128-129
             n += 1
@@ -130,36 +136,49 @@ class UpdateEngine:
         return n
 
     def _stage_scalars(self):
+        ev = getattr(self, "_scalars_read", None)
+        if ev is not None:
+            ev.synchronize()                          # the previous upload of the pinned block has been consumed
         for k in range(self.E):
             s = nv.adam_scalars(self.step + k + 1, self.lr, self.betas[0], self.betas[1], self.eps)
             self.scalars_host[k, :6] = torch.tensor(s)
         self.scalars_dev.copy_(self.scalars_host, non_blocking=True)
+        self._scalars_read = torch.cuda.Event()
+        self._scalars_read.record(torch.cuda.current_stream())
 
-    def run_epochs(self, buf, gshared=None, use_graph=True, indices_staged=False):
+    def run_epochs(self, buf, gshared=None, use_graph=True, indices_staged=False, obs_stats=None, with_gae=False,
+                   scalars_staged=False):
         """The E epochs of one outer iteration on minibatch positions already in
         ``idx_host`` (see draw_indices).  Returns the (E,4) device tensor of per-epoch
         loss terms (clip, value, entropy, -)."""
         if not indices_staged:
             self.idx_dev.copy_(self.idx_host, non_blocking=True)
-        self._stage_scalars()
+        if not scalars_staged:
+            self._stage_scalars()
         if not use_graph or (self.comm is not None and self.comm.mode == "nccl"):
-            self.launches_per_cycle = self._launch_epochs(buf, gshared)
+            self.launches_per_cycle = self._launch_epochs(buf, gshared, obs_stats, with_gae)
         else:
-            key = (id(buf), None if gshared is None else gshared.data_ptr())
+            key = (id(buf), None if gshared is None else gshared.data_ptr(), id(obs_stats), with_gae)
             if key not in self._graphs:
                 # warm-up launch outside capture (sets kernel attributes), on scratch copies of the state
-                saved = [t.clone() for t in (self.theta, self.theta_old, self.m, self.v)]
+                state = [self.theta, self.theta_old, self.m, self.v]
+                if obs_stats is not None:
+                    state += [obs_stats.n, obs_stats.mean, obs_stats.mean_diff, obs_stats.var]
+                    obs_stats._scratch_for(buf.T)                  # allocate outside the capture
+                if with_gae and (self._gae_scratch is None or self._gae_scratch.numel() < nv.gae_scratch_bytes(buf.T)):
+                    self._gae_scratch = torch.empty(nv.gae_scratch_bytes(buf.T), dtype=torch.uint8, device=self.device)
+                saved = [t.clone() for t in state]
                 gsaved = None if gshared is None else gshared.clone()
-                self._launch_epochs(buf, gshared)
+                self._launch_epochs(buf, gshared, obs_stats, with_gae)
                 torch.cuda.synchronize()
-                for t, s in zip((self.theta, self.theta_old, self.m, self.v), saved):
+                for t, s in zip(state, saved):
                     t.copy_(s)
                 if gshared is not None:
                     gshared.copy_(gsaved)
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g):
-                    n = self._launch_epochs(buf, gshared)
-                for t, s in zip((self.theta, self.theta_old, self.m, self.v), saved):
+                    n = self._launch_epochs(buf, gshared, obs_stats, with_gae)
+                for t, s in zip(state, saved):
                     t.copy_(s)                                     # capture does not execute, but be explicit
                 self._graphs[key] = (g, n)
             g, n = self._graphs[key]
@@ -198,3 +217,81 @@ class UpdateEngine:
             self._prefetched = (dev.T, id(rng))
         torch.cuda.current_stream().synchronize()
         return self.loss_host, h2d, self.loss_host.numel() * 4
+
+
+    def update_stream(self, hosts, devs, n_steps, obs_stats=None, rng=random, gshared=None, on_step=None):
+        """``n_steps`` consecutive outer iterations from HOST rollouts, software-pipelined the way a training
+        loop would run them: a copy stream uploads rollout i+1 (pinned ``hosts[(i+1) % len(hosts)]`` ->
+        ``devs[(i+1) % 2]``) while the compute stream runs K4, K1 and the E epochs of rollout i, and the host
+        draws the next minibatch positions meanwhile.  Every step still copies its own inputs H2D and its
+        per-epoch losses D2H.  Returns (list of per-step loss tensors on the host, h2d bytes/step, d2h bytes/step)."""
+        assert len(devs) == 2
+        fields = ["act", "rew", "val", "boot", "seg_end"] + (["raw_obs"] if obs_stats is not None else ["obs"])
+        if self.flavour == nv.FLAVOUR_PPO:
+            fields.append("logp")
+        main = torch.cuda.current_stream()
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream()
+            self._loss_ring = [torch.zeros(self.E, 4, pin_memory=True) for _ in range(4)]
+        cs = self._copy_stream
+        copied = [torch.cuda.Event(), torch.cuda.Event()]
+        consumed = [torch.cuda.Event(), torch.cuda.Event()]
+        h2d = 0
+        cs.wait_stream(main)
+        with torch.cuda.stream(cs):
+            h2d = devs[0].copy_from(hosts[0], fields)
+            copied[0].record(cs)
+        # minibatch positions are drawn by a worker thread (the C sampler releases the GIL) one step ahead,
+        # into the pinned block that is not being uploaded
+        if not hasattr(self, "_sampler_pool"):
+            from concurrent.futures import ThreadPoolExecutor
+            self._sampler_pool = ThreadPoolExecutor(max_workers=1)
+        T = devs[0].T
+        self.draw_indices(T, rng)
+        losses = []
+        idx_read = [None, None]                       # per pinned block: event after the upload that read it
+        cur = 0
+        blocks = [self.idx_host, self._idx_next]
+        fut = None
+        for i in range(n_steps):
+            b = i & 1
+            if fut is not None:
+                fut.result()                          # positions of this step are in blocks[cur]
+            main.wait_event(copied[b])
+            self.idx_host = blocks[cur]
+            self.idx_dev.copy_(self.idx_host, non_blocking=True)
+            idx_read[cur] = torch.cuda.Event()
+            idx_read[cur].record(main)
+            if i + 1 < n_steps:
+                nxt = 1 - cur
+                if idx_read[nxt] is not None:
+                    idx_read[nxt].synchronize()       # the upload that read that block two steps ago is done
+                fut = self._sampler_pool.submit(nv.sample_indices, T, self.B, self.E, rng, blocks[nxt])
+                cur_next = nxt
+            self._stage_scalars()
+            small_done = torch.cuda.Event()
+            small_done.record(main)                   # this step's small uploads have left the H2D engine
+            self.run_epochs(devs[b], gshared=gshared, use_graph=True, indices_staged=True, obs_stats=obs_stats,
+                            with_gae=True, scalars_staged=True)   # K4 + K1 + E x (K2, K3): one graph replay
+            consumed[b].record(main)
+            if i + 1 < n_steps:
+                # upload the next rollout behind this step's compute.  It may only start once this step's own
+                # small uploads are through: there is ONE H2D copy engine, and the 7 MB upload becomes runnable
+                # at the same moment as the index block of this step - queued ahead of it, it held every step
+                # back by 0.2 ms (tools/e2e_gaps.py)
+                with torch.cuda.stream(cs):
+                    cs.wait_event(small_done)
+                    if i >= 1:
+                        cs.wait_event(consumed[1 - b])
+                    devs[1 - b].copy_from(hosts[(i + 1) % len(hosts)], fields)
+                    copied[1 - b].record(cs)
+            out = self._loss_ring[i % len(self._loss_ring)]
+            out.copy_(self.loss_out, non_blocking=True)
+            losses.append(out)
+            if on_step is not None:
+                on_step(i)
+            if i + 1 < n_steps:
+                cur = cur_next
+        self.idx_host, self._idx_next = blocks[cur], blocks[1 - cur]
+        main.synchronize()
+        return losses, h2d + self.idx_host.numel() * 4 + self.scalars_host.numel() * 4, self.E * 16

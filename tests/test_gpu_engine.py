@@ -237,3 +237,36 @@ def test_prefetched_indices_are_the_same_stream():
         eng.update_from_host(host, dev, obs_stats=None, rng=rng, prefetch_next=True)
         want = [ref.sample(range(T), B) for _ in range(E)]
         assert eng.idx_host.tolist() == want, call
+
+
+def test_update_stream_matches_step_by_step():
+    """The pipelined host->device stream (copy stream + two device buffers + early index sampling) must produce
+    exactly what step-by-step update_from_host calls produce."""
+    import b200_native as nv
+    from b200_engine import RolloutBuffer, UpdateEngine
+    from model import Model, Shared_obs_stats
+    from synthetic import make_rollout
+    T, B, E, n = 2048, 256, 3, 5
+    res = []
+    for mode in ("stream", "steps"):
+        torch.manual_seed(1)
+        m = Model(17, 6, device=DEV)
+        stats = Shared_obs_stats(17)
+        hosts = [make_rollout(m, stats, T, seed=40 + i, flavour=nv.FLAVOUR_DPPO, seg_len=500)[0] for i in range(3)]
+        devs = [RolloutBuffer(T, 17, 6, DEV), RolloutBuffer(T, 17, 6, DEV)]
+        eng = UpdateEngine(m, nv.FLAVOUR_DPPO, B, E, 3e-4)
+        rng = random.Random(4)
+        if mode == "stream":
+            losses, h2d, d2h = eng.update_stream(hosts, devs, n, obs_stats=stats, rng=rng)
+            losses = [l.clone() for l in losses[-2:]]
+        else:
+            losses = []
+            for i in range(n):
+                l, _, _ = eng.update_from_host(hosts[i % 3], devs[0], obs_stats=stats, rng=rng)
+                losses.append(l.clone())
+            losses = losses[-2:]
+        torch.cuda.synchronize()
+        res.append((m.flat.clone(), eng.m.clone(), stats.mean.clone(), losses))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2])
+    for a, b in zip(res[0][3], res[1][3]):
+        assert torch.equal(a, b)
