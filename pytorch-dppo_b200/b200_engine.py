@@ -295,3 +295,32 @@ class UpdateEngine:
         self.idx_host, self._idx_next = blocks[cur], blocks[1 - cur]
         main.synchronize()
         return losses, h2d + self.idx_host.numel() * 4 + self.scalars_host.numel() * 4, self.E * 16
+
+
+# ---- checkpoint / resume (the reference has none: SURVEY section 5; "next" row N4) --------------------
+def save_checkpoint(path, engine, obs_stats=None, rng=None):
+    """Parameters, Adam moments and update count, running observation statistics and the Python
+    generator that draws the minibatch positions - everything a bit-identical resume needs."""
+    state = {"theta": engine.theta.detach().cpu(), "m": engine.m.cpu(), "v": engine.v.cpu(), "step": engine.step,
+             "dims": tuple(getattr(engine.dims, f) for f in ("O", "A", "H1", "H2", "G1", "G2"))}
+    if obs_stats is not None:
+        state["obs_stats"] = {k: getattr(obs_stats, k).cpu() for k in ("n", "mean", "mean_diff", "var")}
+    if rng is not None:
+        state["rng"] = rng.getstate()
+    torch.save(state, path)
+
+
+def load_checkpoint(path, engine, obs_stats=None, rng=None):
+    state = torch.load(path, weights_only=False)
+    if tuple(state["dims"]) != tuple(getattr(engine.dims, f) for f in ("O", "A", "H1", "H2", "G1", "G2")):
+        raise nv.DppoError("checkpoint was written for a different network shape")
+    engine.theta.copy_(state["theta"])
+    engine.m.copy_(state["m"])
+    engine.v.copy_(state["v"])
+    engine.step = int(state["step"])
+    engine._prefetched = None
+    if obs_stats is not None and "obs_stats" in state:
+        for k, t in state["obs_stats"].items():
+            getattr(obs_stats, k).copy_(t)
+    if rng is not None and "rng" in state:
+        rng.setstate(state["rng"])
