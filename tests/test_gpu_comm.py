@@ -92,3 +92,13 @@ def test_two_gpus_match_single_process(mode):
                          timeout=300)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "MULTI_GPU_OK" in out.stdout
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_gpus_main_launcher():
+    """pytorch-dppo_b200/main.py `run` under torchrun: train.train on every rank, exchange inside K3."""
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29617",
+                          os.path.join(ROOT, "tests", "multi_gpu_main_worker.py")], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "MAIN_LAUNCHER_OK" in out.stdout
