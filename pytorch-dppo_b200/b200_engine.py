@@ -119,10 +119,12 @@ class UpdateEngine:
             self.theta_old.copy_(self.theta)                       # model_old = copy of model, train.py:128-129
             n += 1
         for k in range(self.E):
+            # epoch 0: model_old is a copy of model (train.py:128-129) - passing theta itself lets K2 skip the
+            # second forward; from epoch 1 on theta_old is the lagging copy K3 maintains (train.py:164)
+            old = None if self.flavour != nv.FLAVOUR_DPPO else (self.theta if k == 0 else self.theta_old)
             nv.update_fused(self.flavour, self.dims, buf.obs, buf.act, buf.adv, buf.ret,
                             buf.logp if self.flavour == nv.FLAVOUR_PPO else None, self.idx_dev[k], self.theta,
-                            self.theta_old if self.flavour == nv.FLAVOUR_DPPO else None, self.clip, self.ent_coeff,
-                            self.partials, self.loss_partials)
+                            old, self.clip, self.ent_coeff, self.partials, self.loss_partials)
             n += 1
             if self.comm is not None:
                 n += self.comm.allreduce_adam(self, k, gshared)

@@ -1191,11 +1191,19 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
 
         K2_TICK(2);
         // ---- forward(s) -----------------------------------------------------------------------
-        if (P.flavour == DPPO_FLAVOUR_DPPO) {
+        // epoch 0 of a cycle: model_old is a copy of model (train.py:128-129), so the caller passes
+        // theta_old == theta and the old network's outputs are the new network's, bit for bit
+        const bool same_old = P.flavour == DPPO_FLAVOUR_DPPO && P.theta_old == P.theta;
+        if (P.flavour == DPPO_FLAVOUR_DPPO && !same_old) {
             const Net no = net_of(P.theta_old, P.lay);
             ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem);              // train.py:142
         }
         ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem);                    // train.py:145 / ppo.py:148
+        if (same_old) {
+            for (int e = threadIdx.x; e < UPD_ROWS * P.ldA; e += UPD_THREADS) S[P.o_muo + e] = S[P.o_mu + e];
+            for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
+            __syncthreads();
+        }
 
         // ---- losses and their derivatives w.r.t. mu, v, log_std ---------------------------------
         const float lo = 1.f - P.clip, hi = 1.f + P.clip;               // clamp bounds (train.py:151)
