@@ -9,7 +9,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdppo_b200.so")
+# DPPO_LIB: load another build of the same library (A/B runs of kernel variants); default is the in-tree build
+LIB_PATH = os.environ.get("DPPO_LIB") or os.path.join(_HERE, "libdppo_b200.so")
 
 FLAVOUR_DPPO = 0
 FLAVOUR_PPO = 1

@@ -20,27 +20,35 @@
 // multiples of 16 B so the quarter-warp phases are bank-conflict free.
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
+#include <cuda.h>
 #include "common.cuh"
 
 // per-phase clock64() stamps of CTA 0 (tools/k2clock.py); compiled in with -DDPPO_K2_TIMING only
 #ifdef DPPO_K2_TIMING
 __device__ long long g_k2_clock[64];
 #define K2_TICK(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_k2_clock[i] = clock64(); } while (0)
-#define K2_ACC_DECL long long acc_t0 = 0
+#define K2_ACC_DECL long long acc_t0 = 0; long long acc_r[8] = {0, 0, 0, 0, 0, 0, 0, 0}
 #define K2_ACC_T0 acc_t0 = clock64()
-#define K2_ACC(i) do { if (blockIdx.x == 0 && (threadIdx.x == 0 || threadIdx.x == 32)) { long long t = clock64(); g_k2_clock[i] += t - acc_t0; acc_t0 = t; } } while (0)
+#define K2_ACC(i) do { long long t = clock64(); acc_r[(i) - 40] += t - acc_t0; acc_t0 = t; } while (0)
+#define K2_ACC_FLUSH do { if (blockIdx.x == 0 && (threadIdx.x == 0 || threadIdx.x == 32)) for (int q = 0; q < 8; ++q) g_k2_clock[40 + q] += acc_r[q]; } while (0)
 #else
 #define K2_TICK(i) do { } while (0)
 #define K2_ACC_DECL
 #define K2_ACC_T0
 #define K2_ACC(i) do { } while (0)
+#define K2_ACC_FLUSH do { } while (0)
 #endif
 
 namespace {
 
-constexpr int UPD_THREADS = 256;
+#ifndef DPPO_K2_THREADS
+#define DPPO_K2_THREADS 256
+#endif
+constexpr int UPD_THREADS = DPPO_K2_THREADS;      // 256 or 512 (8 or 16 warps)
+constexpr int UPD_WGROUPS = UPD_THREADS / 128;      // warp quads: each covers the 128 TMEM lanes once
 constexpr int UPD_TM_MAX = 32;
-constexpr int UPD_STAGE_MAX = 11520;        // floats per staging buffer (45 KB: one tensor-core k-block), two buffers
+constexpr int UPD_STAGE_MAX = 12800;        // floats per staging buffer, two buffers (together the 100 KB tensor-core staging region)
 constexpr int UPD_STAGE_MIN = 4096;
 constexpr int UPD_ROWS = 32;                // sample rows per CTA tile (TM <= 32 of them are real)
 constexpr int UPD_MAX_A = 64;
@@ -95,6 +103,9 @@ struct UpdArgs {
     int smem_floats;
     int SF;                                     // floats per weight staging buffer
     int o_zero_end, o_heads, head_floats, o_bars, heads_in_smem;
+    // tensor maps of the wide layers' weights (TMA tiles for the tensor-core path); use_ts: maps valid and staging region big enough
+    int use_ts;
+    alignas(64) CUtensorMap map_fwd[2][2];          // [theta, theta_old][W2, V2]: box 32 (k) x 128 (n), SWIZZLE_128B
 };
 
 __device__ __forceinline__ Net net_of(const float* t, const Layout& L) {
@@ -377,6 +388,23 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
 }
 
+// tcgen05.ld of NC (8 or 16) consecutive 32-bit columns of this warp's 32 TMEM lanes, waited for
+template <int NC>
+__device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[NC]) {
+    static_assert(NC == 8 || NC == 16, "tmem_ld: 8 or 16 columns");
+    if constexpr (NC == 16) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                     : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                       "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                     : "r"(taddr));
+    } else {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                     : "r"(taddr));
+    }
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
 // Warp 0 only issues the MMAs (one elected thread, as tcgen05 wants); warps 1-7 are producers that
 // split and stage the operands.  No block-wide barrier inside the k loop: producers signal a filled
 // stage on full[s] (one arrival per warp), the issuer waits for it, issues 12 MMAs and commits them to
@@ -441,11 +469,14 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
         // bring the issuer's view of the empty barriers up to date (phases the producers consumed in the
         // loop), then wait for the last commit of each stage like everybody else: `ph` ends up uniform
         for (int kb = 2; kb < nkb; ++kb) ph ^= 1u << (2 + (kb & 1));
+        K2_ACC_T0;
         for (int kb = (nkb > 2 ? nkb - 2 : 0); kb < nkb; ++kb) {
             const int s = kb & 1;
             mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
             ph ^= 1u << (2 + s);
         }
+        K2_ACC(47);
+        K2_ACC_FLUSH;
     } else {
         // ---------------- producers ----------------
         const int pt = tid - 32;                            // 0..223
@@ -463,7 +494,7 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
             so[i] = tc_off(r & 127, kc);
             kc4[i] = e < 1024 ? 4 * kc : K;                 // chunks beyond the tile are never stored
         }
-        const int bm = pt >> 3, bkc = pt & 7;               // B: chunk pt (and pt + 224 for pt < 32)
+        const int bkc = pt & 7;                             // B: chunks pt, pt + TC_PRODUCERS, ...
         // weight chunks are fetched TWO k-blocks ahead (two register sets): one block of lead did not
         // cover the L2 latency
         float4 preA[NCH], preB[NCH];
@@ -497,15 +528,11 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
                     *reinterpret_cast<float4*>(Al + so[i]) = l;
                 }
             }
-            {
-                const int k = kb * TC_KB + 4 * bkc;
-                const float4 x = (k < K) ? *reinterpret_cast<const float4*>(in + bm * ldin + k) : make_float4(0.f, 0.f, 0.f, 0.f);
-                tc_store_split(Bh, Bl, bm, bkc, x);
-                if (pt < 32) {                              // the remaining 32 of the 256 B chunks
-                    const int m2 = (pt + TC_PRODUCERS) >> 3;
-                    const float4 y = (k < K) ? *reinterpret_cast<const float4*>(in + m2 * ldin + k) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    tc_store_split(Bh, Bl, m2, bkc, y);
-                }
+#pragma unroll
+            for (int e = pt; e < 8 * UPD_ROWS; e += TC_PRODUCERS) {     // the 256 B chunks (TC_PRODUCERS % 8 == 0)
+                const int k = kb * TC_KB + 4 * bkc, m = e >> 3;
+                const float4 x = (k < K) ? *reinterpret_cast<const float4*>(in + m * ldin + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+                tc_store_split(Bh, Bl, m, bkc, x);
             }
             K2_ACC(43);
             if (kb + 2 < nkb) prefetch(pre, kb + 2);        // lands while the next block is staged
@@ -517,31 +544,227 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
             K2_ACC(46);
         }
         // drain: wait for the last commits (they cover every MMA issued), keeps `ph` equal to the issuer's
+        K2_ACC_T0;
         for (int kb = (nkb > 2 ? nkb - 2 : 0); kb < nkb; ++kb) {
             const int s = kb & 1;
             mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
             ph ^= 1u << (2 + s);
         }
+        K2_ACC(47);
+        K2_ACC_FLUSH;
         for (int kb = 0; kb < nkb; ++kb) ph ^= 1u << (4 + (kb & 1));       // phases the issuer consumed
     }
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    // epilogue: warp w owns TMEM lanes 32*(w%4)..+31 (= output features), warps 0-3 samples 0-15, 4-7 samples 16-31
+    // epilogue: warp w owns TMEM lanes 32*(w%4)..+31 (= output features) and the EC samples of its warp quad
     {
-        const int n = 32 * (warp & 3) + lane, c0 = (warp >> 2) * 16;
-        float sum[16];
+        constexpr int EC = UPD_ROWS / UPD_WGROUPS;          // 16 (8 warps) or 8 (16 warps)
+        const int n = 32 * (warp & 3) + lane, c0 = (warp >> 2) * EC;
+        float sum[EC];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) sum[j] = 0.f;
+        for (int j = 0; j < EC; ++j) sum[j] = 0.f;
         const int nacc = nkb < TC_NACC ? nkb : TC_NACC;
         // small terms first: lo*hi, then the hi*lo halves, then the hi*hi halves of the accumulators
         for (int t = 0; t < 1 + 2 * nacc; ++t) {
             const uint32_t col = (t == 0) ? 64 * TC_NACC : (t <= nacc ? 64 * (t - 1) + 32 : 64 * (t - 1 - nacc));
+            uint32_t v[EC];
+            tmem_ld<EC>(tmem + ((uint32_t)(32 * (warp & 3)) << 16) + col + c0, v);
+#pragma unroll
+            for (int j = 0; j < EC; ++j) sum[j] += __uint_as_float(v[j]);
+        }
+        if (n < N) {
+            const float bb = __ldg(bias + n);
+#pragma unroll
+            for (int j = 0; j < EC; ++j) {
+                float y = sum[j] + bb;
+                if (TANH) y = tanh_act(y);
+                out[(c0 + j) * ldout + n] = y;
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    return ph;
+}
+
+// ---------------------------------------------------------------------------
+// Tensor-core layers, second generation: the big operand (weights) goes through TENSOR MEMORY.
+//   weights:  global --TMA 2D tile, zero-filled out of bounds--> raw fp32 tile in shared memory
+//             --LDS (thread = TMEM lane), hi/lo split in registers, tcgen05.st--> A_hi | A_lo in tensor memory
+//   samples:  the small operand (32 rows), split into K-major no-swizzle tiles [X_hi | X_lo] in shared memory
+//   MMAs:     per k-step (8 k)  acc[ks] += A_hi x [X_hi | X_lo]  (N = 64: hi*hi | hi*lo), then
+//             acc[ks][32..63] += A_lo x X_hi  (N = 32), four rotating accumulators (the tensor core truncates
+//             when it accumulates; a dependent MMA also costs ~90 cycles, tools/mma_rate.cu)
+// Shared-memory traffic per k-block is 16 KB (TMA) + 16 KB (LDS) + the 32-sample tiles, against 64 KB when both
+// split operands are staged in shared memory; the weight rows never pass through registers of more than one
+// thread.  Warp roles (tools/tc_ts_probe.cu): warps 0-3 transform (warp = TMEM lane quadrant), warps 4-6
+// stage the samples, warp 7 issues TMA refills and MMAs (whole warp, warp-uniform operands, one elected lane:
+// ptxas then keeps the descriptors in uniform registers and emits the MMAs back to back).
+// Barrier rings (initialised once per kernel; `ph` carries one parity bit per barrier, bits 8..19):
+//   raw_full[TS_NS]   TMA tile landed                (count 1 + tx bytes)
+//   a_full[TS_NSA]    A in TMEM and B in smem ready  (count 7: four transform warps + three sample warps)
+//   mma_done[TS_NSA]  MMAs of the stage finished     (tcgen05.commit)
+// ---------------------------------------------------------------------------
+constexpr int TS_NS = 4, TS_NSA = 4;
+constexpr int TS_RAW_BYTES = 128 * TC_KB * 4;               // 16 KB
+constexpr int TS_BT_BYTES = 4 * TC_SBO;                     // one 32-row sample tile (hi or lo)
+constexpr int TS_BYTES = TS_NS * TS_RAW_BYTES + TS_NSA * 2 * TS_BT_BYTES;   // 102 400
+constexpr int TS_TM_A = 256;                                // TMEM: 4 x 64 accumulator columns, then TS_NSA x 64 A columns
+constexpr int TS_BAR0 = 6;                                  // first ring barrier in the barrier array
+constexpr int TS_PH_RAW = 8, TS_PH_AF = 12, TS_PH_MD = 16;  // parity bits in `ph`
+
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+    return pred;
+}
+// D[tmem] (+)= A[tmem] * B[smem descriptor]; whole warp executes it with uniform operands, `elected` picks the lane
+__device__ __forceinline__ void ts_mma(uint32_t d, uint32_t a, uint64_t b, uint32_t idesc, uint32_t acc, uint32_t elected) {
+    asm volatile(
+        "{\n\t.reg .pred p, e;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 e, %5, 0;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(d), "r"(a), "l"(b), "r"(idesc), "r"(acc), "r"(elected) : "memory");
+}
+__device__ __forceinline__ void ts_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_tile_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+                 "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+                 ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                   "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+                   "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+                   "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31]) : "memory");
+}
+// hi = rn_tf32(x); lo = x - hi exactly (<= 13 significant bits): the tensor core truncates it to tf32 (error <= 2^-22 |x|)
+__device__ __forceinline__ void ts_split(float x, uint32_t& hi, uint32_t& lo) {
+    const float h = tc_rn_tf32(x);
+    hi = __float_as_uint(h);
+    lo = __float_as_uint(x - h);
+}
+// the 32 samples' columns [k0, k0+32) of src[32][ld] -> [hi | lo] K-major tiles, by `nthr` threads (t = 0..nthr-1)
+__device__ __forceinline__ void ts_stage_samples(unsigned char* bh, const float* src, int ld, int k0, int K, int t, int nthr) {
+    for (int e = t; e < 8 * UPD_ROWS; e += nthr) {
+        const int m = e >> 3, kc = e & 7, k = k0 + 4 * kc;
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k < K) x = *reinterpret_cast<const float4*>(src + m * ld + k);
+        uint32_t hh[4], ll[4];
+        ts_split(x.x, hh[0], ll[0]); ts_split(x.y, hh[1], ll[1]); ts_split(x.z, hh[2], ll[2]); ts_split(x.w, hh[3], ll[3]);
+        const uint32_t o = tc_off(m, kc);
+        *reinterpret_cast<uint4*>(bh + o) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+        *reinterpret_cast<uint4*>(bh + TS_BT_BYTES + o) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+    }
+}
+// number of uses of ring slot s by blocks 0..n-1 of a ring of size R
+__device__ __forceinline__ int ts_uses(int n, int s, int R) { return (n + R - 1 - s) / R; }
+__device__ __forceinline__ unsigned ts_advance(unsigned ph, int nblocks) {
+#pragma unroll
+    for (int s = 0; s < TS_NS; ++s) ph ^= (unsigned)(ts_uses(nblocks, s, TS_NS) & 1) << (TS_PH_RAW + s);
+#pragma unroll
+    for (int s = 0; s < TS_NSA; ++s) {
+        const unsigned u = (unsigned)(ts_uses(nblocks, s, TS_NSA) & 1);
+        ph ^= (u << (TS_PH_AF + s)) | (u << (TS_PH_MD + s));
+    }
+    return ph;
+}
+
+// forward layer on the tensor cores:  out[m][n] = act(sum_k in[m][k] W[n][k] + b[n]),  N <= 128, K % 4 == 0.
+// wmap: tensor map of W[N][K], box 32 (k) x 128 (n), SWIZZLE_128B.  ts: the TS_BYTES staging region (1024-byte aligned).
+template <bool TANH>
+__device__ __noinline__ unsigned fwd_layer_ts(const CUtensorMap* wmap, const float* __restrict__ bias, int N, int K,
+                                              const float* in, int ldin, float* out, int ldout, unsigned char* ts,
+                                              uint64_t* bars, unsigned ph, uint32_t tmem, uint32_t elected) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nkb = (K + TC_KB - 1) / TC_KB;
+    uint64_t* raw_full = bars + TS_BAR0;
+    uint64_t* a_full = raw_full + TS_NS;
+    uint64_t* mma_done = a_full + TS_NSA;
+    unsigned char* raw = ts;
+    unsigned char* bst = ts + TS_NS * TS_RAW_BYTES;
+    __syncthreads();                                        // previous users of the staging region are done, `in` is complete
+    if (warp < 4) {
+        // ---------------- weight transform: raw tile row -> hi/lo -> tensor memory ----------------
+        const int r = 32 * warp + lane;
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % TS_NS, sa = kb % TS_NSA;
+            mbar_wait(&raw_full[s], ((ph >> (TS_PH_RAW + s)) ^ (unsigned)(kb / TS_NS)) & 1u);
+            if (kb >= TS_NSA) mbar_wait(&mma_done[sa], ((ph >> (TS_PH_MD + sa)) ^ (unsigned)(kb / TS_NSA) ^ 1u) & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const unsigned char* rowp = raw + s * TS_RAW_BYTES + r * 128;
+            uint32_t hi[32], lo[32];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {                   // 128-byte swizzle: chunk c of row r sits at c ^ (r % 8)
+                const float4 x = *reinterpret_cast<const float4*>(rowp + ((c ^ (r & 7)) << 4));
+                ts_split(x.x, hi[4 * c + 0], lo[4 * c + 0]); ts_split(x.y, hi[4 * c + 1], lo[4 * c + 1]);
+                ts_split(x.z, hi[4 * c + 2], lo[4 * c + 2]); ts_split(x.w, hi[4 * c + 3], lo[4 * c + 3]);
+            }
+            const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A + 64 * sa;
+            tmem_st32(ta, hi);
+            tmem_st32(ta + 32, lo);
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&a_full[sa]);
+        }
+    } else if (warp < 7) {
+        // ---------------- sample staging ----------------
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int sa = kb % TS_NSA;
+            if (kb >= TS_NSA) mbar_wait(&mma_done[sa], ((ph >> (TS_PH_MD + sa)) ^ (unsigned)(kb / TS_NSA) ^ 1u) & 1u);
+            ts_stage_samples(bst + sa * 2 * TS_BT_BYTES, in, ldin, kb * TC_KB, K, tid - 128, 96);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&a_full[sa]);
+        }
+    } else {
+        // ---------------- issuer ----------------
+        const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        if (elected)
+            for (int kb = 0; kb < TS_NS && kb < nkb; ++kb) {
+                mbar_expect_tx(&raw_full[kb], TS_RAW_BYTES);
+                tma_tile_2d(raw + kb * TS_RAW_BYTES, wmap, kb * TC_KB, 0, &raw_full[kb]);
+            }
+        constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
+        for (int kb = 0; kb < nkb; ++kb) {
+            const int s = kb % TS_NS, sa = kb % TS_NSA;
+            mbar_wait(&a_full[sa], ((ph >> (TS_PH_AF + sa)) ^ (unsigned)(kb / TS_NSA)) & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t bd = tc_desc(smem_u32(bst + sa * 2 * TS_BT_BYTES));
+            const uint32_t ta = tmem + TS_TM_A + 64 * sa;
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks, ta + 8 * ks, bd + ks * KSTEP, idesc64, kb ? 1u : 0u, elected);
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks + 32, ta + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u, elected);
+            if (elected) {
+                ts_commit(&mma_done[sa]);
+                if (kb + TS_NS < nkb) {                     // a_full(kb) complete: every transform warp has read raw[s]
+                    mbar_expect_tx(&raw_full[s], TS_RAW_BYTES);
+                    tma_tile_2d(raw + s * TS_RAW_BYTES, wmap, (kb + TS_NS) * TC_KB, 0, &raw_full[s]);
+                }
+            }
+            __syncwarp();
+        }
+    }
+    {   // the last commit covers every MMA of the layer
+        const int sl = (nkb - 1) % TS_NSA;
+        mbar_wait(&mma_done[sl], ((ph >> (TS_PH_MD + sl)) ^ (unsigned)((nkb - 1) / TS_NSA)) & 1u);
+    }
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    // epilogue: lane = output feature, this warp's 16 samples; small terms first
+    {
+        const int q = warp & 3, n = 32 * q + lane, c0 = 16 * (warp >> 2);
+        float sum[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) sum[j] = 0.f;
+        const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16) + c0;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
             uint32_t v[16];
-            const uint32_t taddr = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + col + c0;
-            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                         : "r"(taddr));
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            tmem_ld<16>(tb + (t < 4 ? 64 * t + 32 : 64 * (t - 4)), v);
 #pragma unroll
             for (int j = 0; j < 16; ++j) sum[j] += __uint_as_float(v[j]);
         }
@@ -557,14 +780,16 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    return ph;
+    return ts_advance(ph, nkb);
 }
 
 template <bool TANH>
 __device__ __forceinline__ unsigned fwd_layer(const float* __restrict__ W, const float* __restrict__ bias, int N, int K,
                                           const float* in, int ldin, float* out, int ldout, float* stage, int SF,
-                                          uint64_t* bars, unsigned ph, uint32_t tmem) {
+                                          uint64_t* bars, unsigned ph, uint32_t tmem, const CUtensorMap* wmap, uint32_t elected) {
     // wide GEMM-shaped layers go to the tensor cores (tcgen05), the rest stays on the FP32 pipe
+    if (wmap != nullptr && N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0)
+        return fwd_layer_ts<TANH>(wmap, bias, N, K, in, ldin, out, ldout, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
     if (N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0 && SF >= TC_STAGE_FLOATS)
         return fwd_layer_tc<TANH>(W, bias, N, K, in, ldin, out, ldout, stage, SF, bars, ph, tmem);
     // 4*CN columns per warp: 28 fits N = 100 (reference widths) in four blocks, 32 otherwise
@@ -742,8 +967,8 @@ __device__ __noinline__ unsigned dx_layer_t(const float* __restrict__ W, int N, 
 __device__ __forceinline__ unsigned dx_layer(const float* __restrict__ W, int N, int K, const float* dOut, int ldd,
                                          float* act, int lda, float* stage, int SF, uint64_t* bars, unsigned ph) {
     const int KQ = (K + 3) >> 2;
-    if (KQ > 64) return dx_layer_t<4>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
-    if (KQ > 32) return dx_layer_t<2>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
+    if (KQ > UPD_THREADS / 4) return dx_layer_t<4>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
+    if (KQ > UPD_THREADS / 8) return dx_layer_t<2>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
     return dx_layer_t<1>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
 }
 
@@ -1005,18 +1230,14 @@ __device__ __noinline__ unsigned dw_layer_tc(float* __restrict__ gW, float* __re
             for (int t = 0; t < nt; ++t) ph ^= 1u << 4;     // full phases the issuer consumed
         }
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        // epilogue: lane = n; warps 0-3 take columns 0..255 of the group, warps 4-7 columns 256..511
+        // epilogue: lane = n; each warp quad takes an equal share of the group's 512 columns
         {
             const int n = 32 * (warp & 3) + lane;
-            const int cbeg = (warp >> 2) * 256;
-            for (int c0 = cbeg; c0 < cbeg + 256 && c0 < nt * 128; c0 += 16) {
+            constexpr int CW = 512 / UPD_WGROUPS;
+            const int cbeg = (warp >> 2) * CW;
+            for (int c0 = cbeg; c0 < cbeg + CW && c0 < nt * 128; c0 += 16) {
                 uint32_t v[16];
-                const uint32_t taddr = tmem + ((uint32_t)(32 * (warp & 3)) << 16) + c0;
-                asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-                             : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                               "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                             : "r"(taddr));
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                tmem_ld<16>(tmem + ((uint32_t)(32 * (warp & 3)) << 16) + c0, v);
                 const int k0 = 128 * t0 + c0;
                 if (n < N) {
 #pragma unroll
@@ -1082,17 +1303,20 @@ __device__ __noinline__ void heads_dw(float* __restrict__ gWmu, float* __restric
 // whole forward of one network on the tile (model.py:35-45)
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, const UpdArgs& P, float* S, float* mu_out,
-                                            float* v_out, int tick, unsigned ph, uint32_t tmem) {
+                                            float* v_out, int tick, unsigned ph, uint32_t tmem, const CUtensorMap* maps,
+                                            uint32_t elected) {
     const dppo_dims& d = P.d;
     float* stage = S + P.o_stage;
     uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
-    ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, tmem);
+    ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, tmem, nullptr, elected);
     K2_TICK(tick + 0);
-    ph = fwd_layer<true>(nw.W2, nw.b2, d.H2, d.H1, S + P.o_h1, P.ldH1, S + P.o_h2, P.ldH2, stage, P.SF, bars, ph, tmem);
+    ph = fwd_layer<true>(nw.W2, nw.b2, d.H2, d.H1, S + P.o_h1, P.ldH1, S + P.o_h2, P.ldH2, stage, P.SF, bars, ph, tmem,
+                         maps ? maps + 0 : nullptr, elected);
     K2_TICK(tick + 1);
-    ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, tmem);
+    ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, tmem, nullptr, elected);
     K2_TICK(tick + 2);
-    ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph, tmem);
+    ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph, tmem,
+                         maps ? maps + 1 : nullptr, elected);
     K2_TICK(tick + 3);
     heads_fwd(hs, d.A, d.H2, d.G2, S + P.o_h2, P.ldH2, S + P.o_g2, P.ldG2, mu_out, P.ldA, v_out);
     K2_TICK(tick + 4);
@@ -1113,8 +1337,8 @@ __device__ float block_sum(float x, float* red) {
     return r;
 }
 
-__global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdArgs P) {
-    extern __shared__ __align__(16) float S[];
+__global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __grid_constant__ UpdArgs P) {
+    extern __shared__ __align__(1024) float S[];
     const dppo_dims& d = P.d;
     const int TM = P.TM;
     const Net nw = net_of(P.theta, P.lay);
@@ -1130,10 +1354,13 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         mbar_init(&b[3], 1);
         mbar_init(&b[4], UPD_THREADS / 32 - 1);            // tensor-core stages: filled, one arrival per producer warp
         mbar_init(&b[5], UPD_THREADS / 32 - 1);
+        for (int i = 0; i < TS_NS; ++i) mbar_init(&b[TS_BAR0 + i], 1);                       // raw_full
+        for (int i = 0; i < TS_NSA; ++i) mbar_init(&b[TS_BAR0 + TS_NS + i], 7);              // a_full
+        for (int i = 0; i < TS_NSA; ++i) mbar_init(&b[TS_BAR0 + TS_NS + TS_NSA + i], 1);     // mma_done
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     // tensor memory: all 512 columns (one CTA per SM), 9 accumulators of 32 columns are used
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(S + P.o_bars + 12);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(S + P.o_bars + 2 * (TS_BAR0 + TS_NS + 2 * TS_NSA));
     if (threadIdx.x < 32) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
@@ -1142,6 +1369,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot;
+    const uint32_t elected = elect_one();
     unsigned ph = 0;
     // head weights of both networks stay in shared memory for the whole kernel
     // (when shared memory is tight - Humanoid with 256-wide nets - they are read from global memory instead)
@@ -1196,9 +1424,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const UpdA
         const bool same_old = P.flavour == DPPO_FLAVOUR_DPPO && P.theta_old == P.theta;
         if (P.flavour == DPPO_FLAVOUR_DPPO && !same_old) {
             const Net no = net_of(P.theta_old, P.lay);
-            ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem);              // train.py:142
+            ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr, elected);              // train.py:142
         }
-        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem);                    // train.py:145 / ppo.py:148
+        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr, elected);                    // train.py:145 / ppo.py:148
         if (same_old) {
             for (int e = threadIdx.x; e < UPD_ROWS * P.ldA; e += UPD_THREADS) S[P.o_muo + e] = S[P.o_mu + e];
             for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
@@ -1457,7 +1685,7 @@ int plan(UpdArgs& P) {
     P.o_lpo = take(TM);
     P.o_zero_end = o;                           // everything before this is zeroed per tile
     P.o_red = take(UPD_THREADS);
-    P.o_bars = take(16);                        // six mbarriers (8 bytes each) + the TMEM base address
+    P.o_bars = take(2 * (TS_BAR0 + TS_NS + 2 * TS_NSA) + 4);   // the mbarriers (8 bytes each) + the TMEM base address
     P.head_floats = (d.A * P.ldH2 + ((d.A + 3) & ~3) + P.ldG2 + 4 + 3) & ~3;
     // head weights resident in shared memory unless that would squeeze the stage buffers below their
     // minimum (then they are read from global memory, which needs 16-byte aligned rows)
@@ -1465,7 +1693,7 @@ int plan(UpdArgs& P) {
     if ((227 * 1024 / 4 - o - 2 * P.head_floats - 64) / 2 < UPD_STAGE_MIN && (d.H2 & 3) == 0 && (d.G2 & 3) == 0)
         P.heads_in_smem = 0;
     P.o_heads = take(P.heads_in_smem ? 2 * P.head_floats : 4);
-    o = (o + 31) & ~31;                         // 128-byte aligned stage buffers (UMMA descriptors)
+    o = (o + 255) & ~255;                       // 1024-byte aligned stage buffers (UMMA descriptors, TMA swizzle atoms)
     P.o_stage = o;                              // everything before the stage is zeroed per tile
     // two weight staging buffers from what is left of the 227 KB
     int sf = ((227 * 1024 / 4 - o) / 2) & ~127;
@@ -1475,6 +1703,37 @@ int plan(UpdArgs& P) {
     P.smem_floats = o;
     return o;
 }
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+// tensor map of a row-major fp32 matrix W[rows][cols] with a box of box_c x box_r elements
+bool make_wmap(CUtensorMap* map, const float* W, int rows, int cols, int box_c, int box_r, CUtensorMapSwizzle swz) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return false;
+    const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    const cuuint64_t gstr[1] = {(cuuint64_t)cols * 4};
+    const cuuint32_t box[2] = {(cuuint32_t)box_c, (cuuint32_t)box_r};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(W), gdim, gstr, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+bool ts_eligible(int N, int K) { return N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0; }
 
 }  // namespace
 
@@ -1544,6 +1803,19 @@ extern "C" int dppo_update_fused(int flavour, const dppo_dims* d, const float* o
     plan(P);
     const size_t smem = sizeof(float) * (size_t)P.smem_floats;
     if (smem > 227 * 1024 || P.SF < UPD_STAGE_MIN) return DPPO_E_TOOLARGE;
+    // tensor-core path of the wide layers: needs the 100 KB staging region and tensor maps of the weights
+    P.use_ts = 0;
+    if ((size_t)2 * P.SF * sizeof(float) >= (size_t)TS_BYTES && getenv("DPPO_K2_NO_TS") == nullptr) {
+        bool ok = true;
+        for (int net = 0; net < 2 && ok; ++net) {
+            const float* t = net == 0 ? theta : (theta_old ? theta_old : theta);
+            if (ts_eligible(d->H2, d->H1))
+                ok = ok && make_wmap(&P.map_fwd[net][0], t + P.lay.off[3], d->H2, d->H1, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+            if (ts_eligible(d->G2, d->G1))
+                ok = ok && make_wmap(&P.map_fwd[net][1], t + P.lay.off[7], d->G2, d->G1, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+        }
+        P.use_ts = ok ? 1 : 0;
+    }
     static size_t smem_set = 0;
     if (smem > smem_set) {
         DPPO_CUDA_TRY(cudaFuncSetAttribute(update_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -19,5 +19,5 @@ prev=buf[0]
 for i in range(1,26):
     print('%-14s %8d cycles'%(names[i],buf[i]-prev)); prev=buf[i]
 print('total',buf[25]-buf[0])
-for i,nm in ((40,'issuer wait full'),(41,'issuer issue+commit'),(42,'producer wait empty'),(43,'producer split+store'),(44,'producer prefetch issue'),(45,'producer fence.proxy'),(46,'producer arrive')):
-    print('acc40 %-24s %9d cycles (accumulated over launches/layers)'%(nm,buf[i]))
+for i,nm in ((40,'issuer wait full'),(41,'issuer issue+commit'),(42,'producer wait empty'),(43,'producer split+store'),(44,'producer prefetch issue'),(45,'producer fence.proxy'),(46,'producer arrive'),(47,'drain (issuer+producer)')):
+    print('acc40 %-24s %9d cycles total, %7.1f per k-block (120 k-blocks: 3 launches x 2 nets x (4+16))'%(nm,buf[i],buf[i]/120.0))
