@@ -105,7 +105,9 @@ struct UpdArgs {
     int o_zero_end, o_heads, head_floats, o_bars, heads_in_smem;
     // tensor maps of the wide layers' weights (TMA tiles for the tensor-core path); use_ts: maps valid and staging region big enough
     int use_ts;
+    int small_first;                                // first layers (K = O <= 32) run from prefetched flat weight copies
     alignas(64) CUtensorMap map_fwd[2][2];          // [theta, theta_old][W2, V2]: box 32 (k) x 128 (n), SWIZZLE_128B
+    alignas(64) CUtensorMap map_dx[2];              // theta's W2, V2 for dX: box 128 (k) x 32 (n), no swizzle
 };
 
 __device__ __forceinline__ Net net_of(const float* t, const Layout& L) {
@@ -587,6 +589,88 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
 }
 
 // ---------------------------------------------------------------------------
+// First layers (narrow input, K <= 32): out[m][n] = tanh(sum_k in[m][k] W[n][k] + b[n]) with the WHOLE weight
+// matrix already in shared memory, flat [N][K], fetched by a bulk copy that was issued a phase earlier
+// (first_layers_prefetch), so nothing is staged or waited for here.  Lanes are 8 (rows) x 4 (columns); a thread owns
+// rows mi+8i and columns n0+ni+4j; the input row is read as 128-bit vectors, the weights as scalars (rows of K floats
+// are not 16-byte aligned; consecutive columns fall into different banks because K is odd or the rows are short).
+// ---------------------------------------------------------------------------
+template <int CN>
+__device__ __noinline__ void fwd_small_k(const float* Ws, const float* __restrict__ bias, int N, int K, const float* in,
+                                         int ldin, float* out, int ldout) {
+    constexpr int NWARPS = UPD_THREADS / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int mi = lane >> 2, ni = lane & 3;
+    const int K4 = K & ~3;
+    const float* a0 = in + mi * ldin;
+    for (int n0 = warp * 4 * CN; n0 < N; n0 += NWARPS * 4 * CN) {
+        const float* wp[CN];
+#pragma unroll
+        for (int j = 0; j < CN; ++j) wp[j] = Ws + min(n0 + ni + 4 * j, N - 1) * K;   // clamped columns are dropped below
+        float acc[4][CN];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < CN; ++j) acc[i][j] = 0.f;
+        for (int k = 0; k < K4; k += 4) {
+            float4 a[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(a0 + (8 * i) * ldin + k);
+#pragma unroll
+            for (int j = 0; j < CN; ++j) {
+                const float b0 = wp[j][k], b1 = wp[j][k + 1], b2 = wp[j][k + 2], b3 = wp[j][k + 3];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    acc[i][j] = fmaf(a[i].x, b0, acc[i][j]);
+                    acc[i][j] = fmaf(a[i].y, b1, acc[i][j]);
+                    acc[i][j] = fmaf(a[i].z, b2, acc[i][j]);
+                    acc[i][j] = fmaf(a[i].w, b3, acc[i][j]);
+                }
+            }
+        }
+        for (int k = K4; k < K; ++k) {
+            float a[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = a0[(8 * i) * ldin + k];
+#pragma unroll
+            for (int j = 0; j < CN; ++j) {
+                const float b = wp[j][k];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[i][j] = fmaf(a[i], b, acc[i][j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < CN; ++j) {
+            const int n = n0 + ni + 4 * j;
+            if (n < N) {
+                const float bb = __ldg(bias + n);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) out[(mi + 8 * i) * ldout + n] = tanh_act(acc[i][j] + bb);
+            }
+        }
+    }
+    __syncthreads();
+}
+// both first-layer weight matrices of one network -> flat copies in the staging region (W1 at 0, V1 behind it),
+// completion on `bar`; the caller orders this after the last use of the region (block barrier)
+__device__ __forceinline__ int first_v1_offset(const dppo_dims& d) { return (d.H1 * d.O + 3) & ~3; }
+__device__ __forceinline__ void first_layers_prefetch(float* stage, const float* __restrict__ W1, const float* __restrict__ V1,
+                                                      const dppo_dims& d, uint64_t* bar) {
+    const int n1 = d.H1 * d.O, n2 = d.G1 * d.O;
+    float* v1s = stage + first_v1_offset(d);
+    if (threadIdx.x == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the region was last written through the generic proxy
+        mbar_expect_tx(bar, (unsigned)(((n1 & ~3) + (n2 & ~3)) * 4));
+        if (n1 & ~3) bulk_g2s(stage, W1, (unsigned)((n1 & ~3) * 4), bar);
+        if (n2 & ~3) bulk_g2s(v1s, V1, (unsigned)((n2 & ~3) * 4), bar);
+    }
+    if (threadIdx.x == 32) {                                            // tails (visible after the next block barrier)
+        for (int e = n1 & ~3; e < n1; ++e) stage[e] = __ldg(W1 + e);
+        for (int e = n2 & ~3; e < n2; ++e) v1s[e] = __ldg(V1 + e);
+    }
+}
+
+// ---------------------------------------------------------------------------
 // Tensor-core layers, second generation: the big operand (weights) goes through TENSOR MEMORY.
 //   weights:  global --TMA 2D tile, zero-filled out of bounds--> raw fp32 tile in shared memory
 //             --LDS (thread = TMEM lane), hi/lo split in registers, tcgen05.st--> A_hi | A_lo in tensor memory
@@ -964,8 +1048,122 @@ __device__ __noinline__ unsigned dx_layer_t(const float* __restrict__ W, int N, 
     return ph;
 }
 
+// dX through a tanh layer on the tensor cores (same pipeline as fwd_layer_ts, weights transposed on the way into
+// tensor memory):   act[m][k] <- (sum_n dOut[m][n] W[n][k]) (1 - act[m][k]^2)
+//   D[k][m] = A[k][n] . B[m][n]^T,  A = W^T: TMEM lane = k (128 per tile), columns = n (32 per block);
+//   raw tile = W[n0..n0+31][k0..k0+127] (box 128 x 32, no swizzle: thread k reads a column, conflict-free)
+//   B = dOut, K-major over n, split into [hi | lo] tiles per block.
+// The rings run over the global block index g = tile * nnb + block, so the next tile's weights are in flight while
+// a tile drains; only the accumulators are per tile (epilogue between tiles, all eight warps).
+__device__ __noinline__ unsigned dx_layer_ts(const CUtensorMap* xmap, int N, int K, const float* dOut, int ldd, float* act,
+                                             int lda, unsigned char* ts, uint64_t* bars, unsigned ph, uint32_t tmem,
+                                             uint32_t elected) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nnb = (N + TC_KB - 1) / TC_KB, ntiles = (K + 127) >> 7, G = nnb * ntiles;
+    uint64_t* raw_full = bars + TS_BAR0;
+    uint64_t* a_full = raw_full + TS_NS;
+    uint64_t* mma_done = a_full + TS_NSA;
+    unsigned char* raw = ts;
+    unsigned char* bst = ts + TS_NS * TS_RAW_BYTES;
+    __syncthreads();
+    if (warp == 7 && elected)
+        for (int g = 0; g < TS_NS && g < G; ++g) {
+            mbar_expect_tx(&raw_full[g], TS_RAW_BYTES);
+            tma_tile_2d(raw + g * TS_RAW_BYTES, xmap, 128 * (g / nnb), TC_KB * (g % nnb), &raw_full[g]);
+        }
+    for (int mt = 0; mt < ntiles; ++mt) {
+        const int g0 = mt * nnb;
+        if (warp < 4) {
+            const int r = 32 * warp + lane;                 // k within the tile = TMEM lane
+            for (int g = g0; g < g0 + nnb; ++g) {
+                const int s = g % TS_NS, sa = g % TS_NSA;
+                mbar_wait(&raw_full[s], ((ph >> (TS_PH_RAW + s)) ^ (unsigned)(g / TS_NS)) & 1u);
+                if (g >= TS_NSA) mbar_wait(&mma_done[sa], ((ph >> (TS_PH_MD + sa)) ^ (unsigned)(g / TS_NSA) ^ 1u) & 1u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const float* colp = reinterpret_cast<const float*>(raw + s * TS_RAW_BYTES) + r;
+                uint32_t hi[32], lo[32];
+#pragma unroll
+                for (int n = 0; n < 32; ++n) ts_split(colp[n * 128], hi[n], lo[n]);
+                const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A + 64 * sa;
+                tmem_st32(ta, hi);
+                tmem_st32(ta + 32, lo);
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&a_full[sa]);
+            }
+        } else if (warp < 7) {
+            for (int g = g0; g < g0 + nnb; ++g) {
+                const int sa = g % TS_NSA;
+                if (g >= TS_NSA) mbar_wait(&mma_done[sa], ((ph >> (TS_PH_MD + sa)) ^ (unsigned)(g / TS_NSA) ^ 1u) & 1u);
+                ts_stage_samples(bst + sa * 2 * TS_BT_BYTES, dOut, ldd, (g - g0) * TC_KB, N, tid - 128, 96);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&a_full[sa]);
+            }
+        } else {
+            const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+            const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+            constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
+            for (int g = g0; g < g0 + nnb; ++g) {
+                const int s = g % TS_NS, sa = g % TS_NSA;
+                mbar_wait(&a_full[sa], ((ph >> (TS_PH_AF + sa)) ^ (unsigned)(g / TS_NSA)) & 1u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint64_t bd = tc_desc(smem_u32(bst + sa * 2 * TS_BT_BYTES));
+                const uint32_t ta = tmem + TS_TM_A + 64 * sa;
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks, ta + 8 * ks, bd + ks * KSTEP, idesc64, g > g0 ? 1u : 0u, elected);
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks + 32, ta + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u, elected);
+                if (elected) {
+                    ts_commit(&mma_done[sa]);
+                    const int gn = g + TS_NS;
+                    if (gn < G) {
+                        mbar_expect_tx(&raw_full[s], TS_RAW_BYTES);
+                        tma_tile_2d(raw + s * TS_RAW_BYTES, xmap, 128 * (gn / nnb), TC_KB * (gn % nnb), &raw_full[s]);
+                    }
+                }
+                __syncwarp();
+            }
+        }
+        {
+            const int gl = g0 + nnb - 1, sl = gl % TS_NSA;
+            mbar_wait(&mma_done[sl], ((ph >> (TS_PH_MD + sl)) ^ (unsigned)(gl / TS_NSA)) & 1u);
+        }
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        {
+            const int q = warp & 3, k = 128 * mt + 32 * q + lane, c0 = 16 * (warp >> 2);
+            float sum[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) sum[j] = 0.f;
+            const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16) + c0;
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                uint32_t v[16];
+                tmem_ld<16>(tb + (t < 4 ? 64 * t + 32 : 64 * (t - 4)), v);
+#pragma unroll
+                for (int j = 0; j < 16; ++j) sum[j] += __uint_as_float(v[j]);
+            }
+            if (k < K) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    float* ap = act + (c0 + j) * lda + k;
+                    const float h = *ap;
+                    *ap = sum[j] * (1.f - h * h);
+                }
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+    }
+    return ts_advance(ph, G);
+}
+
 __device__ __forceinline__ unsigned dx_layer(const float* __restrict__ W, int N, int K, const float* dOut, int ldd,
-                                         float* act, int lda, float* stage, int SF, uint64_t* bars, unsigned ph) {
+                                         float* act, int lda, float* stage, int SF, uint64_t* bars, unsigned ph,
+                                         const CUtensorMap* xmap, uint32_t tmem, uint32_t elected) {
+    if (xmap != nullptr && N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0)   // = ts_eligible() on the host
+        return dx_layer_ts(xmap, N, K, dOut, ldd, act, lda, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
     const int KQ = (K + 3) >> 2;
     if (KQ > UPD_THREADS / 4) return dx_layer_t<4>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
     if (KQ > UPD_THREADS / 8) return dx_layer_t<2>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
@@ -1302,22 +1500,35 @@ __device__ __noinline__ void heads_dw(float* __restrict__ gWmu, float* __restric
 // ---------------------------------------------------------------------------
 // whole forward of one network on the tile (model.py:35-45)
 // ---------------------------------------------------------------------------
+// `next`: the network whose first layers are prefetched into the staging region while this one's heads run
 __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, const UpdArgs& P, float* S, float* mu_out,
                                             float* v_out, int tick, unsigned ph, uint32_t tmem, const CUtensorMap* maps,
-                                            uint32_t elected) {
+                                            uint32_t elected, const Net* next) {
     const dppo_dims& d = P.d;
     float* stage = S + P.o_stage;
     uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
-    ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, tmem, nullptr, elected);
-    K2_TICK(tick + 0);
+    if (P.small_first) {
+        mbar_wait(&bars[0], ph & 1u);                       // this network's W1 and V1 have landed (prefetched)
+        ph ^= 1u;
+        if (d.H1 <= 128) fwd_small_k<4>(stage, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1);
+        else fwd_small_k<8>(stage, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1);
+        K2_TICK(tick + 0);
+        if (d.G1 <= 128) fwd_small_k<4>(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1);
+        else fwd_small_k<8>(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1);
+        K2_TICK(tick + 1);
+    } else {
+        ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, tmem, nullptr, elected);
+        K2_TICK(tick + 0);
+        ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, tmem, nullptr, elected);
+        K2_TICK(tick + 1);
+    }
     ph = fwd_layer<true>(nw.W2, nw.b2, d.H2, d.H1, S + P.o_h1, P.ldH1, S + P.o_h2, P.ldH2, stage, P.SF, bars, ph, tmem,
                          maps ? maps + 0 : nullptr, elected);
-    K2_TICK(tick + 1);
-    ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, tmem, nullptr, elected);
     K2_TICK(tick + 2);
     ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph, tmem,
                          maps ? maps + 1 : nullptr, elected);
     K2_TICK(tick + 3);
+    if (P.small_first && next != nullptr) first_layers_prefetch(stage, next->W1, next->V1, d, &bars[0]);
     heads_fwd(hs, d.A, d.H2, d.G2, S + P.o_h2, P.ldH2, S + P.o_g2, P.ldG2, mu_out, P.ldA, v_out);
     K2_TICK(tick + 4);
     return ph;
@@ -1398,6 +1609,12 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         K2_TICK(1);
         const int b0 = tile * TM;
         const int valid = min(TM, P.B - b0);
+        const bool same_old = P.flavour == DPPO_FLAVOUR_DPPO && P.theta_old == P.theta;
+        const bool run_old = P.flavour == DPPO_FLAVOUR_DPPO && !same_old;
+        if (P.small_first) {                                 // first layers of the first network to run: in flight during the gather
+            const Net nf = net_of(run_old ? P.theta_old : P.theta, P.lay);
+            first_layers_prefetch(S + P.o_stage, nf.W1, nf.V1, d, reinterpret_cast<uint64_t*>(S + P.o_bars));
+        }
         // ---- zero the activation area (pads must read as 0), then gather --------------------
         for (int i = threadIdx.x; i < P.o_zero_end; i += UPD_THREADS) S[i] = 0.f;
         __syncthreads();
@@ -1421,12 +1638,11 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         // ---- forward(s) -----------------------------------------------------------------------
         // epoch 0 of a cycle: model_old is a copy of model (train.py:128-129), so the caller passes
         // theta_old == theta and the old network's outputs are the new network's, bit for bit
-        const bool same_old = P.flavour == DPPO_FLAVOUR_DPPO && P.theta_old == P.theta;
-        if (P.flavour == DPPO_FLAVOUR_DPPO && !same_old) {
+        if (run_old) {
             const Net no = net_of(P.theta_old, P.lay);
-            ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr, elected);              // train.py:142
+            ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr, elected, &nw);              // train.py:142
         }
-        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr, elected);                    // train.py:145 / ppo.py:148
+        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr, elected, nullptr);                    // train.py:145 / ppo.py:148
         if (same_old) {
             for (int e = threadIdx.x; e < UPD_ROWS * P.ldA; e += UPD_THREADS) S[P.o_muo + e] = S[P.o_mu + e];
             for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
@@ -1579,7 +1795,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         else
             dw_layer(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc);
         K2_TICK(17);
-        ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph);  // h1 <- dz1
+        ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph,
+                      P.use_ts ? &P.map_dx[0] : nullptr, tmem, elected);  // h1 <- dz1
         K2_TICK(18);
         if (d.O <= 24 && d.H1 >= 256 && d.H1 * d.O <= P.SF) dw_layer_smallk(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage);
         else dw_layer(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc);
@@ -1593,7 +1810,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         else
             dw_layer(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc);
         K2_TICK(22);
-        ph = dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph);
+        ph = dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph,
+                      P.use_ts ? &P.map_dx[1] : nullptr, tmem, elected);
         K2_TICK(23);
         if (d.O <= 24 && d.G1 >= 256 && d.G1 * d.O <= P.SF) dw_layer_smallk(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage);
         else dw_layer(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc);
@@ -1701,6 +1919,7 @@ int plan(UpdArgs& P) {
     P.SF = sf;
     o += 2 * (sf > 0 ? sf : 0);
     P.smem_floats = o;
+    P.small_first = (d.O <= 32 && ((d.H1 * d.O + 3) & ~3) + d.G1 * d.O <= 2 * sf) ? 1 : 0;
     return o;
 }
 
@@ -1814,6 +2033,10 @@ extern "C" int dppo_update_fused(int flavour, const dppo_dims* d, const float* o
             if (ts_eligible(d->G2, d->G1))
                 ok = ok && make_wmap(&P.map_fwd[net][1], t + P.lay.off[7], d->G2, d->G1, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
         }
+        if (ts_eligible(d->H2, d->H1))
+            ok = ok && make_wmap(&P.map_dx[0], theta + P.lay.off[3], d->H2, d->H1, 128, TC_KB, CU_TENSOR_MAP_SWIZZLE_NONE);
+        if (ts_eligible(d->G2, d->G1))
+            ok = ok && make_wmap(&P.map_dx[1], theta + P.lay.off[7], d->G2, d->G1, 128, TC_KB, CU_TENSOR_MAP_SWIZZLE_NONE);
         P.use_ts = ok ? 1 : 0;
     }
     static size_t smem_set = 0;

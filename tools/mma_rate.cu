@@ -34,6 +34,69 @@ __device__ __forceinline__ void mma_ts(uint32_t d, uint32_t a, uint64_t b, uint3
         ::"r"(d), "r"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");
 }
 
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+    return pred;
+}
+__device__ __forceinline__ void mma_ts_e(uint32_t d, uint32_t a, uint64_t b, uint32_t idesc, uint32_t acc, uint32_t elected) {
+    asm volatile(
+        "{\n\t.reg .pred p, e;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 e, %5, 0;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(d), "r"(a), "l"(b), "r"(idesc), "r"(acc), "r"(elected) : "memory");
+}
+// K2's k-block, issued by a whole warp with uniform operands (one elected lane): four N = n_main MMAs into rotating
+// accumulators, then (with_cross) four N = 32 MMAs into their upper halves; A from tensor memory
+__global__ void __launch_bounds__(256) mma_rate_uniform_kernel(int nkb, int n_main, int with_cross, long long* out) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    for (int i = tid; i < 24576; i += 256) reinterpret_cast<float*>(smem)[i] = 1.0f;
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = tmem_base_s;
+    const uint64_t bh = make_desc(smem_u32(smem), 0, 144);
+    const uint32_t idm = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n_main >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const uint32_t id32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    if (warp == 7) {
+        const uint32_t el = elect_one();
+        long long t0 = clock64();
+        for (int kb = 0; kb < nkb; ++kb) {
+            const uint32_t ta = tmem + 256 + 64 * (kb & 3);
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) mma_ts_e(tmem + 64 * ks, ta + 8 * ks, bh + ks * 18, idm, kb ? 1u : 0u, el);
+            if (with_cross) {
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) mma_ts_e(tmem + 64 * ks + 32, ta + 32 + 8 * ks, bh + ks * 18, id32, 1u, el);
+            }
+        }
+        long long t1 = clock64();
+        if (el) {
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
+        }
+        unsigned ok = 0;
+        while (!ok)
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(ok) : "r"(smem_u32(&bar)), "r"(0u) : "memory");
+        long long t2 = clock64();
+        if (blockIdx.x == 0 && el) { out[0] = t1 - t0; out[1] = t2 - t0; }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+}
+
 // rotate: main accumulator = k-step (not k-block), cross accumulator alternates; ts: A operand from tensor memory
 __global__ void __launch_bounds__(256) mma_rate_kernel(int mode, int lbo, int nkb, int n_main, int with_cross, int rotate, int ts,
                                                        long long* out) {
@@ -124,6 +187,19 @@ int main() {
         long long h[2];
         cudaMemcpy(h, out, 16, cudaMemcpyDeviceToHost);
         printf("%-62s issue %7.1f  complete %7.1f cycles per k-block (32 k)\n", c.name, (double)h[0] / nkb, (double)h[1] / nkb);
+    }
+    cudaFuncSetAttribute(mma_rate_uniform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    const int ucfg[][2] = {{64, 1}, {64, 0}, {32, 0}, {128, 0}, {256, 0}};
+    for (auto& u : ucfg) {
+        for (int rep = 0; rep < 2; ++rep) {
+            mma_rate_uniform_kernel<<<148, 256, 100 * 1024>>>(nkb, u[0], u[1], out);
+            cudaError_t e = cudaDeviceSynchronize();
+            if (e != cudaSuccess) { printf("uniform: %s\n", cudaGetErrorString(e)); return 1; }
+        }
+        long long h[2];
+        cudaMemcpy(h, out, 16, cudaMemcpyDeviceToHost);
+        printf("uniform issue, TS, 4 x N=%-3d %-22s issue %7.1f  complete %7.1f cycles per k-block (32 k)\n", u[0],
+               u[1] ? "+ 4 x N=32 (K2 block)" : "", (double)h[0] / nkb, (double)h[1] / nkb);
     }
     return 0;
 }

@@ -39,6 +39,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, unsigned parity) {
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
 }
+__device__ __forceinline__ unsigned mbar_test(uint64_t* b, unsigned parity) {
+    unsigned ok;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return ok;
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t* b) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
 }
@@ -105,7 +111,7 @@ __global__ void __launch_bounds__(256, 1) ts_fwd_kernel(const __grid_constant__ 
     }
     if (tid == 0) {
         for (int s = 0; s < NS; ++s) mbar_init(&raw_full[s], 1);
-        for (int s = 0; s < NSA; ++s) { mbar_init(&a_full[s], 7); mbar_init(&mma_done[s], 1); }
+        for (int s = 0; s < NSA; ++s) { mbar_init(&a_full[s], 5); mbar_init(&mma_done[s], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -116,13 +122,18 @@ __global__ void __launch_bounds__(256, 1) ts_fwd_kernel(const __grid_constant__ 
     const int nkb = (K + KB - 1) / KB;
     // the samples live in shared memory, as K2's activations do
     float* xs = reinterpret_cast<float*>(smem + NS * RAW_BYTES + NSA * 2 * BT_BYTES);
-    const int ldx = K + 4;
+    const int ldx = ((K + 3) & ~3) + ((((K + 3) >> 2) & 1) ? 0 : 4);   // odd number of 16-byte units, like K2's activations
     for (int e = tid; e < 32 * K; e += 256) xs[(e / K) * ldx + (e % K)] = X[e];
     __syncthreads();
     const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     long long t0 = clock64();
     long long ta_[6] = {0, 0, 0, 0, 0, 0}, tc_ = t0;
+#ifdef PROBE_TRACE
+#define TR(role, kb, ev) do { if (blockIdx.x == 0 && lane == 0) clocks[64 + ((role) * 32 + (kb)) * 4 + (ev)] = clock64() - t0; } while (0)
+#else
+#define TR(role, kb, ev) do { } while (0)
+#endif
 #ifdef PROBE_TIMING
 #define TACC(i) do { long long t = clock64(); ta_[i] += t - tc_; tc_ = t; } while (0)
 #define TSET() tc_ = clock64()
@@ -132,23 +143,43 @@ __global__ void __launch_bounds__(256, 1) ts_fwd_kernel(const __grid_constant__ 
 #endif
     if (warp < 4) {
         // ---------------- weight transform: raw tile row -> hi/lo -> tensor memory ----------------
+        // software pipelined: the next block's barrier polls and shared-memory loads overlap this block's split
         const int r = 32 * warp + lane;
+        float4 x[8];
+        mbar_wait(&raw_full[0], 0u);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) x[c] = *reinterpret_cast<const float4*>(raw + r * 128 + ((c ^ (r & 7)) << 4));
         for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % NS, sa = kb % NSA;
+            const int sa = kb % NSA, s1 = (kb + 1) % NS;
+            const bool more = kb + 1 < nkb;
+            const unsigned par1 = ((kb + 1) / NS) & 1u, parm = ((kb / NSA) & 1u) ^ 1u;
             TSET();
-            mbar_wait(&raw_full[s], (kb / NS) & 1u);
-            TACC(0);
-            if (kb >= NSA) mbar_wait(&mma_done[sa], ((kb / NSA) & 1u) ^ 1u);
-            TACC(1);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const unsigned char* rowp = raw + s * RAW_BYTES + r * 128;
+            if (warp == 0) TR(0, kb, 0);
+#ifdef PROBE_NO_REFILL
+            unsigned okr = (more && kb + 1 < NS) ? mbar_test(&raw_full[s1], par1) : 1u;
+#else
+            unsigned okr = more ? mbar_test(&raw_full[s1], par1) : 1u;
+#endif
+            unsigned okm = kb >= NSA ? mbar_test(&mma_done[sa], parm) : 1u;
             uint32_t hi[32], lo[32];
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
-                const float4 x = *reinterpret_cast<const float4*>(rowp + ((c ^ (r & 7)) << 4));
-                split(x.x, hi[4 * c + 0], lo[4 * c + 0]); split(x.y, hi[4 * c + 1], lo[4 * c + 1]);
-                split(x.z, hi[4 * c + 2], lo[4 * c + 2]); split(x.w, hi[4 * c + 3], lo[4 * c + 3]);
+                split(x[c].x, hi[4 * c + 0], lo[4 * c + 0]); split(x[c].y, hi[4 * c + 1], lo[4 * c + 1]);
+                split(x[c].z, hi[4 * c + 2], lo[4 * c + 2]); split(x[c].w, hi[4 * c + 3], lo[4 * c + 3]);
             }
+            TACC(3);
+            if (more) {
+                while (!okr) okr = mbar_test(&raw_full[s1], par1);
+                const unsigned char* rowp = raw + s1 * RAW_BYTES + r * 128;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) x[c] = *reinterpret_cast<const float4*>(rowp + ((c ^ (r & 7)) << 4));
+            }
+            TACC(0);
+            if (warp == 0) TR(0, kb, 1);
+            while (!okm) okm = mbar_test(&mma_done[sa], parm);
+            if (warp == 0) TR(0, kb, 2);
+            TACC(1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TM_A + 64 * sa;
             tmem_st32(ta, hi);
             tmem_st32(ta + 32, lo);
@@ -156,34 +187,38 @@ __global__ void __launch_bounds__(256, 1) ts_fwd_kernel(const __grid_constant__ 
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(&a_full[sa]);
-            TACC(2);
+            if (warp == 0) TR(0, kb, 3);
+            TACC(4);
         }
     } else if (warp < 7) {
-        // ---------------- sample staging: activations -> [X_hi | X_lo] K-major tiles ----------------
-        const int t = tid - 128;                                         // 0..95
-        for (int kb = 0; kb < nkb; ++kb) {
+        // ---------------- sample staging: each of the three warps takes every third block ----------------
+        const int kc = lane & 7, m0 = lane >> 3;
+        for (int kb = warp - 4; kb < nkb; kb += 3) {
             const int sa = kb % NSA;
             TSET();
+            TR(1, kb, 0);
             if (kb >= NSA) mbar_wait(&mma_done[sa], ((kb / NSA) & 1u) ^ 1u);
+            TR(1, kb, 1);
             TACC(1);
             unsigned char* bh = bst + sa * 2 * BT_BYTES;
+            const int k = kb * KB + 4 * kc;
+            float4 xv[8];
 #pragma unroll
-            for (int i = 0; i < 3; ++i) {
-                const int e = t + 96 * i;
-                if (e < 256) {
-                    const int m = e >> 3, kc = e & 7, k = kb * KB + 4 * kc;
-                    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (k < K) x = *reinterpret_cast<const float4*>(xs + m * ldx + k);
-                    uint32_t hh[4], ll[4];
-                    split(x.x, hh[0], ll[0]); split(x.y, hh[1], ll[1]); split(x.z, hh[2], ll[2]); split(x.w, hh[3], ll[3]);
-                    const uint32_t o = (m >> 3) * SBO + kc * LBO + (m & 7) * 16;
-                    *reinterpret_cast<uint4*>(bh + o) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
-                    *reinterpret_cast<uint4*>(bh + BT_BYTES + o) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
-                }
+            for (int i = 0; i < 8; ++i)
+                xv[i] = (k < K) ? *reinterpret_cast<const float4*>(xs + (m0 + 4 * i) * ldx + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int m = m0 + 4 * i;
+                uint32_t hh[4], ll[4];
+                split(xv[i].x, hh[0], ll[0]); split(xv[i].y, hh[1], ll[1]); split(xv[i].z, hh[2], ll[2]); split(xv[i].w, hh[3], ll[3]);
+                const uint32_t o = (m >> 3) * SBO + kc * LBO + (m & 7) * 16;
+                *reinterpret_cast<uint4*>(bh + o) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+                *reinterpret_cast<uint4*>(bh + BT_BYTES + o) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(&a_full[sa]);
+            TR(1, kb, 3);
             TACC(2);
         }
     } else {
@@ -196,8 +231,19 @@ __global__ void __launch_bounds__(256, 1) ts_fwd_kernel(const __grid_constant__ 
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb % NS, sa = kb % NSA;
             TSET();
+            TR(2, kb, 0);
             mbar_wait(&a_full[sa], (kb / NSA) & 1u);
+            TR(2, kb, 1);
             TACC(3);
+#ifdef PROBE_NO_REFILL
+            if (false) {
+#else
+            if (elected && kb + NS < nkb) {                              // a_full(kb): everybody has read raw[s], refill it
+#endif
+                mbar_expect_tx(&raw_full[s], RAW_BYTES);
+                tma_2d(raw + s * RAW_BYTES, &wmap, (kb + NS) * KB, 0, &raw_full[s]);
+            }
+            __syncwarp();
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint64_t bd = b_desc(smem_u32(bst + sa * 2 * BT_BYTES));
             const uint32_t ta = tmem + TM_A + 64 * sa;
@@ -208,18 +254,17 @@ __global__ void __launch_bounds__(256, 1) ts_fwd_kernel(const __grid_constant__ 
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks)
                 mma_ts(tmem + TM_MAIN + 64 * ks + 32, ta + 32 + 8 * ks, bd + ks * ((2 * LBO) >> 4), idesc32, 1u, elected);
-            if (elected) {
+            if (elected)
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&mma_done[sa])) : "memory");
-                if (kb + NS < nkb) {                                     // a_full(kb): everybody has read raw[s], refill it
-                    mbar_expect_tx(&raw_full[s], RAW_BYTES);
-                    tma_2d(raw + s * RAW_BYTES, &wmap, (kb + NS) * KB, 0, &raw_full[s]);
-                }
-            }
             __syncwarp();
+            TR(2, kb, 3);
             TACC(4);
         }
     }
-    mbar_wait(&mma_done[(nkb - 1) % NSA], ((nkb - 1) / NSA) & 1u);       // the last commit covers every MMA
+    // the last commit covers every MMA; only the issuer has seen every earlier phase of that barrier (a warp that
+    // skipped phases could pass a parity wait early), so it waits and the others meet it at the block barrier
+    if (warp == 7) mbar_wait(&mma_done[(nkb - 1) % NSA], ((nkb - 1) / NSA) & 1u);
+    __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     long long t1 = clock64();
     // epilogue: lane = weight row, this warp's 16 samples; small terms first
@@ -262,10 +307,10 @@ int main() {
         return 1;
     }
     long long* dclk;
-    cudaMalloc(&dclk, 256);
+    cudaMalloc(&dclk, 8 * (64 + 3 * 32 * 4)); cudaMemset(dclk, 0, 8 * (64 + 3 * 32 * 4));
     const size_t smem = NS * RAW_BYTES + NSA * 2 * BT_BYTES + 32 * 516 * 4 + 1024;
     cudaFuncSetAttribute(ts_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    const int cfg[][2] = {{100, 500}, {100, 100}, {128, 32}, {64, 256}};
+    const int cfg[][2] = {{100, 500}, {100, 100}, {128, 32}, {64, 256}, {100, 288}, {100, 320}, {100, 384}, {100, 416}, {100, 512}};
     for (auto& c : cfg) {
         const int N = c[0], K = c[1];
         std::vector<float> hW((size_t)N * K), hX((size_t)32 * K), hD((size_t)128 * 32);
@@ -285,6 +330,14 @@ int main() {
         CUresult cr = encode(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, dW, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (cr != CUDA_SUCCESS) { printf("encode failed: %d\n", (int)cr); return 1; }
+        if (K == 500)
+            for (int grid : {1, 8, 32, 74}) {
+                for (int rep = 0; rep < 3; ++rep) ts_fwd_kernel<<<grid, 256, smem>>>(map, dX, dD, N, K, dclk);
+                cudaDeviceSynchronize();
+                long long c2[2];
+                cudaMemcpy(c2, dclk, 16, cudaMemcpyDeviceToHost);
+                printf("    grid %3d: k-loop %lld cycles = %.1f per k-block\n", grid, c2[0], (double)c2[0] / c2[1]);
+            }
         for (int rep = 0; rep < 3; ++rep) {
             ts_fwd_kernel<<<148, 256, smem>>>(map, dX, dD, N, K, dclk);
             cudaError_t e = cudaDeviceSynchronize();
@@ -304,7 +357,18 @@ int main() {
             }
         printf("N=%3d K=%3d  max|D-ref| = %.3e (fp32 fma loop %.3e, max|ref| %.2f)   k-loop %lld cycles = %.1f per k-block (%lld blocks)\n",
                N, K, maxerr, maxerr32, maxref, clk[0], (double)clk[0] / clk[1], clk[1]);
-        for (int t = 0; t < 3; ++t) printf("    role %d (0 = A transform, 1 = B staging, 2 = issuer) per k-block: wait raw %.0f, wait mma_done %.0f, stage+arrive %.0f, wait a_full %.0f, issue+tma %.0f\n", t, (double)clk[8 * t + 2] / clk[1], (double)clk[8 * t + 3] / clk[1], (double)clk[8 * t + 4] / clk[1], (double)clk[8 * t + 5] / clk[1], (double)clk[8 * t + 6] / clk[1]);
+#ifdef PROBE_TRACE
+        if (K == 500) {
+            std::vector<long long> tr(64 + 3 * 32 * 4);
+            cudaMemcpy(tr.data(), dclk, tr.size() * 8, cudaMemcpyDeviceToHost);
+            printf("  kb |  A: start split+lds  md-seen arrived |  B: start md-seen arrived |  I: start af-seen committed\n");
+            for (int kb = 0; kb < 16; ++kb) {
+                const long long* a = &tr[64 + (0 * 32 + kb) * 4], *b = &tr[64 + (1 * 32 + kb) * 4], *i = &tr[64 + (2 * 32 + kb) * 4];
+                printf("  %2d | %8lld %8lld %8lld %8lld | %8lld %8lld %8lld | %8lld %8lld %8lld\n", kb, a[0], a[1], a[2], a[3], b[0], b[1], b[3], i[0], i[1], i[3]);
+            }
+        }
+#endif
+        for (int t = 0; t < 3; ++t) printf("    role %d (0 = A transform, 1 = B staging, 2 = issuer) per k-block: [A: wait raw + lds] %.0f, wait mma_done %.0f, [B: stage+arrive] %.0f, [A: polls+split | I: wait a_full] %.0f, [A: st+wait::st+arrive | I: tma+mma+commit] %.0f\n", t, (double)clk[8 * t + 2] / clk[1], (double)clk[8 * t + 3] / clk[1], (double)clk[8 * t + 4] / clk[1], (double)clk[8 * t + 5] / clk[1], (double)clk[8 * t + 6] / clk[1]);
         cudaFree(dW); cudaFree(dX); cudaFree(dD);
     }
     return 0;
