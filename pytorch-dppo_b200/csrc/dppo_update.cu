@@ -31,7 +31,7 @@ __device__ long long g_k2_clock[64];
 #define K2_ACC_DECL long long acc_t0 = 0; long long acc_r[8] = {0, 0, 0, 0, 0, 0, 0, 0}
 #define K2_ACC_T0 acc_t0 = clock64()
 #define K2_ACC(i) do { long long t = clock64(); acc_r[(i) - 40] += t - acc_t0; acc_t0 = t; } while (0)
-#define K2_ACC_FLUSH do { if (blockIdx.x == 0 && (threadIdx.x == 0 || threadIdx.x == 32)) for (int q = 0; q < 8; ++q) g_k2_clock[40 + q] += acc_r[q]; } while (0)
+#define K2_ACC_FLUSH do { if (blockIdx.x == 0 && (threadIdx.x == 0 || threadIdx.x == 224)) for (int q = 0; q < 8; ++q) g_k2_clock[(threadIdx.x ? 48 : 40) + q] += acc_r[q]; } while (0)
 #else
 #define K2_TICK(i) do { } while (0)
 #define K2_ACC_DECL
@@ -105,6 +105,7 @@ struct UpdArgs {
     int o_zero_end, o_heads, head_floats, o_bars, heads_in_smem;
     // tensor maps of the wide layers' weights (TMA tiles for the tensor-core path); use_ts: maps valid and staging region big enough
     int use_ts;
+    int first_ts;                                   // ... and on the tensor cores (small_first, room for the sample tiles)
     int small_first;                                // first layers (K = O <= 32) run from prefetched flat weight copies
     alignas(64) CUtensorMap map_fwd[2][2];          // [theta, theta_old][W2, V2]: box 32 (k) x 128 (n), SWIZZLE_128B
     alignas(64) CUtensorMap map_dx[2];              // theta's W2, V2 for dX: box 128 (k) x 32 (n), no swizzle
@@ -391,6 +392,22 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 }
 
 // tcgen05.ld of NC (8 or 16) consecutive 32-bit columns of this warp's 32 TMEM lanes, waited for
+// tmem_ld_issue only starts the load: several can be in flight before one tmem_ld_wait
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+template <int NC>
+__device__ __forceinline__ void tmem_ld_issue(uint32_t taddr, uint32_t* v) {
+    static_assert(NC == 8 || NC == 16, "tmem_ld: 8 or 16 columns");
+    if constexpr (NC == 16) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                     : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                       "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                     : "r"(taddr));
+    } else {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                     : "r"(taddr));
+    }
+}
 template <int NC>
 __device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[NC]) {
     static_assert(NC == 8 || NC == 16, "tmem_ld: 8 or 16 columns");
@@ -426,7 +443,6 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
     __syncthreads();                                        // previous users of the stage buffers are done
     if (warp == 0) {
         // ---------------- MMA issuer ----------------
-        K2_ACC_DECL;
         // descriptors of the four operand tiles of both stages, built once: inside the loop a k-step only
         // adds a constant to the start-address field (one thread issues everything, so every instruction
         // in this loop is on the critical path)
@@ -444,10 +460,8 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
         const uint32_t idesc64 = (idesc & ~(0x3fu << 17)) | ((uint32_t)(64 >> 3) << 17);
         for (int kb = 0; kb < nkb; ++kb) {
             const int s = kb & 1;
-            K2_ACC_T0;
             mbar_wait(&full[s], (ph >> (4 + s)) & 1u);
             ph ^= 1u << (4 + s);
-            K2_ACC(40);
             if (lane == 0) {
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 // B_hi and B_lo tiles are adjacent, so ONE N = 64 MMA with A_hi produces hi*hi (columns
@@ -466,23 +480,18 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
                              : "memory");
             }
             __syncwarp();
-            K2_ACC(41);
         }
         // bring the issuer's view of the empty barriers up to date (phases the producers consumed in the
         // loop), then wait for the last commit of each stage like everybody else: `ph` ends up uniform
         for (int kb = 2; kb < nkb; ++kb) ph ^= 1u << (2 + (kb & 1));
-        K2_ACC_T0;
         for (int kb = (nkb > 2 ? nkb - 2 : 0); kb < nkb; ++kb) {
             const int s = kb & 1;
             mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
             ph ^= 1u << (2 + s);
         }
-        K2_ACC(47);
-        K2_ACC_FLUSH;
     } else {
         // ---------------- producers ----------------
         const int pt = tid - 32;                            // 0..223
-        K2_ACC_DECL;
         constexpr int NCH = (1024 + TC_PRODUCERS - 1) / TC_PRODUCERS;     // A chunks per producer (5)
         // per-thread constants of the staging loop: source pointer and tile offset of each chunk
         const float* gp[NCH];
@@ -514,12 +523,10 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
             float4 (&pre)[NCH] = (kb & 1) ? preB : preA;
             char* base = reinterpret_cast<char*>(stage + (size_t)s * SF);
             char *Ah = base, *Al = base + TC_A_BYTES, *Bh = base + 2 * TC_A_BYTES, *Bl = Bh + TC_B_BYTES;
-            K2_ACC_T0;
             if (kb >= 2) {                                  // the MMAs of k-block kb-2 have read this stage
                 mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
                 ph ^= 1u << (2 + s);
             }
-            K2_ACC(42);
 #pragma unroll
             for (int i = 0; i < NCH; ++i) {
                 if (i < NCH - 1 || pt + TC_PRODUCERS * i < 1024) {
@@ -536,24 +543,17 @@ __device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const
                 const float4 x = (k < K) ? *reinterpret_cast<const float4*>(in + m * ldin + k) : make_float4(0.f, 0.f, 0.f, 0.f);
                 tc_store_split(Bh, Bl, m, bkc, x);
             }
-            K2_ACC(43);
             if (kb + 2 < nkb) prefetch(pre, kb + 2);        // lands while the next block is staged
-            K2_ACC(44);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> tensor-core reads
-            K2_ACC(45);
             __syncwarp();
             if (lane == 0) mbar_arrive(&full[s]);           // one arrival per producer warp
-            K2_ACC(46);
         }
         // drain: wait for the last commits (they cover every MMA issued), keeps `ph` equal to the issuer's
-        K2_ACC_T0;
         for (int kb = (nkb > 2 ? nkb - 2 : 0); kb < nkb; ++kb) {
             const int s = kb & 1;
             mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
             ph ^= 1u << (2 + s);
         }
-        K2_ACC(47);
-        K2_ACC_FLUSH;
         for (int kb = 0; kb < nkb; ++kb) ph ^= 1u << (4 + (kb & 1));       // phases the issuer consumed
     }
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -768,6 +768,8 @@ __device__ __noinline__ unsigned fwd_layer_ts(const CUtensorMap* wmap, const flo
     uint64_t* mma_done = a_full + TS_NSA;
     unsigned char* raw = ts;
     unsigned char* bst = ts + TS_NS * TS_RAW_BYTES;
+    const int n_epi = 32 * (warp & 3) + lane;               // my output feature in the epilogue: its bias is fetched now
+    const float bb = n_epi < N ? __ldg(bias + n_epi) : 0.f;
     __syncthreads();                                        // previous users of the staging region are done, `in` is complete
     if (warp < 4) {
         // ---------------- weight transform: raw tile row -> hi/lo -> tensor memory ----------------
@@ -846,14 +848,17 @@ __device__ __noinline__ unsigned fwd_layer_ts(const CUtensorMap* wmap, const flo
         for (int j = 0; j < 16; ++j) sum[j] = 0.f;
         const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16) + c0;
 #pragma unroll
-        for (int t = 0; t < 8; ++t) {
-            uint32_t v[16];
-            tmem_ld<16>(tb + (t < 4 ? 64 * t + 32 : 64 * (t - 4)), v);
+        for (int hf = 0; hf < 2; ++hf) {                    // the four small halves first, then the four hi*hi halves
+            uint32_t v[4][16];
 #pragma unroll
-            for (int j = 0; j < 16; ++j) sum[j] += __uint_as_float(v[j]);
+            for (int t = 0; t < 4; ++t) tmem_ld_issue<16>(tb + 64 * t + (hf ? 0 : 32), v[t]);
+            tmem_ld_wait();
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+#pragma unroll
+                for (int j = 0; j < 16; ++j) sum[j] += __uint_as_float(v[t][j]);
         }
         if (n < N) {
-            const float bb = __ldg(bias + n);
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
                 float y = sum[j] + bb;
@@ -865,6 +870,187 @@ __device__ __noinline__ unsigned fwd_layer_ts(const CUtensorMap* wmap, const flo
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     return ts_advance(ph, nkb);
+}
+
+// ---------------------------------------------------------------------------
+// First layers (K = O <= 32 inputs) on the tensor cores.  Up to four tiles of 128 output features are transformed
+// into tensor memory at once (4 x 64 A columns next to 4 x 64 accumulator columns), so there is no pipeline: stage,
+// one block barrier, all MMAs, one commit, epilogue.  The weights come from the flat copy in shared memory that
+// first_layers_prefetch fetched a phase earlier; the samples' tiles live behind those copies in the staging region.
+//   forward  D[n][m] = W[n][:] . x[m][:]        A = W rows (lane = n, columns = k),   B = x       [hi | lo], K-major over k
+//   dW       D[n][k] = dOut[:][n] . x[:][k]     A = dOut^T (lane = n, columns = s),   B = x^T     [hi | lo], K-major over s
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ unsigned char* first_b_tiles(float* stage, const dppo_dims& d) {
+    const int floats = (first_v1_offset(d) + d.G1 * d.O + 31) & ~31;
+    return reinterpret_cast<unsigned char*>(stage + floats);
+}
+__device__ __noinline__ unsigned fwd_first_ts(const float* Ws, const float* __restrict__ bias, int N, int K, const float* in,
+                                              int ldin, float* out, int ldout, unsigned char* bt, uint64_t* bars, unsigned ph,
+                                              uint32_t tmem, uint32_t elected) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ntiles = (N + 127) >> 7, nks = (K + 7) >> 3;
+    uint64_t* mma_done = bars + TS_BAR0 + TS_NS + TS_NSA;
+    float bb[4];                                            // biases of my output feature in each tile: fetched now, used in the epilogue
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int n = 128 * t + 32 * (warp & 3) + lane;
+        bb[t] = n < N ? __ldg(bias + n) : 0.f;
+    }
+    // ---- B: the samples, one 16-byte chunk per thread ----
+    ts_stage_samples(bt, in, ldin, 0, K, tid, UPD_THREADS);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    // ---- A: weight rows -> tensor memory, all tiles ----
+    if (warp < 4) {
+        for (int t = 0; t < ntiles; ++t) {
+            const int n = 128 * t + 32 * warp + lane;
+            const float* wr = Ws + min(n, N - 1) * K;
+            uint32_t hi[32], lo[32];
+#pragma unroll
+            for (int k = 0; k < 32; ++k) ts_split((n < N && k < K) ? wr[k] : 0.f, hi[k], lo[k]);
+            const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A + 64 * t;
+            tmem_st32(ta, hi);
+            tmem_st32(ta + 32, lo);
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 7) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint64_t bd = tc_desc(smem_u32(bt));
+        constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
+        for (int t = 0; t < ntiles; ++t)
+            for (int ks = 0; ks < nks; ++ks)
+                ts_mma(tmem + 64 * t, tmem + TS_TM_A + 64 * t + 8 * ks, bd + ks * KSTEP, idesc64, ks ? 1u : 0u, elected);
+        for (int t = 0; t < ntiles; ++t)
+            for (int ks = 0; ks < nks; ++ks)
+                ts_mma(tmem + 64 * t + 32, tmem + TS_TM_A + 64 * t + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u, elected);
+        if (elected) ts_commit(&mma_done[0]);
+        __syncwarp();
+    }
+    mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);
+    ph ^= 1u << TS_PH_MD;
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    {
+        const int q = warp & 3, c0 = 16 * (warp >> 2);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            if (t >= ntiles) break;
+            const int n = 128 * t + 32 * q + lane;
+            uint32_t v[2][16];
+            const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16) + 64 * t + c0;
+            tmem_ld_issue<16>(tb + 32, v[0]);
+            tmem_ld_issue<16>(tb, v[1]);
+            tmem_ld_wait();
+            if (n < N) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    out[(c0 + j) * ldout + n] = tanh_act((__uint_as_float(v[0][j]) + __uint_as_float(v[1][j])) + bb[t]);
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    return ph;
+}
+
+// dW / db of a first layer (see above).  img: N*K floats of shared memory (the flat image is flushed coalesced).
+__device__ __noinline__ unsigned dw_first_ts(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut,
+                                             int ldd, const float* in, int ldin, bool accumulate, float* img, unsigned char* bt,
+                                             uint64_t* bars, unsigned ph, uint32_t tmem, uint32_t elected) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ntiles = (N + 127) >> 7;
+    uint64_t* mma_done = bars + TS_BAR0 + TS_NS + TS_NSA;
+    __syncthreads();                                        // staging region free, dOut complete
+    // ---- B = x^T: row k (< 32), chunk kc = samples 4kc..4kc+3 ----
+    {
+        const int k = tid & 31, kc = tid >> 5;              // 256 chunks, one per thread
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k < K) {
+            const float* p = in + (4 * kc) * ldin + k;
+            x = make_float4(p[0], p[ldin], p[2 * ldin], p[3 * ldin]);
+        }
+        uint32_t hh[4], ll[4];
+        ts_split(x.x, hh[0], ll[0]); ts_split(x.y, hh[1], ll[1]); ts_split(x.z, hh[2], ll[2]); ts_split(x.w, hh[3], ll[3]);
+        const uint32_t o = tc_off(k, kc);
+        *reinterpret_cast<uint4*>(bt + o) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+        *reinterpret_cast<uint4*>(bt + TS_BT_BYTES + o) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (warp < 4) {
+        for (int t = 0; t < ntiles; ++t) {
+            const int n = 128 * t + 32 * warp + lane;
+            const float* cp = dOut + min(n, N - 1);
+            uint32_t hi[32], lo[32];
+#pragma unroll
+            for (int sidx = 0; sidx < 32; ++sidx) ts_split(n < N ? cp[sidx * ldd] : 0.f, hi[sidx], lo[sidx]);
+            const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A + 64 * t;
+            tmem_st32(ta, hi);
+            tmem_st32(ta + 32, lo);
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 7) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint64_t bd = tc_desc(smem_u32(bt));
+        constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
+        for (int t = 0; t < ntiles; ++t)
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks)
+                ts_mma(tmem + 64 * t, tmem + TS_TM_A + 64 * t + 8 * ks, bd + ks * KSTEP, idesc64, ks ? 1u : 0u, elected);
+        for (int t = 0; t < ntiles; ++t)
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks)
+                ts_mma(tmem + 64 * t + 32, tmem + TS_TM_A + 64 * t + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u, elected);
+        if (elected) ts_commit(&mma_done[0]);
+        __syncwarp();
+    }
+    mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);
+    ph ^= 1u << TS_PH_MD;
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    {
+        const int q = warp & 3, c0 = 16 * (warp >> 2);      // this warp's 16 of the 32 k columns
+        for (int t = 0; t < ntiles; ++t) {
+            const int n = 128 * t + 32 * q + lane;
+            uint32_t v[2][16];
+            const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16) + 64 * t + c0;
+            tmem_ld_issue<16>(tb + 32, v[0]);
+            tmem_ld_issue<16>(tb, v[1]);
+            tmem_ld_wait();
+            if (n < N) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    if (c0 + j < K) img[n * K + c0 + j] = __uint_as_float(v[0][j]) + __uint_as_float(v[1][j]);
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    const int tot = N * K;
+    if ((tot & 3) == 0) {
+        float4* g4 = reinterpret_cast<float4*>(gW);
+        const float4* s4 = reinterpret_cast<const float4*>(img);
+        for (int e = tid; e < (tot >> 2); e += UPD_THREADS) {
+            float4 o = s4[e];
+            if (accumulate) { const float4 p4 = g4[e]; o.x += p4.x; o.y += p4.y; o.z += p4.z; o.w += p4.w; }
+            g4[e] = o;
+        }
+    } else {
+        for (int e = tid; e < tot; e += UPD_THREADS) gW[e] = accumulate ? gW[e] + img[e] : img[e];
+    }
+    for (int n = tid; n < N; n += UPD_THREADS) {
+        float sb = 0.f;
+        for (int m = 0; m < 32; ++m) sb += dOut[m * ldd + n];
+        gb[n] = accumulate ? gb[n] + sb : sb;
+    }
+    __syncthreads();
+    return ph;
 }
 
 template <bool TANH>
@@ -1138,11 +1324,15 @@ __device__ __noinline__ unsigned dx_layer_ts(const CUtensorMap* xmap, int N, int
             for (int j = 0; j < 16; ++j) sum[j] = 0.f;
             const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16) + c0;
 #pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                uint32_t v[16];
-                tmem_ld<16>(tb + (t < 4 ? 64 * t + 32 : 64 * (t - 4)), v);
+            for (int hf = 0; hf < 2; ++hf) {
+                uint32_t v[4][16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) sum[j] += __uint_as_float(v[j]);
+                for (int t = 0; t < 4; ++t) tmem_ld_issue<16>(tb + 64 * t + (hf ? 0 : 32), v[t]);
+                tmem_ld_wait();
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) sum[j] += __uint_as_float(v[t][j]);
             }
             if (k < K) {
 #pragma unroll
@@ -1464,6 +1654,124 @@ __device__ __noinline__ unsigned dw_layer_tc(float* __restrict__ gW, float* __re
 }
 
 
+// dW of a wide layer on the tensor cores, operands through tensor memory:
+//   dW[n][k] (+)= sum_s dOut[s][n] in[s][k]      D[k][n] = A[k][s] . B[n][s]^T  per tile of 128 k
+//   A = in^T: TMEM lane = k, columns = the 32 samples (read down a column of the activations, conflict-free)
+//   B = dOut^T as [hi rows 0..Np-1 | lo rows Np..2Np-1] K-major tiles (Np = N rounded up to 16), staged once
+//   MMAs per k-step: D[:, 0..2Np) += A_hi x [B_hi | B_lo]  (N = 2 Np),  D[:, Np..2Np) += A_lo x B_hi  (N = Np)
+// Only 4 k-steps per tile, so one accumulator is accurate.  The epilogue has lane = k: for a fixed n a warp writes
+// 128 contiguous bytes of the partial.  Tiles are processed one after the other (transform, MMA, epilogue); the
+// epilogue - 2 Np columns of tensor memory and N x 128 floats to global memory - dominates.
+__device__ __noinline__ unsigned dw_layer_ts(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut,
+                                             int ldd, const float* in, int ldin, bool accumulate, unsigned char* ts,
+                                             uint64_t* bars, unsigned ph, uint32_t tmem, uint32_t elected) {
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int Np = (N + 15) & ~15;
+    const int ntiles = (K + 127) >> 7;
+    uint64_t* mma_done = bars + TS_BAR0 + TS_NS + TS_NSA;
+    __syncthreads();                                        // staging region free, dOut / in complete
+    K2_ACC_DECL;
+    K2_ACC_T0;
+    // ---- B: dOut^T, split, once ----
+    for (int e = tid; e < Np * 8; e += UPD_THREADS) {
+        const int n = e % Np, kc = e / Np;                  // consecutive threads -> consecutive n
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (n < N) {
+            const float* p = dOut + (4 * kc) * ldd + n;
+            x = make_float4(p[0], p[ldd], p[2 * ldd], p[3 * ldd]);
+        }
+        uint32_t hh[4], ll[4];
+        ts_split(x.x, hh[0], ll[0]); ts_split(x.y, hh[1], ll[1]); ts_split(x.z, hh[2], ll[2]); ts_split(x.w, hh[3], ll[3]);
+        *reinterpret_cast<uint4*>(ts + tc_off(n, kc)) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+        *reinterpret_cast<uint4*>(ts + tc_off(Np + n, kc)) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    K2_ACC(40);
+    const uint32_t idm = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)((2 * Np) >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const uint32_t idc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(Np >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const uint64_t bd = tc_desc(smem_u32(ts));
+    constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
+    for (int t = 0; t < ntiles; ++t) {
+        if (warp < 4) {                                     // ---- A: 32 samples of my activation column ----
+            const int k = 128 * t + 32 * warp + lane;
+            uint32_t hi[32], lo[32];
+            const float* cp = in + min(k, K - 1);
+#pragma unroll
+            for (int sidx = 0; sidx < 32; ++sidx) ts_split(k < K ? cp[sidx * ldin] : 0.f, hi[sidx], lo[sidx]);
+            const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A;
+            tmem_st32(ta, hi);
+            tmem_st32(ta + 32, lo);
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        }
+        K2_ACC(41);
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        K2_ACC(42);
+        if (warp == 7) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem, tmem + TS_TM_A + 8 * ks, bd + ks * KSTEP, idm, ks ? 1u : 0u, elected);
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + Np, tmem + TS_TM_A + 32 + 8 * ks, bd + ks * KSTEP, idc, 1u, elected);
+            if (elected) ts_commit(&mma_done[0]);
+            __syncwarp();
+        }
+        mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);     // every thread sees every phase of this barrier
+        ph ^= 1u << TS_PH_MD;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        K2_ACC(43);
+        {
+            const int q = warp & 3, k = 128 * t + 32 * q + lane;
+            const int nh = Np >> 1, n0 = (warp >> 2) * nh;  // this warp's half of the columns
+            const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16);
+            for (int c = 0; c < nh; c += 32) {              // up to 32 columns of both halves in flight, one wait
+                uint32_t v1[32], v2[32];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (c + 8 * i < nh) {
+                        tmem_ld_issue<8>(tb + n0 + c + 8 * i, v1 + 8 * i);
+                        tmem_ld_issue<8>(tb + Np + n0 + c + 8 * i, v2 + 8 * i);
+                    }
+                tmem_ld_wait();
+                // straight-line stores: one running pointer, the column limit as a predicate (a branch per element
+                // costs more than the store here)
+                const int lim = min(nh - c, N - n0 - c);
+                if (k < K && lim > 0) {
+                    float* dst = gW + (size_t)(n0 + c) * K + k;
+                    if (!accumulate) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float o = __uint_as_float(v2[j]) + __uint_as_float(v1[j]);
+                            if (j < lim) *dst = o;
+                            dst += K;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float o = __uint_as_float(v2[j]) + __uint_as_float(v1[j]);
+                            if (j < lim) *dst += o;
+                            dst += K;
+                        }
+                    }
+                }
+            }
+        }
+        K2_ACC(44);
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();                                    // accumulator and A columns free for the next tile
+        K2_ACC(45);
+    }
+    for (int n = tid; n < N; n += UPD_THREADS) {
+        float sb = 0.f;
+        for (int m = 0; m < 32; ++m) sb += dOut[m * ldd + n];
+        gb[n] = accumulate ? gb[n] + sb : sb;
+    }
+    K2_ACC(46);
+    K2_ACC_FLUSH;
+    __syncthreads();
+    return ph;
+}
+
 // dW / db of both heads in one pass, one thread per output element (A*H2 + G2 weights, A + 1 biases):
 //   dWmu[n][k] = sum_s dmu[s][n] h2[s][k],   dWv[k] = sum_s dv[s] g2[s][k]    (s ascending: fixed order)
 __device__ __noinline__ void heads_dw(float* __restrict__ gWmu, float* __restrict__ gbmu, float* __restrict__ gWv,
@@ -1510,10 +1818,14 @@ __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, 
     if (P.small_first) {
         mbar_wait(&bars[0], ph & 1u);                       // this network's W1 and V1 have landed (prefetched)
         ph ^= 1u;
-        if (d.H1 <= 128) fwd_small_k<4>(stage, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1);
+        if (P.first_ts && d.H1 <= 512)
+            ph = fwd_first_ts(stage, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, first_b_tiles(stage, d), bars, ph, tmem, elected);
+        else if (d.H1 <= 128) fwd_small_k<4>(stage, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1);
         else fwd_small_k<8>(stage, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1);
         K2_TICK(tick + 0);
-        if (d.G1 <= 128) fwd_small_k<4>(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1);
+        if (P.first_ts && d.G1 <= 512)
+            ph = fwd_first_ts(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, first_b_tiles(stage, d), bars, ph, tmem, elected);
+        else if (d.G1 <= 128) fwd_small_k<4>(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1);
         else fwd_small_k<8>(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1);
         K2_TICK(tick + 1);
     } else {
@@ -1790,7 +2102,10 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         K2_TICK(15);
         head_dx(hs_new.Wmu, hs_new.ldw, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2);          // h2 <- dz2
         K2_TICK(16);
-        if (d.H2 <= 128 && d.H2 >= 32 && d.H1 >= 64 && (d.H1 & 3) == 0 && P.SF >= TC_STAGE_FLOATS)
+        if (P.use_ts && d.H2 <= 128 && d.H2 >= 32 && d.H1 >= 64 && (d.H1 & 3) == 0)
+            ph = dw_layer_ts(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc,
+                             reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
+        else if (d.H2 <= 128 && d.H2 >= 32 && d.H1 >= 64 && (d.H1 & 3) == 0 && P.SF >= TC_STAGE_FLOATS)
             ph = dw_layer_tc(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc, stage, P.SF, bars, ph, tmem);
         else
             dw_layer(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc);
@@ -1798,14 +2113,19 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph,
                       P.use_ts ? &P.map_dx[0] : nullptr, tmem, elected);  // h1 <- dz1
         K2_TICK(18);
-        if (d.O <= 24 && d.H1 >= 256 && d.H1 * d.O <= P.SF) dw_layer_smallk(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage);
+        if (P.first_ts && d.H1 <= 512)
+            ph = dw_first_ts(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem, elected);
+        else if (d.O <= 24 && d.H1 >= 256 && d.H1 * d.O <= P.SF) dw_layer_smallk(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage);
         else dw_layer(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc);
         K2_TICK(19);
         // ---- backward, value trunk --------------------------------------------------------------
         K2_TICK(20);
         head_dx(hs_new.Wv, 0, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);
         K2_TICK(21);
-        if (d.G2 <= 128 && d.G2 >= 32 && d.G1 >= 64 && (d.G1 & 3) == 0 && P.SF >= TC_STAGE_FLOATS)
+        if (P.use_ts && d.G2 <= 128 && d.G2 >= 32 && d.G1 >= 64 && (d.G1 & 3) == 0)
+            ph = dw_layer_ts(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc,
+                             reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
+        else if (d.G2 <= 128 && d.G2 >= 32 && d.G1 >= 64 && (d.G1 & 3) == 0 && P.SF >= TC_STAGE_FLOATS)
             ph = dw_layer_tc(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc, stage, P.SF, bars, ph, tmem);
         else
             dw_layer(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc);
@@ -1813,7 +2133,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         ph = dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph,
                       P.use_ts ? &P.map_dx[1] : nullptr, tmem, elected);
         K2_TICK(23);
-        if (d.O <= 24 && d.G1 >= 256 && d.G1 * d.O <= P.SF) dw_layer_smallk(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage);
+        if (P.first_ts && d.G1 <= 512)
+            ph = dw_first_ts(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem, elected);
+        else if (d.O <= 24 && d.G1 >= 256 && d.G1 * d.O <= P.SF) dw_layer_smallk(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage);
         else dw_layer(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc);
         K2_TICK(24);
     }
@@ -1920,6 +2242,8 @@ int plan(UpdArgs& P) {
     o += 2 * (sf > 0 ? sf : 0);
     P.smem_floats = o;
     P.small_first = (d.O <= 32 && ((d.H1 * d.O + 3) & ~3) + d.G1 * d.O <= 2 * sf) ? 1 : 0;
+    P.first_ts = (P.small_first && ((((d.H1 * d.O + 3) & ~3) + d.G1 * d.O + 31) & ~31) + 2 * TS_BT_BYTES / 4 <= 2 * sf &&
+                  getenv("DPPO_K2_NO_TS") == nullptr) ? 1 : 0;
     return o;
 }
 

@@ -19,5 +19,5 @@ prev=buf[0]
 for i in range(1,26):
     print('%-14s %8d cycles'%(names[i],buf[i]-prev)); prev=buf[i]
 print('total',buf[25]-buf[0])
-for i,nm in ((40,'issuer wait full'),(41,'issuer issue+commit'),(42,'producer wait empty'),(43,'producer split+store'),(44,'producer prefetch issue'),(45,'producer fence.proxy'),(46,'producer arrive'),(47,'drain (issuer+producer)')):
-    print('acc40 %-24s %9d cycles total, %7.1f per k-block (120 k-blocks: 3 launches x 2 nets x (4+16))'%(nm,buf[i],buf[i]/120.0))
+for i,nm in ((40,'dW ts: B stage'),(41,'dW ts: A transform'),(42,'dW ts: block barrier'),(43,'dW ts: MMAs (wait)'),(44,'dW ts: epilogue'),(45,'dW ts: end-of-tile barrier'),(46,'dW ts: db')):
+    print('acc %-26s per tile (3 launches x 5 tiles): thread 0 %7.1f   thread 224 (issuer warp) %7.1f'%(nm,buf[i]/15.0,buf[i+8]/15.0))
