@@ -39,6 +39,12 @@ __device__ long long g_k2_clock[64];
 #define K2_ACC(i) do { } while (0)
 #define K2_ACC_FLUSH do { } while (0)
 #endif
+#ifdef DPPO_K2_TRACE
+__device__ long long g_k2_trace[4 * 64 * 8];
+#define K2_TR(role, gp, ev) do { if (trace_on && lane == 0) g_k2_trace[(((role) * 64 + (gp)) << 3) + (ev)] = clock64() - trace_t0; } while (0)
+#else
+#define K2_TR(role, gp, ev) do { } while (0)
+#endif
 
 namespace {
 
@@ -702,14 +708,30 @@ __device__ __forceinline__ uint32_t elect_one() {
     return pred;
 }
 // D[tmem] (+)= A[tmem] * B[smem descriptor]; whole warp executes it with uniform operands, `elected` picks the lane
-__device__ __forceinline__ void ts_mma(uint32_t d, uint32_t a, uint64_t b, uint32_t idesc, uint32_t acc, uint32_t elected) {
+__device__ __forceinline__ void ts_mma(uint32_t d, uint32_t a, uint64_t b, uint32_t idesc, uint32_t acc, uint32_t enable) {
+    // executed by a whole converged warp with warp-uniform operands; elect.sync sits next to the MMA so that ptxas sees
+    // a single issuing lane (a predicate that arrives from elsewhere makes it wrap the MMA in a per-thread loop)
     asm volatile(
-        "{\n\t.reg .pred p, e;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 e, %5, 0;\n\t"
+        "{\n\t.reg .pred p, e, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\tand.pred e, e, q;\n\t"
         "@e tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
-        ::"r"(d), "r"(a), "l"(b), "r"(idesc), "r"(acc), "r"(elected) : "memory");
+        ::"r"(d), "r"(a), "l"(b), "r"(idesc), "r"(acc), "r"(enable) : "memory");
 }
+// whole converged warp; one elected lane commits (no divergent branch in the issuing warp)
 __device__ __forceinline__ void ts_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+    asm volatile("{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+                 "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
+// whole converged warp: one elected lane arms `bar` with the byte count and issues one or two 2D tile loads
+// (the second one when `two` is non-zero): a raw tile pair of the wide-layer pipeline
+__device__ __forceinline__ void tma_pair_elect(uint32_t dst0, uint32_t dst1, const CUtensorMap* map, int a0, int b0, int a1, int b1,
+                                               uint32_t bar, uint32_t bytes, uint32_t two) {
+    asm volatile(
+        "{\n\t.reg .pred e, t;\n\tsetp.ne.b32 t, %9, 0;\n\telect.sync _|e, 0xffffffff;\n\tand.pred t, t, e;\n\t"
+        "@e mbarrier.arrive.expect_tx.shared::cta.b64 _, [%3], %8;\n\t"
+        "@e cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%2, {%4, %5}], [%3];\n\t"
+        "@t cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2, {%6, %7}], [%3];\n\t}"
+        ::"r"(dst0), "r"(dst1), "l"(map), "r"(bar), "r"(a0), "r"(b0), "r"(a1), "r"(b1), "r"(bytes), "r"(two) : "memory");
 }
 __device__ __forceinline__ void tma_tile_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
@@ -729,6 +751,22 @@ __device__ __forceinline__ void ts_split(float x, uint32_t& hi, uint32_t& lo) {
     hi = __float_as_uint(h);
     lo = __float_as_uint(x - h);
 }
+// the same block by ONE warp, straight-line: lane = (row group of 4, chunk), eight rows per lane, loads first
+__device__ __forceinline__ void ts_stage_block_warp(unsigned char* bh, const float* src, int ld, int k0, int K, int lane) {
+    const int kc = lane & 7, m0 = lane >> 3, k = k0 + 4 * kc;
+    float4 xv[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        xv[i] = (k < K) ? *reinterpret_cast<const float4*>(src + (m0 + 4 * i) * ld + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        uint32_t hh[4], ll[4];
+        ts_split(xv[i].x, hh[0], ll[0]); ts_split(xv[i].y, hh[1], ll[1]); ts_split(xv[i].z, hh[2], ll[2]); ts_split(xv[i].w, hh[3], ll[3]);
+        const uint32_t o = tc_off(m0 + 4 * i, kc);
+        *reinterpret_cast<uint4*>(bh + o) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+        *reinterpret_cast<uint4*>(bh + TS_BT_BYTES + o) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+    }
+}
 // the 32 samples' columns [k0, k0+32) of src[32][ld] -> [hi | lo] K-major tiles, by `nthr` threads (t = 0..nthr-1)
 __device__ __forceinline__ void ts_stage_samples(unsigned char* bh, const float* src, int ld, int k0, int K, int t, int nthr) {
     for (int e = t; e < 8 * UPD_ROWS; e += nthr) {
@@ -742,134 +780,213 @@ __device__ __forceinline__ void ts_stage_samples(unsigned char* bh, const float*
         *reinterpret_cast<uint4*>(bh + TS_BT_BYTES + o) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
     }
 }
-// number of uses of ring slot s by blocks 0..n-1 of a ring of size R
-__device__ __forceinline__ int ts_uses(int n, int s, int R) { return (n + R - 1 - s) / R; }
-__device__ __forceinline__ unsigned ts_advance(unsigned ph, int nblocks) {
-#pragma unroll
-    for (int s = 0; s < TS_NS; ++s) ph ^= (unsigned)(ts_uses(nblocks, s, TS_NS) & 1) << (TS_PH_RAW + s);
-#pragma unroll
-    for (int s = 0; s < TS_NSA; ++s) {
-        const unsigned u = (unsigned)(ts_uses(nblocks, s, TS_NSA) & 1);
-        ph ^= (u << (TS_PH_AF + s)) | (u << (TS_PH_MD + s));
-    }
-    return ph;
-}
-
-// forward layer on the tensor cores:  out[m][n] = act(sum_k in[m][k] W[n][k] + b[n]),  N <= 128, K % 4 == 0.
-// wmap: tensor map of W[N][K], box 32 (k) x 128 (n), SWIZZLE_128B.  ts: the TS_BYTES staging region (1024-byte aligned).
-template <bool TANH>
-__device__ __noinline__ unsigned fwd_layer_ts(const CUtensorMap* wmap, const float* __restrict__ bias, int N, int K,
-                                              const float* in, int ldin, float* out, int ldout, unsigned char* ts,
-                                              uint64_t* bars, unsigned ph, uint32_t tmem, uint32_t elected) {
+// ---------------------------------------------------------------------------
+// The wide-layer pipeline (forward and dX share it).  Ring granule = a PAIR of k-blocks (64 reduction elements):
+// every barrier round trip, tcgen05.commit (which drains the MMA queue) and loop iteration is paid once per pair.
+// Two ring slots; slot s holds two raw tiles (2 x 16 KB), two sample tile pairs, 128 A columns of tensor memory.
+//   warps 0-3  transform: raw tile -> registers -> hi/lo -> tensor memory (warp = TMEM lane quadrant)
+//   warps 4,5  samples:   one block of the pair each (activations -> [hi | lo] K-major tiles)
+//   warp 6     TMA producer: refills a slot as soon as the transform warps have consumed it (raw_free)
+//   warp 7     MMA issuer (whole warp, uniform operands, elected lane), one commit per pair
+// Barriers (index from TS_BAR0; parity bit in `ph`):  raw_full[2] +0 (bits 8,9)   raw_free[2] +2 (bits 10,11)
+//                                                      a_full[2]  +4 (bits 12,13)  mma_done[2] +8 (bits 16,17)
+// DX = false: out[m][n] = tanh(sum_k in[m][k] W[n][k] + b[n]); map box 32 (k) x 128 (n), SWIZZLE_128B; one tile.
+// DX = true : act[m][k] <- (sum_n dOut[m][n] W[n][k]) (1 - act[m][k]^2); map box 128 (k) x 32 (n), no swizzle;
+//             tiles of 128 k, the rings run across tiles, the accumulators are drained between tiles.
+// ---------------------------------------------------------------------------
+constexpr int TS_PH_RF = 10;
+template <bool DX>
+__device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* __restrict__ bias, int N, int K,
+                                          const float* bsrc, int ldb, float* dst, int ldo, unsigned char* ts, uint64_t* bars,
+                                          unsigned ph, uint32_t tmem, uint32_t /*elected*/) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nkb = (K + TC_KB - 1) / TC_KB;
+    const int R = DX ? N : K;                               // reduction length
+    const int nrb = (R + TC_KB - 1) / TC_KB;                // k-blocks per tile
+    const int npt = (nrb + 1) >> 1;                         // pairs per tile
+    const int ntiles = DX ? (K + 127) >> 7 : 1;
+    const int NP = npt * ntiles;                            // pairs in all
     uint64_t* raw_full = bars + TS_BAR0;
-    uint64_t* a_full = raw_full + TS_NS;
-    uint64_t* mma_done = a_full + TS_NSA;
+    uint64_t* raw_free = raw_full + 2;
+    uint64_t* a_full = raw_full + 4;
+    uint64_t* mma_done = raw_full + 8;
     unsigned char* raw = ts;
-    unsigned char* bst = ts + TS_NS * TS_RAW_BYTES;
-    const int n_epi = 32 * (warp & 3) + lane;               // my output feature in the epilogue: its bias is fetched now
-    const float bb = n_epi < N ? __ldg(bias + n_epi) : 0.f;
-    __syncthreads();                                        // previous users of the staging region are done, `in` is complete
-    if (warp < 4) {
-        // ---------------- weight transform: raw tile row -> hi/lo -> tensor memory ----------------
-        const int r = 32 * warp + lane;
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % TS_NS, sa = kb % TS_NSA;
-            mbar_wait(&raw_full[s], ((ph >> (TS_PH_RAW + s)) ^ (unsigned)(kb / TS_NS)) & 1u);
-            if (kb >= TS_NSA) mbar_wait(&mma_done[sa], ((ph >> (TS_PH_MD + sa)) ^ (unsigned)(kb / TS_NSA) ^ 1u) & 1u);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const unsigned char* rowp = raw + s * TS_RAW_BYTES + r * 128;
-            uint32_t hi[32], lo[32];
+    unsigned char* bst = ts + 4 * TS_RAW_BYTES;
+    float bb = 0.f;                                         // forward: bias of my epilogue feature, fetched now
+    if (!DX) { const int n = 32 * (warp & 3) + lane; bb = n < N ? __ldg(bias + n) : 0.f; }
+    // parity of the u-th use (u = 0, 1, ...) of a barrier whose tracked bit is `bit`
+    auto par = [&](int bit, int u) -> unsigned { return ((ph >> bit) ^ (unsigned)u) & 1u; };
+    auto tma_pair = [&](int gp) {                           // (whole warp 6) both raw tiles of pair gp into slot gp & 1
+        const int s = gp & 1, mt = gp / npt, p = gp - mt * npt;
+        const uint32_t two = (nrb - 2 * p >= 2) ? 1u : 0u;
+        const uint32_t d0 = smem_u32(raw + (2 * s) * TS_RAW_BYTES), bar = smem_u32(&raw_full[s]);
+        const int blk = 2 * p;
+        if (DX) tma_pair_elect(d0, d0 + TS_RAW_BYTES, map, 128 * mt, TC_KB * blk, 128 * mt, TC_KB * (blk + 1), bar, (1u + two) * TS_RAW_BYTES, two);
+        else tma_pair_elect(d0, d0 + TS_RAW_BYTES, map, TC_KB * blk, 0, TC_KB * (blk + 1), 0, bar, (1u + two) * TS_RAW_BYTES, two);
+    };
+    __syncthreads();                                        // previous users of the staging region are done
+#ifdef DPPO_K2_TRACE
+    const bool trace_on = blockIdx.x == 0 && !DX && K > 256;
+    const long long trace_t0 = clock64();
+#endif
+    if (warp == 6) {
+        tma_pair(0);
+        if (NP > 1) tma_pair(1);
+    }
+    for (int mt = 0; mt < ntiles; ++mt) {
+        const int gp0 = mt * npt;
+        if (warp < 4) {
+            // ---------------- transform ----------------
+            const int r = 32 * warp + lane;                 // TMEM lane: weight row (forward) / k within the tile (dX)
+            for (int gp = gp0; gp < gp0 + npt; ++gp) {
+                const int s = gp & 1, u = gp >> 1;
+                const int nb2 = min(2, nrb - 2 * (gp - gp0));
+                if (warp == 0) K2_TR(0, gp, 0);
+                mbar_wait(&raw_full[s], par(TS_PH_RAW + s, u));
+                if (warp == 0) K2_TR(0, gp, 1);
+                const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A + 128 * s;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {                   // 128-byte swizzle: chunk c of row r sits at c ^ (r % 8)
-                const float4 x = *reinterpret_cast<const float4*>(rowp + ((c ^ (r & 7)) << 4));
-                ts_split(x.x, hi[4 * c + 0], lo[4 * c + 0]); ts_split(x.y, hi[4 * c + 1], lo[4 * c + 1]);
-                ts_split(x.z, hi[4 * c + 2], lo[4 * c + 2]); ts_split(x.w, hi[4 * c + 3], lo[4 * c + 3]);
+                for (int i = 0; i < 2; ++i) {
+                    if (i < nb2) {
+                        uint32_t hi[32], lo[32];
+                        const unsigned char* tile = raw + (2 * s + i) * TS_RAW_BYTES;
+                        if (DX) {
+                            const float* colp = reinterpret_cast<const float*>(tile) + r;
+#pragma unroll
+                            for (int n = 0; n < 32; ++n) ts_split(colp[n * 128], hi[n], lo[n]);
+                        } else {
+                            const unsigned char* rowp = tile + r * 128;
+#pragma unroll
+                            for (int c = 0; c < 8; ++c) {   // 128-byte swizzle: chunk c of row r sits at c ^ (r % 8)
+                                const float4 x = *reinterpret_cast<const float4*>(rowp + ((c ^ (r & 7)) << 4));
+                                ts_split(x.x, hi[4 * c + 0], lo[4 * c + 0]); ts_split(x.y, hi[4 * c + 1], lo[4 * c + 1]);
+                                ts_split(x.z, hi[4 * c + 2], lo[4 * c + 2]); ts_split(x.w, hi[4 * c + 3], lo[4 * c + 3]);
+                            }
+                        }
+                        if (i == 0) {                       // the slot's previous MMAs have read these A columns
+                            if (warp == 0) K2_TR(0, gp, 2);
+                            if (gp >= 2) mbar_wait(&mma_done[s], par(TS_PH_MD + s, u - 1));
+                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                            if (warp == 0) K2_TR(0, gp, 3);
+                        }
+                        tmem_st32(ta + 64 * i, hi);
+                        tmem_st32(ta + 64 * i + 32, lo);
+                    }
+                }
+                if (warp == 0) K2_TR(0, gp, 4);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&raw_free[s]);   // every raw value of the slot has been consumed by a split
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&a_full[s]);
+                if (warp == 0) K2_TR(0, gp, 5);
             }
-            const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A + 64 * sa;
-            tmem_st32(ta, hi);
-            tmem_st32(ta + 32, lo);
-            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&a_full[sa]);
-        }
-    } else if (warp < 7) {
-        // ---------------- sample staging ----------------
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int sa = kb % TS_NSA;
-            if (kb >= TS_NSA) mbar_wait(&mma_done[sa], ((ph >> (TS_PH_MD + sa)) ^ (unsigned)(kb / TS_NSA) ^ 1u) & 1u);
-            ts_stage_samples(bst + sa * 2 * TS_BT_BYTES, in, ldin, kb * TC_KB, K, tid - 128, 96);
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&a_full[sa]);
-        }
-    } else {
-        // ---------------- issuer ----------------
-        const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-        const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-        if (elected)
-            for (int kb = 0; kb < TS_NS && kb < nkb; ++kb) {
-                mbar_expect_tx(&raw_full[kb], TS_RAW_BYTES);
-                tma_tile_2d(raw + kb * TS_RAW_BYTES, wmap, kb * TC_KB, 0, &raw_full[kb]);
+        } else if (warp < 6) {
+            // ---------------- samples: warp 4 stages the first block of every pair, warp 5 the second ----------------
+            const int i = warp - 4;
+            for (int gp = gp0; gp < gp0 + npt; ++gp) {
+                const int s = gp & 1, u = gp >> 1, blk = 2 * (gp - gp0) + i;
+                K2_TR(1, gp, 0);
+                if (gp >= 2) mbar_wait(&mma_done[s], par(TS_PH_MD + s, u - 1));
+                K2_TR(1, gp, 1);
+                if (blk < nrb) ts_stage_block_warp(bst + (2 * s + i) * 2 * TS_BT_BYTES, bsrc, ldb, blk * TC_KB, R, lane);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&a_full[s]);
+                K2_TR(1, gp, 2);
             }
-        constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % TS_NS, sa = kb % TS_NSA;
-            mbar_wait(&a_full[sa], ((ph >> (TS_PH_AF + sa)) ^ (unsigned)(kb / TS_NSA)) & 1u);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint64_t bd = tc_desc(smem_u32(bst + sa * 2 * TS_BT_BYTES));
-            const uint32_t ta = tmem + TS_TM_A + 64 * sa;
+        } else if (warp == 6) {
+            // ---------------- TMA producer ----------------
+            for (int gp = gp0; gp < gp0 + npt; ++gp)
+                if (gp + 2 < NP) {
+                    K2_TR(2, gp, 0);
+                    mbar_wait(&raw_free[gp & 1], par(TS_PH_RF + (gp & 1), gp >> 1));
+                    K2_TR(2, gp, 1);
+                    tma_pair(gp + 2);
+                    K2_TR(2, gp, 2);
+                }
+        } else {
+            // ---------------- MMA issuer ----------------
+            const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+            const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+            constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
+            for (int gp = gp0; gp < gp0 + npt; ++gp) {
+                const int s = gp & 1, u = gp >> 1;
+                const uint32_t e1 = (nrb - 2 * (gp - gp0) >= 2) ? 1u : 0u;          // second block of the pair present
+                K2_TR(3, gp, 0);
+                mbar_wait(&a_full[s], par(TS_PH_AF + s, u));
+                K2_TR(3, gp, 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint64_t bd0 = tc_desc(smem_u32(bst + (2 * s) * 2 * TS_BT_BYTES));
+                const uint64_t bd1 = tc_desc(smem_u32(bst + (2 * s + 1) * 2 * TS_BT_BYTES));
+                const uint32_t ta = tmem + TS_TM_A + 128 * s;
+                // main terms into the four rotating accumulators, the cross terms (into their hi*lo halves) four MMAs
+                // later: consecutive MMAs never touch the same accumulator
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks, ta + 8 * ks, bd + ks * KSTEP, idesc64, kb ? 1u : 0u, elected);
+                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks, ta + 8 * ks, bd0 + ks * KSTEP, idesc64, gp > gp0 ? 1u : 0u, 1u);
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks + 32, ta + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u, elected);
-            if (elected) {
-                ts_commit(&mma_done[sa]);
-                if (kb + TS_NS < nkb) {                     // a_full(kb) complete: every transform warp has read raw[s]
-                    mbar_expect_tx(&raw_full[s], TS_RAW_BYTES);
-                    tma_tile_2d(raw + s * TS_RAW_BYTES, wmap, (kb + TS_NS) * TC_KB, 0, &raw_full[s]);
+                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks + 32, ta + 32 + 8 * ks, bd0 + ks * KSTEP, idesc32, 1u, 1u);
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks, ta + 64 + 8 * ks, bd1 + ks * KSTEP, idesc64, 1u, e1);
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks + 32, ta + 96 + 8 * ks, bd1 + ks * KSTEP, idesc32, 1u, e1);
+                ts_commit(&mma_done[s]);
+                K2_TR(3, gp, 2);
+            }
+            // the tile's last commit covers all its MMAs; the issuer has seen every phase of these barriers, the other
+            // warps have not (a parity wait could let them through early), so they meet it at the block barrier
+            const int gl = gp0 + npt - 1;
+            mbar_wait(&mma_done[gl & 1], par(TS_PH_MD + (gl & 1), gl >> 1));
+            K2_TR(3, gl, 3);
+        }
+        __syncthreads();
+        if (warp == 0) K2_TR(0, 63, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        // ---------------- epilogue: lane = feature, this warp's 16 samples; the four small halves first ----------------
+        {
+            const int q = warp & 3, f = 128 * mt + 32 * q + lane, c0 = 16 * (warp >> 2);
+            float sum[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) sum[j] = 0.f;
+            const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16) + c0;
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+                uint32_t v[4][16];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) tmem_ld_issue<16>(tb + 64 * t + (hf ? 0 : 32), v[t]);
+                tmem_ld_wait();
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) sum[j] += __uint_as_float(v[t][j]);
+            }
+            if (DX) {
+                if (f < K) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        float* ap = dst + (c0 + j) * ldo + f;
+                        const float h = *ap;
+                        *ap = sum[j] * (1.f - h * h);
+                    }
+                }
+            } else {
+                if (f < N) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) dst[(c0 + j) * ldo + f] = tanh_act(sum[j] + bb);
                 }
             }
-            __syncwarp();
         }
+        if (warp == 0) K2_TR(0, 63, 1);
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
     }
-    {   // the last commit covers every MMA of the layer
-        const int sl = (nkb - 1) % TS_NSA;
-        mbar_wait(&mma_done[sl], ((ph >> (TS_PH_MD + sl)) ^ (unsigned)((nkb - 1) / TS_NSA)) & 1u);
+    // every phase of every ring barrier has completed: advance the tracked parities by the number of uses
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+        const unsigned uses = (unsigned)(((NP + 1 - s) >> 1) & 1);
+        ph ^= (uses << (TS_PH_RAW + s)) | (uses << (TS_PH_RF + s)) | (uses << (TS_PH_AF + s)) | (uses << (TS_PH_MD + s));
     }
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    // epilogue: lane = output feature, this warp's 16 samples; small terms first
-    {
-        const int q = warp & 3, n = 32 * q + lane, c0 = 16 * (warp >> 2);
-        float sum[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) sum[j] = 0.f;
-        const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16) + c0;
-#pragma unroll
-        for (int hf = 0; hf < 2; ++hf) {                    // the four small halves first, then the four hi*hi halves
-            uint32_t v[4][16];
-#pragma unroll
-            for (int t = 0; t < 4; ++t) tmem_ld_issue<16>(tb + 64 * t + (hf ? 0 : 32), v[t]);
-            tmem_ld_wait();
-#pragma unroll
-            for (int t = 0; t < 4; ++t)
-#pragma unroll
-                for (int j = 0; j < 16; ++j) sum[j] += __uint_as_float(v[t][j]);
-        }
-        if (n < N) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                float y = sum[j] + bb;
-                if (TANH) y = tanh_act(y);
-                out[(c0 + j) * ldout + n] = y;
-            }
-        }
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    return ts_advance(ph, nkb);
+    return ph;
 }
 
 // ---------------------------------------------------------------------------
@@ -886,7 +1003,7 @@ __device__ __forceinline__ unsigned char* first_b_tiles(float* stage, const dppo
 }
 __device__ __noinline__ unsigned fwd_first_ts(const float* Ws, const float* __restrict__ bias, int N, int K, const float* in,
                                               int ldin, float* out, int ldout, unsigned char* bt, uint64_t* bars, unsigned ph,
-                                              uint32_t tmem, uint32_t elected) {
+                                              uint32_t tmem, uint32_t /*elected*/) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ntiles = (N + 127) >> 7, nks = (K + 7) >> 3;
     uint64_t* mma_done = bars + TS_BAR0 + TS_NS + TS_NSA;
@@ -921,14 +1038,21 @@ __device__ __noinline__ unsigned fwd_first_ts(const float* Ws, const float* __re
         const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         const uint64_t bd = tc_desc(smem_u32(bt));
         constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
-        for (int t = 0; t < ntiles; ++t)
-            for (int ks = 0; ks < nks; ++ks)
-                ts_mma(tmem + 64 * t, tmem + TS_TM_A + 64 * t + 8 * ks, bd + ks * KSTEP, idesc64, ks ? 1u : 0u, elected);
-        for (int t = 0; t < ntiles; ++t)
-            for (int ks = 0; ks < nks; ++ks)
-                ts_mma(tmem + 64 * t + 32, tmem + TS_TM_A + 64 * t + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u, elected);
-        if (elected) ts_commit(&mma_done[0]);
-        __syncwarp();
+        // straight-line, k-step outer / tile inner: consecutive MMAs go to different accumulators (a dependent MMA
+        // waits ~90 cycles) and there is no loop branch between them; absent tiles / k-steps are predicated off
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                ts_mma(tmem + 64 * t, tmem + TS_TM_A + 64 * t + 8 * ks, bd + ks * KSTEP, idesc64, ks ? 1u : 0u,
+                       (t < ntiles && ks < nks) ? 1u : 0u);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                ts_mma(tmem + 64 * t + 32, tmem + TS_TM_A + 64 * t + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u,
+                       (t < ntiles && ks < nks) ? 1u : 0u);
+        ts_commit(&mma_done[0]);
     }
     mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);
     ph ^= 1u << TS_PH_MD;
@@ -959,7 +1083,7 @@ __device__ __noinline__ unsigned fwd_first_ts(const float* Ws, const float* __re
 // dW / db of a first layer (see above).  img: N*K floats of shared memory (the flat image is flushed coalesced).
 __device__ __noinline__ unsigned dw_first_ts(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut,
                                              int ldd, const float* in, int ldin, bool accumulate, float* img, unsigned char* bt,
-                                             uint64_t* bars, unsigned ph, uint32_t tmem, uint32_t elected) {
+                                             uint64_t* bars, unsigned ph, uint32_t tmem, uint32_t /*elected*/) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ntiles = (N + 127) >> 7;
     uint64_t* mma_done = bars + TS_BAR0 + TS_NS + TS_NSA;
@@ -1000,16 +1124,19 @@ __device__ __noinline__ unsigned dw_first_ts(float* __restrict__ gW, float* __re
         const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         const uint64_t bd = tc_desc(smem_u32(bt));
         constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
-        for (int t = 0; t < ntiles; ++t)
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks)
-                ts_mma(tmem + 64 * t, tmem + TS_TM_A + 64 * t + 8 * ks, bd + ks * KSTEP, idesc64, ks ? 1u : 0u, elected);
-        for (int t = 0; t < ntiles; ++t)
+        for (int ks = 0; ks < 4; ++ks)
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks)
-                ts_mma(tmem + 64 * t + 32, tmem + TS_TM_A + 64 * t + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u, elected);
-        if (elected) ts_commit(&mma_done[0]);
-        __syncwarp();
+            for (int t = 0; t < 4; ++t)
+                ts_mma(tmem + 64 * t, tmem + TS_TM_A + 64 * t + 8 * ks, bd + ks * KSTEP, idesc64, ks ? 1u : 0u,
+                       t < ntiles ? 1u : 0u);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+                ts_mma(tmem + 64 * t + 32, tmem + TS_TM_A + 64 * t + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u,
+                       t < ntiles ? 1u : 0u);
+        ts_commit(&mma_done[0]);
     }
     mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);
     ph ^= 1u << TS_PH_MD;
@@ -1059,7 +1186,7 @@ __device__ __forceinline__ unsigned fwd_layer(const float* __restrict__ W, const
                                           uint64_t* bars, unsigned ph, uint32_t tmem, const CUtensorMap* wmap, uint32_t elected) {
     // wide GEMM-shaped layers go to the tensor cores (tcgen05), the rest stays on the FP32 pipe
     if (wmap != nullptr && N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0)
-        return fwd_layer_ts<TANH>(wmap, bias, N, K, in, ldin, out, ldout, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
+        return ts_layer<false>(wmap, bias, N, K, in, ldin, out, ldout, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
     if (N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0 && SF >= TC_STAGE_FLOATS)
         return fwd_layer_tc<TANH>(W, bias, N, K, in, ldin, out, ldout, stage, SF, bars, ph, tmem);
     // 4*CN columns per warp: 28 fits N = 100 (reference widths) in four blocks, 32 otherwise
@@ -1234,126 +1361,11 @@ __device__ __noinline__ unsigned dx_layer_t(const float* __restrict__ W, int N, 
     return ph;
 }
 
-// dX through a tanh layer on the tensor cores (same pipeline as fwd_layer_ts, weights transposed on the way into
-// tensor memory):   act[m][k] <- (sum_n dOut[m][n] W[n][k]) (1 - act[m][k]^2)
-//   D[k][m] = A[k][n] . B[m][n]^T,  A = W^T: TMEM lane = k (128 per tile), columns = n (32 per block);
-//   raw tile = W[n0..n0+31][k0..k0+127] (box 128 x 32, no swizzle: thread k reads a column, conflict-free)
-//   B = dOut, K-major over n, split into [hi | lo] tiles per block.
-// The rings run over the global block index g = tile * nnb + block, so the next tile's weights are in flight while
-// a tile drains; only the accumulators are per tile (epilogue between tiles, all eight warps).
-__device__ __noinline__ unsigned dx_layer_ts(const CUtensorMap* xmap, int N, int K, const float* dOut, int ldd, float* act,
-                                             int lda, unsigned char* ts, uint64_t* bars, unsigned ph, uint32_t tmem,
-                                             uint32_t elected) {
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nnb = (N + TC_KB - 1) / TC_KB, ntiles = (K + 127) >> 7, G = nnb * ntiles;
-    uint64_t* raw_full = bars + TS_BAR0;
-    uint64_t* a_full = raw_full + TS_NS;
-    uint64_t* mma_done = a_full + TS_NSA;
-    unsigned char* raw = ts;
-    unsigned char* bst = ts + TS_NS * TS_RAW_BYTES;
-    __syncthreads();
-    if (warp == 7 && elected)
-        for (int g = 0; g < TS_NS && g < G; ++g) {
-            mbar_expect_tx(&raw_full[g], TS_RAW_BYTES);
-            tma_tile_2d(raw + g * TS_RAW_BYTES, xmap, 128 * (g / nnb), TC_KB * (g % nnb), &raw_full[g]);
-        }
-    for (int mt = 0; mt < ntiles; ++mt) {
-        const int g0 = mt * nnb;
-        if (warp < 4) {
-            const int r = 32 * warp + lane;                 // k within the tile = TMEM lane
-            for (int g = g0; g < g0 + nnb; ++g) {
-                const int s = g % TS_NS, sa = g % TS_NSA;
-                mbar_wait(&raw_full[s], ((ph >> (TS_PH_RAW + s)) ^ (unsigned)(g / TS_NS)) & 1u);
-                if (g >= TS_NSA) mbar_wait(&mma_done[sa], ((ph >> (TS_PH_MD + sa)) ^ (unsigned)(g / TS_NSA) ^ 1u) & 1u);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const float* colp = reinterpret_cast<const float*>(raw + s * TS_RAW_BYTES) + r;
-                uint32_t hi[32], lo[32];
-#pragma unroll
-                for (int n = 0; n < 32; ++n) ts_split(colp[n * 128], hi[n], lo[n]);
-                const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A + 64 * sa;
-                tmem_st32(ta, hi);
-                tmem_st32(ta + 32, lo);
-                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&a_full[sa]);
-            }
-        } else if (warp < 7) {
-            for (int g = g0; g < g0 + nnb; ++g) {
-                const int sa = g % TS_NSA;
-                if (g >= TS_NSA) mbar_wait(&mma_done[sa], ((ph >> (TS_PH_MD + sa)) ^ (unsigned)(g / TS_NSA) ^ 1u) & 1u);
-                ts_stage_samples(bst + sa * 2 * TS_BT_BYTES, dOut, ldd, (g - g0) * TC_KB, N, tid - 128, 96);
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&a_full[sa]);
-            }
-        } else {
-            const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-            const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-            constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
-            for (int g = g0; g < g0 + nnb; ++g) {
-                const int s = g % TS_NS, sa = g % TS_NSA;
-                mbar_wait(&a_full[sa], ((ph >> (TS_PH_AF + sa)) ^ (unsigned)(g / TS_NSA)) & 1u);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint64_t bd = tc_desc(smem_u32(bst + sa * 2 * TS_BT_BYTES));
-                const uint32_t ta = tmem + TS_TM_A + 64 * sa;
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks, ta + 8 * ks, bd + ks * KSTEP, idesc64, g > g0 ? 1u : 0u, elected);
-#pragma unroll
-                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks + 32, ta + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u, elected);
-                if (elected) {
-                    ts_commit(&mma_done[sa]);
-                    const int gn = g + TS_NS;
-                    if (gn < G) {
-                        mbar_expect_tx(&raw_full[s], TS_RAW_BYTES);
-                        tma_tile_2d(raw + s * TS_RAW_BYTES, xmap, 128 * (gn / nnb), TC_KB * (gn % nnb), &raw_full[s]);
-                    }
-                }
-                __syncwarp();
-            }
-        }
-        {
-            const int gl = g0 + nnb - 1, sl = gl % TS_NSA;
-            mbar_wait(&mma_done[sl], ((ph >> (TS_PH_MD + sl)) ^ (unsigned)(gl / TS_NSA)) & 1u);
-        }
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        {
-            const int q = warp & 3, k = 128 * mt + 32 * q + lane, c0 = 16 * (warp >> 2);
-            float sum[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) sum[j] = 0.f;
-            const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16) + c0;
-#pragma unroll
-            for (int hf = 0; hf < 2; ++hf) {
-                uint32_t v[4][16];
-#pragma unroll
-                for (int t = 0; t < 4; ++t) tmem_ld_issue<16>(tb + 64 * t + (hf ? 0 : 32), v[t]);
-                tmem_ld_wait();
-#pragma unroll
-                for (int t = 0; t < 4; ++t)
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) sum[j] += __uint_as_float(v[t][j]);
-            }
-            if (k < K) {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    float* ap = act + (c0 + j) * lda + k;
-                    const float h = *ap;
-                    *ap = sum[j] * (1.f - h * h);
-                }
-            }
-        }
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();
-    }
-    return ts_advance(ph, G);
-}
-
 __device__ __forceinline__ unsigned dx_layer(const float* __restrict__ W, int N, int K, const float* dOut, int ldd,
                                          float* act, int lda, float* stage, int SF, uint64_t* bars, unsigned ph,
                                          const CUtensorMap* xmap, uint32_t tmem, uint32_t elected) {
     if (xmap != nullptr && N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0)   // = ts_eligible() on the host
-        return dx_layer_ts(xmap, N, K, dOut, ldd, act, lda, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
+        return ts_layer<true>(xmap, nullptr, N, K, dOut, ldd, act, lda, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
     const int KQ = (K + 3) >> 2;
     if (KQ > UPD_THREADS / 4) return dx_layer_t<4>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
     if (KQ > UPD_THREADS / 8) return dx_layer_t<2>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
@@ -1664,7 +1676,7 @@ __device__ __noinline__ unsigned dw_layer_tc(float* __restrict__ gW, float* __re
 // epilogue - 2 Np columns of tensor memory and N x 128 floats to global memory - dominates.
 __device__ __noinline__ unsigned dw_layer_ts(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut,
                                              int ldd, const float* in, int ldin, bool accumulate, unsigned char* ts,
-                                             uint64_t* bars, unsigned ph, uint32_t tmem, uint32_t elected) {
+                                             uint64_t* bars, unsigned ph, uint32_t tmem, uint32_t /*elected*/) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int Np = (N + 15) & ~15;
     const int ntiles = (K + 127) >> 7;
@@ -1710,11 +1722,10 @@ __device__ __noinline__ unsigned dw_layer_ts(float* __restrict__ gW, float* __re
         if (warp == 7) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem, tmem + TS_TM_A + 8 * ks, bd + ks * KSTEP, idm, ks ? 1u : 0u, elected);
+            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem, tmem + TS_TM_A + 8 * ks, bd + ks * KSTEP, idm, ks ? 1u : 0u, 1u);
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + Np, tmem + TS_TM_A + 32 + 8 * ks, bd + ks * KSTEP, idc, 1u, elected);
-            if (elected) ts_commit(&mma_done[0]);
-            __syncwarp();
+            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + Np, tmem + TS_TM_A + 32 + 8 * ks, bd + ks * KSTEP, idc, 1u, 1u);
+            ts_commit(&mma_done[0]);
         }
         mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);     // every thread sees every phase of this barrier
         ph ^= 1u << TS_PH_MD;
@@ -1839,6 +1850,11 @@ __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, 
     K2_TICK(tick + 2);
     ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph, tmem,
                          maps ? maps + 1 : nullptr, elected);
+#ifdef DPPO_K2_TWICE
+    K2_TICK(tick + 2);                                      // experiment: the same layer again, instruction cache warm
+    ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph, tmem,
+                         maps ? maps + 1 : nullptr, elected);
+#endif
     K2_TICK(tick + 3);
     if (P.small_first && next != nullptr) first_layers_prefetch(stage, next->W1, next->V1, d, &bars[0]);
     heads_fwd(hs, d.A, d.H2, d.G2, S + P.o_h2, P.ldH2, S + P.o_g2, P.ldG2, mu_out, P.ldA, v_out);
@@ -1877,9 +1893,12 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         mbar_init(&b[3], 1);
         mbar_init(&b[4], UPD_THREADS / 32 - 1);            // tensor-core stages: filled, one arrival per producer warp
         mbar_init(&b[5], UPD_THREADS / 32 - 1);
-        for (int i = 0; i < TS_NS; ++i) mbar_init(&b[TS_BAR0 + i], 1);                       // raw_full
-        for (int i = 0; i < TS_NSA; ++i) mbar_init(&b[TS_BAR0 + TS_NS + i], 7);              // a_full
-        for (int i = 0; i < TS_NSA; ++i) mbar_init(&b[TS_BAR0 + TS_NS + TS_NSA + i], 1);     // mma_done
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&b[TS_BAR0 + i], 1);                  // raw_full (TMA tx)
+            mbar_init(&b[TS_BAR0 + 2 + i], 4);              // raw_free: the four transform warps
+            mbar_init(&b[TS_BAR0 + 4 + i], 6);              // a_full: four transform warps + the two sample warps
+            mbar_init(&b[TS_BAR0 + 8 + i], 1);              // mma_done (tcgen05.commit)
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     // tensor memory: all 512 columns (one CTA per SM), 9 accumulators of 32 columns are used
@@ -2373,6 +2392,11 @@ extern "C" int dppo_update_fused(int flavour, const dppo_dims* d, const float* o
     return 0;
 }
 
+#ifdef DPPO_K2_TRACE
+extern "C" int dppo_debug_k2_trace(long long* out_host) {
+    return (int)cudaMemcpyFromSymbol(out_host, g_k2_trace, sizeof(long long) * 4 * 64 * 8);
+}
+#endif
 #ifdef DPPO_K2_TIMING
 extern "C" int dppo_debug_k2_clocks(long long* out64_host) {
     return (int)cudaMemcpyFromSymbol(out64_host, g_k2_clock, sizeof(long long) * 64);

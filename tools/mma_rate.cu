@@ -47,9 +47,9 @@ __device__ __forceinline__ void mma_ts_e(uint32_t d, uint32_t a, uint64_t b, uin
 }
 // K2's k-block, issued by a whole warp with uniform operands (one elected lane): four N = n_main MMAs into rotating
 // accumulators, then (with_cross) four N = 32 MMAs into their upper halves; A from tensor memory
-__global__ void __launch_bounds__(256) mma_rate_uniform_kernel(int nkb, int n_main, int with_cross, long long* out) {
+__global__ void __launch_bounds__(256) mma_rate_uniform_kernel(int nkb, int n_main, int with_cross, int commit_every, int fence_every, long long* out) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    __shared__ uint64_t bar;
+    __shared__ uint64_t bar, bar2;
     __shared__ uint32_t tmem_base_s;
     const int tid = threadIdx.x, warp = tid >> 5;
     for (int i = tid; i < 24576; i += 256) reinterpret_cast<float*>(smem)[i] = 1.0f;
@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(256) mma_rate_uniform_kernel(int nkb, int n_ma
     }
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar2)));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -79,6 +80,15 @@ __global__ void __launch_bounds__(256) mma_rate_uniform_kernel(int nkb, int n_ma
             if (with_cross) {
 #pragma unroll
                 for (int ks = 0; ks < 4; ++ks) mma_ts_e(tmem + 64 * ks + 32, ta + 32 + 8 * ks, bh + ks * 18, id32, 1u, el);
+            }
+            if (commit_every) {                              // predicated commit: no divergent branch in the issuing warp
+                const uint32_t ec = ((kb % commit_every) == commit_every - 1) ? el : 0u;
+                asm volatile("{\n\t.reg .pred e;\n\tsetp.ne.b32 e, %1, 0;\n\t"
+                             "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(&bar2)), "r"(ec) : "memory");
+            }
+            if (fence_every && (kb % fence_every) == fence_every - 1) {
+                __syncwarp();
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             }
         }
         long long t1 = clock64();
@@ -189,17 +199,17 @@ int main() {
         printf("%-62s issue %7.1f  complete %7.1f cycles per k-block (32 k)\n", c.name, (double)h[0] / nkb, (double)h[1] / nkb);
     }
     cudaFuncSetAttribute(mma_rate_uniform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-    const int ucfg[][2] = {{64, 1}, {64, 0}, {32, 0}, {128, 0}, {256, 0}};
+    const int ucfg[][4] = {{64, 1, 0, 0}, {64, 1, 2, 0}, {64, 1, 1, 0}, {64, 1, 2, 2}, {64, 0, 0, 0}, {32, 0, 0, 0}, {128, 0, 0, 0}};
     for (auto& u : ucfg) {
         for (int rep = 0; rep < 2; ++rep) {
-            mma_rate_uniform_kernel<<<148, 256, 100 * 1024>>>(nkb, u[0], u[1], out);
+            mma_rate_uniform_kernel<<<148, 256, 100 * 1024>>>(nkb, u[0], u[1], u[2], u[3], out);
             cudaError_t e = cudaDeviceSynchronize();
             if (e != cudaSuccess) { printf("uniform: %s\n", cudaGetErrorString(e)); return 1; }
         }
         long long h[2];
         cudaMemcpy(h, out, 16, cudaMemcpyDeviceToHost);
-        printf("uniform issue, TS, 4 x N=%-3d %-22s issue %7.1f  complete %7.1f cycles per k-block (32 k)\n", u[0],
-               u[1] ? "+ 4 x N=32 (K2 block)" : "", (double)h[0] / nkb, (double)h[1] / nkb);
+        printf("uniform issue, TS, 4 x N=%-3d %-22s commit every %d, fence every %d blocks: issue %7.1f  complete %7.1f cycles per k-block\n", u[0],
+               u[1] ? "+ 4 x N=32 (K2 block)" : "", u[2], u[3], (double)h[0] / nkb, (double)h[1] / nkb);
     }
     return 0;
 }

@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(256, 1) ts_fwd_kernel(const __grid_constant__ 
     extern __shared__ __align__(1024) unsigned char smem[];
     unsigned char* raw = smem;                                           // NS x 16 KB, 1024-byte aligned (swizzle atom)
     unsigned char* bst = smem + NS * RAW_BYTES;                          // NSA x [X_hi tile | X_lo tile]
-    __shared__ uint64_t raw_full[NS], a_full[NSA], mma_done[NSA];
+    __shared__ uint64_t raw_full[NS], raw_free[NS], a_full[NSA], mma_done[NSA];
     __shared__ uint32_t tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (warp == 0) {
@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(256, 1) ts_fwd_kernel(const __grid_constant__ 
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     if (tid == 0) {
-        for (int s = 0; s < NS; ++s) mbar_init(&raw_full[s], 1);
+        for (int s = 0; s < NS; ++s) { mbar_init(&raw_full[s], 1); mbar_init(&raw_free[s], 4); }
         for (int s = 0; s < NSA; ++s) { mbar_init(&a_full[s], 5); mbar_init(&mma_done[s], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -135,73 +135,93 @@ __global__ void __launch_bounds__(256, 1) ts_fwd_kernel(const __grid_constant__ 
 #define TR(role, kb, ev) do { } while (0)
 #endif
 #ifdef PROBE_TIMING
-#define TACC(i) do { long long t = clock64(); ta_[i] += t - tc_; tc_ = t; } while (0)
-#define TSET() tc_ = clock64()
+#define TACC(i) do { } while (0)
+#define TSET() do { } while (0)
 #else
 #define TACC(i) do { } while (0)
 #define TSET() do { } while (0)
 #endif
     if (warp < 4) {
-        // ---------------- weight transform: raw tile row -> hi/lo -> tensor memory ----------------
-        // software pipelined: the next block's barrier polls and shared-memory loads overlap this block's split
+        // ---------------- weight transform, two k-blocks per loop iteration ----------------
         const int r = 32 * warp + lane;
-        float4 x[8];
-        mbar_wait(&raw_full[0], 0u);
+        const int sw = r & 7;
+        float4 x0[8], x1[8];
+        auto load_row = [&](float4 (&x)[8], int kb) {
+            const unsigned char* rowp = raw + (kb % NS) * RAW_BYTES + r * 128;
 #pragma unroll
-        for (int c = 0; c < 8; ++c) x[c] = *reinterpret_cast<const float4*>(raw + r * 128 + ((c ^ (r & 7)) << 4));
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int sa = kb % NSA, s1 = (kb + 1) % NS;
-            const bool more = kb + 1 < nkb;
-            const unsigned par1 = ((kb + 1) / NS) & 1u, parm = ((kb / NSA) & 1u) ^ 1u;
-            TSET();
-            if (warp == 0) TR(0, kb, 0);
-#ifdef PROBE_NO_REFILL
-            unsigned okr = (more && kb + 1 < NS) ? mbar_test(&raw_full[s1], par1) : 1u;
-#else
-            unsigned okr = more ? mbar_test(&raw_full[s1], par1) : 1u;
+            for (int c = 0; c < 8; ++c) x[c] = *reinterpret_cast<const float4*>(rowp + ((c ^ sw) << 4));
+            // the values are consumed by the split before this warp's next arrival on the same slot; signalling
+            // right after the loads were ISSUED would be too early, so the arrival follows the first use (below)
+        };
+        auto free_slot = [&](int kb) { __syncwarp(); if (lane == 0) mbar_arrive(&raw_free[kb % NS]); };
+        auto split_store = [&](const float4 (&x)[8], int kb) {
+#ifdef PROBE_EMPTY_STAGES
+            { const int sa = kb % NSA; if (kb >= NSA) mbar_wait(&mma_done[sa], ((kb / NSA) & 1u) ^ 1u); return; }
 #endif
-            unsigned okm = kb >= NSA ? mbar_test(&mma_done[sa], parm) : 1u;
             uint32_t hi[32], lo[32];
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
                 split(x[c].x, hi[4 * c + 0], lo[4 * c + 0]); split(x[c].y, hi[4 * c + 1], lo[4 * c + 1]);
                 split(x[c].z, hi[4 * c + 2], lo[4 * c + 2]); split(x[c].w, hi[4 * c + 3], lo[4 * c + 3]);
             }
-            TACC(3);
-            if (more) {
-                while (!okr) okr = mbar_test(&raw_full[s1], par1);
-                const unsigned char* rowp = raw + s1 * RAW_BYTES + r * 128;
-#pragma unroll
-                for (int c = 0; c < 8; ++c) x[c] = *reinterpret_cast<const float4*>(rowp + ((c ^ (r & 7)) << 4));
-            }
-            TACC(0);
-            if (warp == 0) TR(0, kb, 1);
-            while (!okm) okm = mbar_test(&mma_done[sa], parm);
-            if (warp == 0) TR(0, kb, 2);
-            TACC(1);
+            const int sa = kb % NSA;
+            if (kb >= NSA) mbar_wait(&mma_done[sa], ((kb / NSA) & 1u) ^ 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TM_A + 64 * sa;
+#ifndef PROBE_NO_ST
             tmem_st32(ta, hi);
             tmem_st32(ta + 32, lo);
+#else
+            if (hi[0] == 0x12345u && lo[5] == 0x777u) tmem_st32(ta, hi);
+#endif
+        };
+        mbar_wait(&raw_full[0], 0u);
+        load_row(x0, 0);
+        if (nkb > 1) { mbar_wait(&raw_full[1 % NS], 0u); load_row(x1, 1); }
+        for (int kb = 0; kb < nkb; kb += 2) {
+            if (warp == 0) TR(0, kb, 0);
+            const bool two = kb + 1 < nkb;
+            split_store(x0, kb);
+            free_slot(kb);
+            if (kb + 2 < nkb) { mbar_wait(&raw_full[(kb + 2) % NS], ((kb + 2) / NS) & 1u); load_row(x0, kb + 2); }
+            if (two) { split_store(x1, kb + 1); free_slot(kb + 1); }
+            if (kb + 3 < nkb) { mbar_wait(&raw_full[(kb + 3) % NS], ((kb + 3) / NS) & 1u); load_row(x1, kb + 3); }
+            if (warp == 0) TR(0, kb, 1);
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
-            if (lane == 0) mbar_arrive(&a_full[sa]);
+            if (lane == 0) {
+                mbar_arrive(&a_full[kb % NSA]);
+                if (two) mbar_arrive(&a_full[(kb + 1) % NSA]);
+            }
             if (warp == 0) TR(0, kb, 3);
-            TACC(4);
         }
-    } else if (warp < 7) {
-        // ---------------- sample staging: each of the three warps takes every third block ----------------
+    } else if (warp == 6) {
+        // ---------------- TMA producer: refill a raw slot as soon as the four transform warps have consumed it ----------------
+        if (lane == 0) {
+            for (int kb = 0; kb < NS && kb < nkb; ++kb) {
+                mbar_expect_tx(&raw_full[kb], RAW_BYTES);
+                tma_2d(raw + kb * RAW_BYTES, &wmap, kb * KB, 0, &raw_full[kb]);
+            }
+            for (int kb = 0; kb + NS < nkb; ++kb) {
+                const int s = kb % NS;
+                mbar_wait(&raw_free[s], (kb / NS) & 1u);
+                mbar_expect_tx(&raw_full[s], RAW_BYTES);
+                tma_2d(raw + s * RAW_BYTES, &wmap, (kb + NS) * KB, 0, &raw_full[s]);
+            }
+        }
+        __syncwarp();
+    } else if (warp < 6) {
+        // ---------------- sample staging: the two warps alternate blocks ----------------
         const int kc = lane & 7, m0 = lane >> 3;
-        for (int kb = warp - 4; kb < nkb; kb += 3) {
+        for (int kb = warp - 4; kb < nkb; kb += 2) {
             const int sa = kb % NSA;
-            TSET();
             TR(1, kb, 0);
             if (kb >= NSA) mbar_wait(&mma_done[sa], ((kb / NSA) & 1u) ^ 1u);
             TR(1, kb, 1);
-            TACC(1);
             unsigned char* bh = bst + sa * 2 * BT_BYTES;
             const int k = kb * KB + 4 * kc;
+#ifndef PROBE_EMPTY_STAGES
             float4 xv[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i)
@@ -215,50 +235,44 @@ __global__ void __launch_bounds__(256, 1) ts_fwd_kernel(const __grid_constant__ 
                 *reinterpret_cast<uint4*>(bh + o) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
                 *reinterpret_cast<uint4*>(bh + BT_BYTES + o) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
             }
+#endif
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0) mbar_arrive(&a_full[sa]);
             TR(1, kb, 3);
-            TACC(2);
         }
     } else {
-        // ---------------- issuer: TMA refills and MMAs (whole warp, uniform operands, one elected lane) ----------------
-        if (elected)
-            for (int kb = 0; kb < NS && kb < nkb; ++kb) {
-                mbar_expect_tx(&raw_full[kb], RAW_BYTES);
-                tma_2d(raw + kb * RAW_BYTES, &wmap, kb * KB, 0, &raw_full[kb]);
-            }
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb % NS, sa = kb % NSA;
-            TSET();
+        // ---------------- issuer: two k-blocks per loop iteration ----------------
+        for (int kb = 0; kb < nkb; kb += 2) {
+            const bool two = kb + 1 < nkb;
+            const int sa0 = kb % NSA, sa1 = (kb + 1) % NSA;
             TR(2, kb, 0);
-            mbar_wait(&a_full[sa], (kb / NSA) & 1u);
+            mbar_wait(&a_full[sa0], (kb / NSA) & 1u);
+            if (two) mbar_wait(&a_full[sa1], ((kb + 1) / NSA) & 1u);
             TR(2, kb, 1);
-            TACC(3);
-#ifdef PROBE_NO_REFILL
-            if (false) {
-#else
-            if (elected && kb + NS < nkb) {                              // a_full(kb): everybody has read raw[s], refill it
-#endif
-                mbar_expect_tx(&raw_full[s], RAW_BYTES);
-                tma_2d(raw + s * RAW_BYTES, &wmap, (kb + NS) * KB, 0, &raw_full[s]);
-            }
-            __syncwarp();
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint64_t bd = b_desc(smem_u32(bst + sa * 2 * BT_BYTES));
-            const uint32_t ta = tmem + TM_A + 64 * sa;
-            // main terms first, the cross terms (into the hi*lo half of the same accumulators) four MMAs later
+            const uint64_t bd0 = b_desc(smem_u32(bst + sa0 * 2 * BT_BYTES)), bd1 = b_desc(smem_u32(bst + sa1 * 2 * BT_BYTES));
+            const uint32_t ta0 = tmem + TM_A + 64 * sa0, ta1 = tmem + TM_A + 64 * sa1;
+            const uint32_t e1 = two ? elected : 0u;
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks)
-                mma_ts(tmem + TM_MAIN + 64 * ks, ta + 8 * ks, bd + ks * ((2 * LBO) >> 4), idesc64, kb ? 1u : 0u, elected);
+                mma_ts(tmem + TM_MAIN + 64 * ks, ta0 + 8 * ks, bd0 + ks * ((2 * LBO) >> 4), idesc64, kb ? 1u : 0u, elected);
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks)
-                mma_ts(tmem + TM_MAIN + 64 * ks + 32, ta + 32 + 8 * ks, bd + ks * ((2 * LBO) >> 4), idesc32, 1u, elected);
-            if (elected)
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&mma_done[sa])) : "memory");
+                mma_ts(tmem + TM_MAIN + 64 * ks + 32, ta0 + 32 + 8 * ks, bd0 + ks * ((2 * LBO) >> 4), idesc32, 1u, elected);
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks)
+                mma_ts(tmem + TM_MAIN + 64 * ks, ta1 + 8 * ks, bd1 + ks * ((2 * LBO) >> 4), idesc64, 1u, e1);
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks)
+                mma_ts(tmem + TM_MAIN + 64 * ks + 32, ta1 + 32 + 8 * ks, bd1 + ks * ((2 * LBO) >> 4), idesc32, 1u, e1);
+            if (elected) {
+                // one commit covers both blocks (it arrives when every MMA issued so far is done)
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&mma_done[sa0])) : "memory");
+                if (two) asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&mma_done[sa1])) : "memory");
+            }
             __syncwarp();
             TR(2, kb, 3);
-            TACC(4);
         }
     }
     // the last commit covers every MMA; only the issuer has seen every earlier phase of that barrier (a warp that
