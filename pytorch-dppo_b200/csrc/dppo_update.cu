@@ -4,20 +4,22 @@
 // (model.py:35-45), the DPPO loss train.py:140-161 (+ normal() 41-44) or the
 // ppo.py loss ppo.py:147-170, and backward (train.py:166 / ppo.py:172).
 //
-// CUDA-core path (all widths).  One CTA owns a tile of TM <= 32 gathered
-// samples and carries them through old-net forward, new-net forward, the loss
-// and the whole backward with every activation resident in shared memory;
-// weights stream L2 -> shared memory in chunks (they are shared by all CTAs and
-// stay L2-resident).  Each CTA writes ONE partial of every gradient tensor
-// (its samples' contribution); K3 sums the partials in CTA order, so results
-// are bit-reproducible (no float atomics).
+// One CTA (256 threads, one per SM) owns a tile of TM <= 32 gathered samples and carries them through the old-net
+// forward, the new-net forward, the loss and the whole backward with every activation resident in shared memory.
+// Each CTA writes ONE partial of every gradient tensor (its samples' contribution); K3 sums the partials in CTA
+// order, so results are bit-reproducible (no float atomics).
 //
-// Register tiling: forward  C[m][n] += in[m][k..k+3] . W[n][k..k+3]   4x4 per thread
-//                  dX       C[m][k] += dOut[m][n..n+3] . W[n..n+3][k] 4x(4*KT)
-//                  dW       C[n][k] += dOut[m][n] * in[m][k]          4x4
-// all operands read as 128-bit shared-memory vectors along their contiguous
-// dimension; rows are interleaved over threads and leading dimensions are odd
-// multiples of 16 B so the quarter-warp phases are bank-conflict free.
+// Tensor-core path (tcgen05, 3xTF32 with fp32 accumulation in tensor memory) for the reference-sized layers:
+//   wide layers (N <= 128 outputs, K >= 64, K % 4 == 0): forward and dX through ts_layer (TMA tiles -> registers ->
+//     tensor memory -> MMA, role-specialised warps), dW through dw_layer_ts;
+//   first layers (K = observation width <= 32, N <= 512): fwd_first_ts / dw_first_ts from weight copies that a bulk
+//     copy fetched one phase earlier.
+// FP32-pipe path for every other shape (wide nets such as 256x256, odd widths): register-tiled FFMA layers
+//   forward  C[m][n] += in[m][k..k+3] . W[n][k..k+3]   4x4 per thread
+//   dX       C[m][k] += dOut[m][n..n+3] . W[n..n+3][k] 4x(4*KT)
+//   dW       C[n][k] += dOut[m][n] * in[m][k]          4x4
+// with weights streamed L2 -> shared memory by TMA bulk copies on mbarriers, all operands read as 128-bit
+// shared-memory vectors; leading dimensions are odd multiples of 16 B so quarter-warp phases are conflict free.
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -48,11 +50,7 @@ __device__ long long g_k2_trace[4 * 64 * 8];
 
 namespace {
 
-#ifndef DPPO_K2_THREADS
-#define DPPO_K2_THREADS 256
-#endif
-constexpr int UPD_THREADS = DPPO_K2_THREADS;      // 256 or 512 (8 or 16 warps)
-constexpr int UPD_WGROUPS = UPD_THREADS / 128;      // warp quads: each covers the 128 TMEM lanes once
+constexpr int UPD_THREADS = 256;                  // the tensor-core layers assign roles to exactly eight warps
 constexpr int UPD_TM_MAX = 32;
 constexpr int UPD_STAGE_MAX = 12800;        // floats per staging buffer, two buffers (together the 100 KB tensor-core staging region)
 constexpr int UPD_STAGE_MIN = 4096;
@@ -340,27 +338,12 @@ __device__ __noinline__ unsigned fwd_layer_t(const float* __restrict__ W, const 
 
 
 // ---------------------------------------------------------------------------
-// Tensor-core forward layer (tcgen05, sm_100a) for the wide GEMM-shaped layers:
-//   out[m][n] = tanh(sum_k in[m][k] W[n][k] + b[n]),  N <= 128, K % 4 == 0
-// computed transposed on the 5th-generation tensor cores as  D[n][m] = W[n][:] . in[m][:]
-// (M = 128 weight rows, N = 32 samples, K in blocks of 32) with 3xTF32: every fp32 operand is split
-// into hi = rn_tf32(x) and lo = rn_tf32(x - hi) and hi*hi + lo*hi + hi*lo is accumulated in fp32 in
-// tensor memory.  The tensor core truncates when it adds into an accumulator, so the k-blocks go round
-// robin into four 64-column TMEM accumulators ([hi*hi | hi*lo], one N = 64 MMA) and lo*hi into a fifth;
-// they are added in registers in the epilogue.  Measured (tools/tc_probe.cu): max error 6.8e-6 at K = 500 against
-// 2.3e-5 for the fp32 FMA loop.
-//
-// Operands are staged by all threads (global/L2 -> registers -> split -> shared memory) into the
-// canonical K-major no-swizzle UMMA layout: 16-byte chunk (row r, chunk kc) at
-// (r/8)*SBO + kc*LBO + (r%8)*16 with LBO = 144 B (padded so the chunk stores are bank-conflict
-// free).  Two stage buffers; one thread issues the MMAs and commits them to an mbarrier that frees
-// the stage.  The epilogue reads TMEM with tcgen05.ld (lane = output feature, columns = samples).
+// tcgen05 building blocks shared by the tensor-core layers below.
+// Shared-memory operand tiles use the canonical K-major no-swizzle UMMA layout: 16-byte chunk (row r, chunk kc) at
+// (r/8)*SBO + kc*LBO + (r%8)*16 with LBO = 144 B (padded: chunk stores with kc fastest are bank-conflict free).
 // ---------------------------------------------------------------------------
 constexpr int TC_KB = 32;                                   // k-block: 32 floats = 8 chunks
 constexpr int TC_LBO = 144, TC_SBO = (TC_KB / 4) * TC_LBO;  // bytes
-constexpr int TC_A_BYTES = 16 * TC_SBO, TC_B_BYTES = 4 * TC_SBO;
-constexpr int TC_STAGE_FLOATS = (2 * TC_A_BYTES + 2 * TC_B_BYTES) / 4;      // 11520
-constexpr int TC_NACC = 4;                                  // 64-column accumulators [hi*hi | hi*lo] (+1 for lo*hi)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ uint32_t tc_off(int r, int kc) { return (r >> 3) * TC_SBO + kc * TC_LBO + (r & 7) * 16; }
@@ -368,36 +351,15 @@ __device__ __forceinline__ uint64_t tc_desc(uint32_t saddr) {
     return (uint64_t)((saddr >> 4) & 0x3fff) | ((uint64_t)(TC_LBO >> 4) << 16) | ((uint64_t)(TC_SBO >> 4) << 32) |
            ((uint64_t)1 << 46);                             // version 1, SWIZZLE_NONE, K-major
 }
-// round-to-nearest (ties away) split of an fp32 number into two tf32 numbers with integer ALU ops:
-// cvt.rna.tf32.f32 gives the same result but runs on the conversion pipe at 1/8 of the ALU rate, and
-// the split is the inner loop of the operand staging (checked against cvt.rna in tools/tc_probe.cu)
+// round-to-nearest (ties away) of an fp32 number to tf32 with integer ALU ops: cvt.rna.tf32.f32 gives the same
+// result but runs on the conversion pipe at 1/8 of the ALU rate (checked against cvt.rna in tools/tc_probe.cu)
 __device__ __forceinline__ float tc_rn_tf32(float x) {
     return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
 }
-__device__ __forceinline__ void tc_split(float x, float& hi, float& lo) {
-    hi = tc_rn_tf32(x);
-    lo = tc_rn_tf32(x - hi);
-}
-__device__ __forceinline__ void tc_store_split(char* hi_tile, char* lo_tile, int r, int kc, float4 x) {
-    float4 h, l;
-    tc_split(x.x, h.x, l.x); tc_split(x.y, h.y, l.y); tc_split(x.z, h.z, l.z); tc_split(x.w, h.w, l.w);
-    const uint32_t o = tc_off(r, kc);
-    *reinterpret_cast<float4*>(hi_tile + o) = h;
-    *reinterpret_cast<float4*>(lo_tile + o) = l;
-}
-__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}"
-        ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(0), "r"(0), "r"(0), "r"(0)
-        : "memory");
-}
-
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
 }
 
-// tcgen05.ld of NC (8 or 16) consecutive 32-bit columns of this warp's 32 TMEM lanes, waited for
 // tmem_ld_issue only starts the load: several can be in flight before one tmem_ld_wait
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 template <int NC>
@@ -428,170 +390,6 @@ __device__ __forceinline__ void tmem_ld(uint32_t taddr, uint32_t (&v)[NC]) {
                      : "r"(taddr));
     }
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// Warp 0 only issues the MMAs (one elected thread, as tcgen05 wants); warps 1-7 are producers that
-// split and stage the operands.  No block-wide barrier inside the k loop: producers signal a filled
-// stage on full[s] (one arrival per warp), the issuer waits for it, issues 12 MMAs and commits them to
-// empty[s], which producers wait on before they overwrite the stage two k-blocks later.
-constexpr int TC_PRODUCERS = UPD_THREADS - 32;
-
-template <bool TANH>
-__device__ __noinline__ unsigned fwd_layer_tc(const float* __restrict__ W, const float* __restrict__ bias, int N, int K,
-                                              const float* in, int ldin, float* out, int ldout, float* stage, int SF,
-                                              uint64_t* bars, unsigned ph, uint32_t tmem) {
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nkb = (K + TC_KB - 1) / TC_KB;
-    uint64_t* empty = bars + 2;                             // MMAs of a stage done   (ph bits 2, 3)
-    uint64_t* full = bars + 4;                              // stage filled            (ph bits 4, 5)
-    // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 32, M = 128
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-    __syncthreads();                                        // previous users of the stage buffers are done
-    if (warp == 0) {
-        // ---------------- MMA issuer ----------------
-        // descriptors of the four operand tiles of both stages, built once: inside the loop a k-step only
-        // adds a constant to the start-address field (one thread issues everything, so every instruction
-        // in this loop is on the critical path)
-        uint64_t dAh[2], dAl[2], dBh[2], dBl[2];
-#pragma unroll
-        for (int s = 0; s < 2; ++s) {
-            const uint32_t base = smem_u32(stage + (size_t)s * SF);
-            dAh[s] = tc_desc(base);
-            dAl[s] = tc_desc(base + TC_A_BYTES);
-            dBh[s] = tc_desc(base + 2 * TC_A_BYTES);
-            dBl[s] = tc_desc(base + 2 * TC_A_BYTES + TC_B_BYTES);
-        }
-        constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;       // start-address increment per 8 tf32
-        const uint32_t tcross = tmem + 64 * TC_NACC;
-        const uint32_t idesc64 = (idesc & ~(0x3fu << 17)) | ((uint32_t)(64 >> 3) << 17);
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb & 1;
-            mbar_wait(&full[s], (ph >> (4 + s)) & 1u);
-            ph ^= 1u << (4 + s);
-            if (lane == 0) {
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                // B_hi and B_lo tiles are adjacent, so ONE N = 64 MMA with A_hi produces hi*hi (columns
-                // 0-31) and hi*lo (columns 32-63): A_hi is read from shared memory once for both terms
-                const uint64_t ah = dAh[s], al = dAl[s], bb = dBh[s];
-                const uint32_t tmain = tmem + 64 * (kb % TC_NACC);
-                tc_mma(tmain, ah, bb, idesc64, kb >= TC_NACC ? 1u : 0u);
-                tc_mma(tcross, al, bb, idesc, kb ? 1u : 0u);
-#pragma unroll
-                for (int ks = 1; ks < TC_KB / 8; ++ks) {    // one MMA covers 8 tf32 = two chunks
-                    tc_mma(tmain, ah + ks * KSTEP, bb + ks * KSTEP, idesc64, 1u);
-                    tc_mma(tcross, al + ks * KSTEP, bb + ks * KSTEP, idesc, 1u);
-                }
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                                 smem_u32(&empty[s]))
-                             : "memory");
-            }
-            __syncwarp();
-        }
-        // bring the issuer's view of the empty barriers up to date (phases the producers consumed in the
-        // loop), then wait for the last commit of each stage like everybody else: `ph` ends up uniform
-        for (int kb = 2; kb < nkb; ++kb) ph ^= 1u << (2 + (kb & 1));
-        for (int kb = (nkb > 2 ? nkb - 2 : 0); kb < nkb; ++kb) {
-            const int s = kb & 1;
-            mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
-            ph ^= 1u << (2 + s);
-        }
-    } else {
-        // ---------------- producers ----------------
-        const int pt = tid - 32;                            // 0..223
-        constexpr int NCH = (1024 + TC_PRODUCERS - 1) / TC_PRODUCERS;     // A chunks per producer (5)
-        // per-thread constants of the staging loop: source pointer and tile offset of each chunk
-        const float* gp[NCH];
-        uint32_t so[NCH];
-        int kc4[NCH];
-#pragma unroll
-        for (int i = 0; i < NCH; ++i) {
-            const int e = pt + TC_PRODUCERS * i, r = e >> 3, kc = e & 7;
-            const bool ok = e < 1024 && r < N;
-            gp[i] = ok ? W + (size_t)r * K + 4 * kc : nullptr;
-            so[i] = tc_off(r & 127, kc);
-            kc4[i] = e < 1024 ? 4 * kc : K;                 // chunks beyond the tile are never stored
-        }
-        const int bkc = pt & 7;                             // B: chunks pt, pt + TC_PRODUCERS, ...
-        // weight chunks are fetched TWO k-blocks ahead (two register sets): one block of lead did not
-        // cover the L2 latency
-        float4 preA[NCH], preB[NCH];
-        auto prefetch = [&](float4 (&pre)[NCH], int kb) {
-#pragma unroll
-            for (int i = 0; i < NCH; ++i)
-                pre[i] = (gp[i] != nullptr && kb * TC_KB + kc4[i] < K) ? __ldg(reinterpret_cast<const float4*>(gp[i] + kb * TC_KB))
-                                                                        : make_float4(0.f, 0.f, 0.f, 0.f);
-        };
-        prefetch(preA, 0);
-        if (nkb > 1) prefetch(preB, 1);
-#pragma unroll 2
-        for (int kb = 0; kb < nkb; ++kb) {
-            const int s = kb & 1;
-            float4 (&pre)[NCH] = (kb & 1) ? preB : preA;
-            char* base = reinterpret_cast<char*>(stage + (size_t)s * SF);
-            char *Ah = base, *Al = base + TC_A_BYTES, *Bh = base + 2 * TC_A_BYTES, *Bl = Bh + TC_B_BYTES;
-            if (kb >= 2) {                                  // the MMAs of k-block kb-2 have read this stage
-                mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
-                ph ^= 1u << (2 + s);
-            }
-#pragma unroll
-            for (int i = 0; i < NCH; ++i) {
-                if (i < NCH - 1 || pt + TC_PRODUCERS * i < 1024) {
-                    float4 h, l;
-                    tc_split(pre[i].x, h.x, l.x); tc_split(pre[i].y, h.y, l.y);
-                    tc_split(pre[i].z, h.z, l.z); tc_split(pre[i].w, h.w, l.w);
-                    *reinterpret_cast<float4*>(Ah + so[i]) = h;
-                    *reinterpret_cast<float4*>(Al + so[i]) = l;
-                }
-            }
-#pragma unroll
-            for (int e = pt; e < 8 * UPD_ROWS; e += TC_PRODUCERS) {     // the 256 B chunks (TC_PRODUCERS % 8 == 0)
-                const int k = kb * TC_KB + 4 * bkc, m = e >> 3;
-                const float4 x = (k < K) ? *reinterpret_cast<const float4*>(in + m * ldin + k) : make_float4(0.f, 0.f, 0.f, 0.f);
-                tc_store_split(Bh, Bl, m, bkc, x);
-            }
-            if (kb + 2 < nkb) prefetch(pre, kb + 2);        // lands while the next block is staged
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> tensor-core reads
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&full[s]);           // one arrival per producer warp
-        }
-        // drain: wait for the last commits (they cover every MMA issued), keeps `ph` equal to the issuer's
-        for (int kb = (nkb > 2 ? nkb - 2 : 0); kb < nkb; ++kb) {
-            const int s = kb & 1;
-            mbar_wait(&empty[s], (ph >> (2 + s)) & 1u);
-            ph ^= 1u << (2 + s);
-        }
-        for (int kb = 0; kb < nkb; ++kb) ph ^= 1u << (4 + (kb & 1));       // phases the issuer consumed
-    }
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    // epilogue: warp w owns TMEM lanes 32*(w%4)..+31 (= output features) and the EC samples of its warp quad
-    {
-        constexpr int EC = UPD_ROWS / UPD_WGROUPS;          // 16 (8 warps) or 8 (16 warps)
-        const int n = 32 * (warp & 3) + lane, c0 = (warp >> 2) * EC;
-        float sum[EC];
-#pragma unroll
-        for (int j = 0; j < EC; ++j) sum[j] = 0.f;
-        const int nacc = nkb < TC_NACC ? nkb : TC_NACC;
-        // small terms first: lo*hi, then the hi*lo halves, then the hi*hi halves of the accumulators
-        for (int t = 0; t < 1 + 2 * nacc; ++t) {
-            const uint32_t col = (t == 0) ? 64 * TC_NACC : (t <= nacc ? 64 * (t - 1) + 32 : 64 * (t - 1 - nacc));
-            uint32_t v[EC];
-            tmem_ld<EC>(tmem + ((uint32_t)(32 * (warp & 3)) << 16) + col + c0, v);
-#pragma unroll
-            for (int j = 0; j < EC; ++j) sum[j] += __uint_as_float(v[j]);
-        }
-        if (n < N) {
-            const float bb = __ldg(bias + n);
-#pragma unroll
-            for (int j = 0; j < EC; ++j) {
-                float y = sum[j] + bb;
-                if (TANH) y = tanh_act(y);
-                out[(c0 + j) * ldout + n] = y;
-            }
-        }
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    return ph;
 }
 
 // ---------------------------------------------------------------------------
@@ -677,37 +475,31 @@ __device__ __forceinline__ void first_layers_prefetch(float* stage, const float*
 }
 
 // ---------------------------------------------------------------------------
-// Tensor-core layers, second generation: the big operand (weights) goes through TENSOR MEMORY.
-//   weights:  global --TMA 2D tile, zero-filled out of bounds--> raw fp32 tile in shared memory
-//             --LDS (thread = TMEM lane), hi/lo split in registers, tcgen05.st--> A_hi | A_lo in tensor memory
-//   samples:  the small operand (32 rows), split into K-major no-swizzle tiles [X_hi | X_lo] in shared memory
-//   MMAs:     per k-step (8 k)  acc[ks] += A_hi x [X_hi | X_lo]  (N = 64: hi*hi | hi*lo), then
-//             acc[ks][32..63] += A_lo x X_hi  (N = 32), four rotating accumulators (the tensor core truncates
-//             when it accumulates; a dependent MMA also costs ~90 cycles, tools/mma_rate.cu)
-// Shared-memory traffic per k-block is 16 KB (TMA) + 16 KB (LDS) + the 32-sample tiles, against 64 KB when both
-// split operands are staged in shared memory; the weight rows never pass through registers of more than one
-// thread.  Warp roles (tools/tc_ts_probe.cu): warps 0-3 transform (warp = TMEM lane quadrant), warps 4-6
-// stage the samples, warp 7 issues TMA refills and MMAs (whole warp, warp-uniform operands, one elected lane:
-// ptxas then keeps the descriptors in uniform registers and emits the MMAs back to back).
-// Barrier rings (initialised once per kernel; `ph` carries one parity bit per barrier, bits 8..19):
-//   raw_full[TS_NS]   TMA tile landed                (count 1 + tx bytes)
-//   a_full[TS_NSA]    A in TMEM and B in smem ready  (count 7: four transform warps + three sample warps)
-//   mma_done[TS_NSA]  MMAs of the stage finished     (tcgen05.commit)
+// Tensor-core layers: the big operand goes through TENSOR MEMORY (tcgen05.mma with A in TMEM, B in shared memory).
+//   big operand:    global --TMA 2D tile, zero-filled out of bounds--> raw fp32 tile in shared memory (or, for the
+//                   activation operands of the dW layers, straight from the activations in shared memory)
+//                   --LDS (thread = TMEM lane), hi/lo split in registers, tcgen05.st--> A_hi | A_lo in tensor memory
+//   small operand:  32 samples (or <= 128 output features for dW), split into K-major no-swizzle tiles [hi | lo]
+//   MMAs:           per k-step (8 k)  acc += A_hi x [B_hi | B_lo]  (hi*hi | hi*lo in adjacent columns), then
+//                   acc[hi*lo half] += A_lo x B_hi: 3xTF32, fp32 accumulation in tensor memory.  The tensor core
+//                   truncates when it accumulates, so long reductions rotate over four accumulators; a dependent
+//                   MMA also waits ~90 cycles (tools/mma_rate.cu), so consecutive MMAs go to different ones.
+// Shared-memory traffic per k-block is 16 KB (TMA) + 16 KB (LDS) + the 32-sample tiles, against 64 KB when both split
+// operands are staged in shared memory, and no weight passes through more than one thread's registers.
+// Issue rules found the hard way (tools/mma_rate.cu, tools/tc_ts_probe.cu): tcgen05.mma / commit / the TMA copy are
+// executed by a whole converged warp with elect.sync right next to the instruction - a lane-0 branch or a predicate
+// handed in from elsewhere makes ptxas wrap each one in a per-thread loop (60-80 cycles per MMA instead of N/2);
+// every branch in an eight-warp CTA costs tens of cycles, so epilogues and issue sequences are straight-line.
 // ---------------------------------------------------------------------------
-constexpr int TS_NS = 4, TS_NSA = 4;
-constexpr int TS_RAW_BYTES = 128 * TC_KB * 4;               // 16 KB
+constexpr int TS_RAW_BYTES = 128 * TC_KB * 4;               // 16 KB: one raw weight tile
 constexpr int TS_BT_BYTES = 4 * TC_SBO;                     // one 32-row sample tile (hi or lo)
-constexpr int TS_BYTES = TS_NS * TS_RAW_BYTES + TS_NSA * 2 * TS_BT_BYTES;   // 102 400
-constexpr int TS_TM_A = 256;                                // TMEM: 4 x 64 accumulator columns, then TS_NSA x 64 A columns
-constexpr int TS_BAR0 = 6;                                  // first ring barrier in the barrier array
-constexpr int TS_PH_RAW = 8, TS_PH_AF = 12, TS_PH_MD = 16;  // parity bits in `ph`
+constexpr int TS_BYTES = 4 * TS_RAW_BYTES + 4 * 2 * TS_BT_BYTES;   // 102 400: two ring slots of two k-blocks each
+constexpr int TS_TM_A = 256;                                // TMEM: 4 x 64 accumulator columns, then 256 A columns
+constexpr int TS_BAR0 = 2;                                  // first pipeline barrier in the barrier array (0, 1: FP32-path stages)
+constexpr int TS_NBARS = 10;                                // raw_full[2] +0, raw_free[2] +2, a_full[2] +4, mma_done[2] +8
+constexpr int TS_PH_RAW = 8, TS_PH_AF = 12, TS_PH_MD = 16;  // parity bits in `ph` (raw_free: TS_PH_RF = 10)
 
-__device__ __forceinline__ uint32_t elect_one() {
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
-    return pred;
-}
-// D[tmem] (+)= A[tmem] * B[smem descriptor]; whole warp executes it with uniform operands, `elected` picks the lane
+// D[tmem] (+)= A[tmem] * B[smem descriptor]
 __device__ __forceinline__ void ts_mma(uint32_t d, uint32_t a, uint64_t b, uint32_t idesc, uint32_t acc, uint32_t enable) {
     // executed by a whole converged warp with warp-uniform operands; elect.sync sits next to the MMA so that ptxas sees
     // a single issuing lane (a predicate that arrives from elsewhere makes it wrap the MMA in a per-thread loop)
@@ -732,10 +524,6 @@ __device__ __forceinline__ void tma_pair_elect(uint32_t dst0, uint32_t dst1, con
         "@e cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%2, {%4, %5}], [%3];\n\t"
         "@t cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2, {%6, %7}], [%3];\n\t}"
         ::"r"(dst0), "r"(dst1), "l"(map), "r"(bar), "r"(a0), "r"(b0), "r"(a1), "r"(b1), "r"(bytes), "r"(two) : "memory");
-}
-__device__ __forceinline__ void tma_tile_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
 }
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
@@ -798,7 +586,7 @@ constexpr int TS_PH_RF = 10;
 template <bool DX>
 __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* __restrict__ bias, int N, int K,
                                           const float* bsrc, int ldb, float* dst, int ldo, unsigned char* ts, uint64_t* bars,
-                                          unsigned ph, uint32_t tmem, uint32_t /*elected*/) {
+                                          unsigned ph, uint32_t tmem) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int R = DX ? N : K;                               // reduction length
     const int nrb = (R + TC_KB - 1) / TC_KB;                // k-blocks per tile
@@ -1003,10 +791,10 @@ __device__ __forceinline__ unsigned char* first_b_tiles(float* stage, const dppo
 }
 __device__ __noinline__ unsigned fwd_first_ts(const float* Ws, const float* __restrict__ bias, int N, int K, const float* in,
                                               int ldin, float* out, int ldout, unsigned char* bt, uint64_t* bars, unsigned ph,
-                                              uint32_t tmem, uint32_t /*elected*/) {
+                                              uint32_t tmem) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ntiles = (N + 127) >> 7, nks = (K + 7) >> 3;
-    uint64_t* mma_done = bars + TS_BAR0 + TS_NS + TS_NSA;
+    uint64_t* mma_done = bars + TS_BAR0 + 8;
     float bb[4];                                            // biases of my output feature in each tile: fetched now, used in the epilogue
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
@@ -1083,10 +871,10 @@ __device__ __noinline__ unsigned fwd_first_ts(const float* Ws, const float* __re
 // dW / db of a first layer (see above).  img: N*K floats of shared memory (the flat image is flushed coalesced).
 __device__ __noinline__ unsigned dw_first_ts(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut,
                                              int ldd, const float* in, int ldin, bool accumulate, float* img, unsigned char* bt,
-                                             uint64_t* bars, unsigned ph, uint32_t tmem, uint32_t /*elected*/) {
+                                             uint64_t* bars, unsigned ph, uint32_t tmem) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int ntiles = (N + 127) >> 7;
-    uint64_t* mma_done = bars + TS_BAR0 + TS_NS + TS_NSA;
+    uint64_t* mma_done = bars + TS_BAR0 + 8;
     __syncthreads();                                        // staging region free, dOut complete
     // ---- B = x^T: row k (< 32), chunk kc = samples 4kc..4kc+3 ----
     {
@@ -1183,12 +971,10 @@ __device__ __noinline__ unsigned dw_first_ts(float* __restrict__ gW, float* __re
 template <bool TANH>
 __device__ __forceinline__ unsigned fwd_layer(const float* __restrict__ W, const float* __restrict__ bias, int N, int K,
                                           const float* in, int ldin, float* out, int ldout, float* stage, int SF,
-                                          uint64_t* bars, unsigned ph, uint32_t tmem, const CUtensorMap* wmap, uint32_t elected) {
+                                          uint64_t* bars, unsigned ph, uint32_t tmem, const CUtensorMap* wmap) {
     // wide GEMM-shaped layers go to the tensor cores (tcgen05), the rest stays on the FP32 pipe
     if (wmap != nullptr && N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0)
-        return ts_layer<false>(wmap, bias, N, K, in, ldin, out, ldout, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
-    if (N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0 && SF >= TC_STAGE_FLOATS)
-        return fwd_layer_tc<TANH>(W, bias, N, K, in, ldin, out, ldout, stage, SF, bars, ph, tmem);
+        return ts_layer<false>(wmap, bias, N, K, in, ldin, out, ldout, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
     // 4*CN columns per warp: 28 fits N = 100 (reference widths) in four blocks, 32 otherwise
     const int blocks32 = (N + 31) / 32;
     if (N > 28 * (blocks32 - 1) && N <= 28 * blocks32 && blocks32 <= 8)
@@ -1363,9 +1149,9 @@ __device__ __noinline__ unsigned dx_layer_t(const float* __restrict__ W, int N, 
 
 __device__ __forceinline__ unsigned dx_layer(const float* __restrict__ W, int N, int K, const float* dOut, int ldd,
                                          float* act, int lda, float* stage, int SF, uint64_t* bars, unsigned ph,
-                                         const CUtensorMap* xmap, uint32_t tmem, uint32_t elected) {
+                                         const CUtensorMap* xmap, uint32_t tmem) {
     if (xmap != nullptr && N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0)   // = ts_eligible() on the host
-        return ts_layer<true>(xmap, nullptr, N, K, dOut, ldd, act, lda, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
+        return ts_layer<true>(xmap, nullptr, N, K, dOut, ldd, act, lda, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
     const int KQ = (K + 3) >> 2;
     if (KQ > UPD_THREADS / 4) return dx_layer_t<4>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
     if (KQ > UPD_THREADS / 8) return dx_layer_t<2>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
@@ -1550,122 +1336,6 @@ __device__ __noinline__ void dw_layer_smallk(float* __restrict__ gW, float* __re
 }
 
 
-// ---------------------------------------------------------------------------
-// Tensor-core dW (tcgen05) for the wide layers:  dW[n][k] = sum_s dOut[s][n] in[s][k],  s < 32 samples.
-//   D_t[128 n][128 k] = A[n][s] . B_t[k][s]^T,  K_mma = 32 samples = four k-steps, 3xTF32 into ONE
-// 128-column accumulator per k-tile (only 12 accumulations, so a single accumulator is accurate);
-// up to four k-tiles live in the 512 TMEM columns at once and are drained in one epilogue.
-// Both operands are TRANSPOSED activations, gathered from shared memory (4 scalar loads per chunk)
-// by the producer warps: A = dOut^T (staged once), B_t = in^T tile (staged per tile, single buffer).
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ void tc_stage_transposed(char* hi_tile, char* lo_tile, const float* src, int ld, int col0,
-                                                    int ncols, int pt) {
-    // 128 rows (columns col0..col0+127 of src) x 8 chunks (samples 4kc..4kc+3); rows >= ncols are zero
-    for (int e = pt; e < 1024; e += TC_PRODUCERS) {
-        const int r = e & 127, kc = e >> 7;                 // consecutive lanes -> consecutive columns of src
-        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (col0 + r < ncols) {
-            const float* p = src + (4 * kc) * ld + col0 + r;
-            x = make_float4(p[0], p[ld], p[2 * ld], p[3 * ld]);
-        }
-        tc_store_split(hi_tile, lo_tile, r, kc, x);
-    }
-}
-
-__device__ __noinline__ unsigned dw_layer_tc(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut,
-                                             int ldd, const float* in, int ldin, bool accumulate, float* stage, int SF,
-                                             uint64_t* bars, unsigned ph, uint32_t tmem) {
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    uint64_t* empty = bars + 2;                             // stage 0's pair of barriers is enough here
-    uint64_t* full = bars + 4;
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-    char* Abase = reinterpret_cast<char*>(stage);
-    char* Bbase = reinterpret_cast<char*>(stage + SF);
-    const int ntiles = (K + 127) >> 7;
-    __syncthreads();                                        // stage buffers free, dOut / in complete
-    for (int t0 = 0; t0 < ntiles; t0 += 4) {                // groups of four k-tiles = 512 TMEM columns
-        const int nt = min(4, ntiles - t0);
-        if (warp == 0) {
-            uint32_t adA = smem_u32(Abase), adB = smem_u32(Bbase);
-            const uint64_t ah = tc_desc(adA), al = tc_desc(adA + TC_A_BYTES);
-            const uint64_t bh = tc_desc(adB), bl = tc_desc(adB + TC_A_BYTES);
-            constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
-            for (int t = 0; t < nt; ++t) {
-                mbar_wait(&full[0], (ph >> 4) & 1u);
-                ph ^= 1u << 4;
-                if (lane == 0) {
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t d = tmem + 128 * t;
-#pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
-                        tc_mma(d, al + ks * KSTEP, bh + ks * KSTEP, idesc, ks ? 1u : 0u);
-                        tc_mma(d, ah + ks * KSTEP, bl + ks * KSTEP, idesc, 1u);
-                        tc_mma(d, ah + ks * KSTEP, bh + ks * KSTEP, idesc, 1u);
-                    }
-                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                                     smem_u32(&empty[0]))
-                                 : "memory");
-                }
-                __syncwarp();
-            }
-            for (int t = 1; t < nt; ++t) ph ^= 1u << 2;     // empty phases the producers consumed in their loop
-            mbar_wait(&empty[0], (ph >> 2) & 1u);           // last commit: everything is in TMEM
-            ph ^= 1u << 2;
-        } else {
-            const int pt = tid - 32;
-            for (int t = 0; t < nt; ++t) {
-                if (t == 0) {
-                    if (t0 == 0) tc_stage_transposed(Abase, Abase + TC_A_BYTES, dOut, ldd, 0, N, pt);
-                } else {
-                    mbar_wait(&empty[0], (ph >> 2) & 1u);   // MMAs of the previous tile have read the B buffer
-                    ph ^= 1u << 2;
-                }
-                tc_stage_transposed(Bbase, Bbase + TC_A_BYTES, in, ldin, 128 * (t0 + t), K, pt);
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&full[0]);
-            }
-            mbar_wait(&empty[0], (ph >> 2) & 1u);
-            ph ^= 1u << 2;
-            for (int t = 0; t < nt; ++t) ph ^= 1u << 4;     // full phases the issuer consumed
-        }
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        // epilogue: lane = n; each warp quad takes an equal share of the group's 512 columns
-        {
-            const int n = 32 * (warp & 3) + lane;
-            constexpr int CW = 512 / UPD_WGROUPS;
-            const int cbeg = (warp >> 2) * CW;
-            for (int c0 = cbeg; c0 < cbeg + CW && c0 < nt * 128; c0 += 16) {
-                uint32_t v[16];
-                tmem_ld<16>(tmem + ((uint32_t)(32 * (warp & 3)) << 16) + c0, v);
-                const int k0 = 128 * t0 + c0;
-                if (n < N) {
-#pragma unroll
-                    for (int j = 0; j < 16; j += 4) {
-                        if (k0 + j < K) {                   // K % 4 == 0
-                            float4 o = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
-                                                   __uint_as_float(v[j + 3]));
-                            float4* dst = reinterpret_cast<float4*>(gW + (size_t)n * K + k0 + j);
-                            if (accumulate) { const float4 p = *dst; o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
-                            *dst = o;
-                        }
-                    }
-                }
-            }
-        }
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();                                    // TMEM and the B buffer are free for the next group
-    }
-    for (int n = tid; n < N; n += UPD_THREADS) {
-        float sb = 0.f;
-        for (int m = 0; m < 32; ++m) sb += dOut[m * ldd + n];
-        gb[n] = accumulate ? gb[n] + sb : sb;
-    }
-    __syncthreads();
-    return ph;
-}
-
-
 // dW of a wide layer on the tensor cores, operands through tensor memory:
 //   dW[n][k] (+)= sum_s dOut[s][n] in[s][k]      D[k][n] = A[k][s] . B[n][s]^T  per tile of 128 k
 //   A = in^T: TMEM lane = k, columns = the 32 samples (read down a column of the activations, conflict-free)
@@ -1676,11 +1346,11 @@ __device__ __noinline__ unsigned dw_layer_tc(float* __restrict__ gW, float* __re
 // epilogue - 2 Np columns of tensor memory and N x 128 floats to global memory - dominates.
 __device__ __noinline__ unsigned dw_layer_ts(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut,
                                              int ldd, const float* in, int ldin, bool accumulate, unsigned char* ts,
-                                             uint64_t* bars, unsigned ph, uint32_t tmem, uint32_t /*elected*/) {
+                                             uint64_t* bars, unsigned ph, uint32_t tmem) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int Np = (N + 15) & ~15;
     const int ntiles = (K + 127) >> 7;
-    uint64_t* mma_done = bars + TS_BAR0 + TS_NS + TS_NSA;
+    uint64_t* mma_done = bars + TS_BAR0 + 8;
     __syncthreads();                                        // staging region free, dOut / in complete
     K2_ACC_DECL;
     K2_ACC_T0;
@@ -1822,7 +1492,7 @@ __device__ __noinline__ void heads_dw(float* __restrict__ gWmu, float* __restric
 // `next`: the network whose first layers are prefetched into the staging region while this one's heads run
 __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, const UpdArgs& P, float* S, float* mu_out,
                                             float* v_out, int tick, unsigned ph, uint32_t tmem, const CUtensorMap* maps,
-                                            uint32_t elected, const Net* next) {
+                                            const Net* next) {
     const dppo_dims& d = P.d;
     float* stage = S + P.o_stage;
     uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
@@ -1830,31 +1500,26 @@ __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, 
         mbar_wait(&bars[0], ph & 1u);                       // this network's W1 and V1 have landed (prefetched)
         ph ^= 1u;
         if (P.first_ts && d.H1 <= 512)
-            ph = fwd_first_ts(stage, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, first_b_tiles(stage, d), bars, ph, tmem, elected);
+            ph = fwd_first_ts(stage, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, first_b_tiles(stage, d), bars, ph, tmem);
         else if (d.H1 <= 128) fwd_small_k<4>(stage, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1);
         else fwd_small_k<8>(stage, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1);
         K2_TICK(tick + 0);
         if (P.first_ts && d.G1 <= 512)
-            ph = fwd_first_ts(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, first_b_tiles(stage, d), bars, ph, tmem, elected);
+            ph = fwd_first_ts(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, first_b_tiles(stage, d), bars, ph, tmem);
         else if (d.G1 <= 128) fwd_small_k<4>(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1);
         else fwd_small_k<8>(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1);
         K2_TICK(tick + 1);
     } else {
-        ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, tmem, nullptr, elected);
+        ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, tmem, nullptr);
         K2_TICK(tick + 0);
-        ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, tmem, nullptr, elected);
+        ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, tmem, nullptr);
         K2_TICK(tick + 1);
     }
     ph = fwd_layer<true>(nw.W2, nw.b2, d.H2, d.H1, S + P.o_h1, P.ldH1, S + P.o_h2, P.ldH2, stage, P.SF, bars, ph, tmem,
-                         maps ? maps + 0 : nullptr, elected);
+                         maps ? maps + 0 : nullptr);
     K2_TICK(tick + 2);
     ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph, tmem,
-                         maps ? maps + 1 : nullptr, elected);
-#ifdef DPPO_K2_TWICE
-    K2_TICK(tick + 2);                                      // experiment: the same layer again, instruction cache warm
-    ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph, tmem,
-                         maps ? maps + 1 : nullptr, elected);
-#endif
+                         maps ? maps + 1 : nullptr);
     K2_TICK(tick + 3);
     if (P.small_first && next != nullptr) first_layers_prefetch(stage, next->W1, next->V1, d, &bars[0]);
     heads_fwd(hs, d.A, d.H2, d.G2, S + P.o_h2, P.ldH2, S + P.o_g2, P.ldG2, mu_out, P.ldA, v_out);
@@ -1889,10 +1554,6 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         uint64_t* b = reinterpret_cast<uint64_t*>(S + P.o_bars);
         mbar_init(&b[0], 1);                               // weight stage buffers (TMA bulk copies)
         mbar_init(&b[1], 1);
-        mbar_init(&b[2], 1);                               // tensor-core stages: MMAs done (tcgen05.commit)
-        mbar_init(&b[3], 1);
-        mbar_init(&b[4], UPD_THREADS / 32 - 1);            // tensor-core stages: filled, one arrival per producer warp
-        mbar_init(&b[5], UPD_THREADS / 32 - 1);
         for (int i = 0; i < 2; ++i) {
             mbar_init(&b[TS_BAR0 + i], 1);                  // raw_full (TMA tx)
             mbar_init(&b[TS_BAR0 + 2 + i], 4);              // raw_free: the four transform warps
@@ -1902,7 +1563,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     // tensor memory: all 512 columns (one CTA per SM), 9 accumulators of 32 columns are used
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(S + P.o_bars + 2 * (TS_BAR0 + TS_NS + 2 * TS_NSA));
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(S + P.o_bars + 2 * (TS_BAR0 + TS_NBARS));
     if (threadIdx.x < 32) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
@@ -1911,7 +1572,6 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot;
-    const uint32_t elected = elect_one();
     unsigned ph = 0;
     // head weights of both networks stay in shared memory for the whole kernel
     // (when shared memory is tight - Humanoid with 256-wide nets - they are read from global memory instead)
@@ -1971,9 +1631,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         // theta_old == theta and the old network's outputs are the new network's, bit for bit
         if (run_old) {
             const Net no = net_of(P.theta_old, P.lay);
-            ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr, elected, &nw);              // train.py:142
+            ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr, &nw);              // train.py:142
         }
-        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr, elected, nullptr);                    // train.py:145 / ppo.py:148
+        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr, nullptr);                    // train.py:145 / ppo.py:148
         if (same_old) {
             for (int e = threadIdx.x; e < UPD_ROWS * P.ldA; e += UPD_THREADS) S[P.o_muo + e] = S[P.o_mu + e];
             for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
@@ -2123,17 +1783,15 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         K2_TICK(16);
         if (P.use_ts && d.H2 <= 128 && d.H2 >= 32 && d.H1 >= 64 && (d.H1 & 3) == 0)
             ph = dw_layer_ts(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc,
-                             reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
-        else if (d.H2 <= 128 && d.H2 >= 32 && d.H1 >= 64 && (d.H1 & 3) == 0 && P.SF >= TC_STAGE_FLOATS)
-            ph = dw_layer_tc(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc, stage, P.SF, bars, ph, tmem);
+                             reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
         else
             dw_layer(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc);
         K2_TICK(17);
         ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph,
-                      P.use_ts ? &P.map_dx[0] : nullptr, tmem, elected);  // h1 <- dz1
+                      P.use_ts ? &P.map_dx[0] : nullptr, tmem);  // h1 <- dz1
         K2_TICK(18);
         if (P.first_ts && d.H1 <= 512)
-            ph = dw_first_ts(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem, elected);
+            ph = dw_first_ts(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem);
         else if (d.O <= 24 && d.H1 >= 256 && d.H1 * d.O <= P.SF) dw_layer_smallk(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage);
         else dw_layer(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc);
         K2_TICK(19);
@@ -2143,17 +1801,15 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         K2_TICK(21);
         if (P.use_ts && d.G2 <= 128 && d.G2 >= 32 && d.G1 >= 64 && (d.G1 & 3) == 0)
             ph = dw_layer_ts(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc,
-                             reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, elected);
-        else if (d.G2 <= 128 && d.G2 >= 32 && d.G1 >= 64 && (d.G1 & 3) == 0 && P.SF >= TC_STAGE_FLOATS)
-            ph = dw_layer_tc(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc, stage, P.SF, bars, ph, tmem);
+                             reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
         else
             dw_layer(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc);
         K2_TICK(22);
         ph = dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph,
-                      P.use_ts ? &P.map_dx[1] : nullptr, tmem, elected);
+                      P.use_ts ? &P.map_dx[1] : nullptr, tmem);
         K2_TICK(23);
         if (P.first_ts && d.G1 <= 512)
-            ph = dw_first_ts(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem, elected);
+            ph = dw_first_ts(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem);
         else if (d.O <= 24 && d.G1 >= 256 && d.G1 * d.O <= P.SF) dw_layer_smallk(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage);
         else dw_layer(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc);
         K2_TICK(24);
@@ -2244,7 +1900,7 @@ int plan(UpdArgs& P) {
     P.o_lpo = take(TM);
     P.o_zero_end = o;                           // everything before this is zeroed per tile
     P.o_red = take(UPD_THREADS);
-    P.o_bars = take(2 * (TS_BAR0 + TS_NS + 2 * TS_NSA) + 4);   // the mbarriers (8 bytes each) + the TMEM base address
+    P.o_bars = take(2 * (TS_BAR0 + TS_NBARS) + 4);   // the mbarriers (8 bytes each) + the TMEM base address
     P.head_floats = (d.A * P.ldH2 + ((d.A + 3) & ~3) + P.ldG2 + 4 + 3) & ~3;
     // head weights resident in shared memory unless that would squeeze the stage buffers below their
     // minimum (then they are read from global memory, which needs 16-byte aligned rows)
