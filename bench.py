@@ -53,6 +53,15 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def tensor_peak_tf32():
+    """Dense TF32 tensor-core ceiling in TFLOP/s: half of the measured dense bf16 figure (same MMA unit, twice the
+    operand width); the burst figure, K2 is timed alone."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return 0.5 * float(json.load(open(p))["bf16_tflops"]), "0.5 x measured dense bf16 (MEASURED_PEAKS.json)"
+    return 0.5 * 2250.0, "0.5 x nominal dense bf16 (B200_PROFILING.md)"
+
+
 class ClockSampler(threading.Thread):
     """SM clock and throttle reasons during the timed region (NVML, 5 ms period)."""
 
@@ -301,10 +310,18 @@ def main():
     roofline = {
         "kernel": "update_fused_kernel (K2)", "bound": "hbm", "achieved": k2_bytes / k2_s / 1e9, "peak": hbm_peak,
         "unit": "GB/s", "frac": k2_bytes / k2_s / 1e9 / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-        "note": "K2 is bound by the FP32 FMA pipe (%.0f FLOP per algorithmic byte), not HBM: see 'compute'"
+        "note": "K2 does %.0f FLOP per algorithmic byte, so HBM is not its bound; its layers run on the tensor cores as "
+                "3xTF32 (three MMA flops per algorithmic flop) with 28 samples = 32 MMA columns per SM, and the kernel is "
+                "latency bound (eight warps per SM, profiles/r01e_k2_summary.md): see 'compute' and 'tensor'"
                 % (k2_flops / k2_bytes),
         "compute": {"bound": "fp32_fma", "achieved": k2_flops / k2_s / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
-                    "frac": k2_flops / k2_s / 1e12 / fp32_peak, "peak_source": "dppo_fp32_probe, measured in this run"},
+                    "frac": k2_flops / k2_s / 1e12 / fp32_peak, "peak_source": "dppo_fp32_probe, measured in this run",
+                    "note": "algorithmic fp32 flops against the FP32 FMA pipe, the ceiling of a CUDA-core implementation"},
+        "tensor": {"bound": "tensor", "achieved": 3.0 * k2_flops / k2_s / 1e12, "peak": tensor_peak_tf32()[0],
+                   "unit": "TFLOP/s", "frac": 3.0 * k2_flops / k2_s / 1e12 / tensor_peak_tf32()[0],
+                   "peak_source": tensor_peak_tf32()[1],
+                   "note": "3xTF32 MMA flops; an MMA with N = 32..64 columns occupies the unit as long as its 128 rows "
+                           "need, so 25-50 % of this peak is the most this tiling can reach"},
         "share_of_step": wl["E"] * kt["k2_us"] / (t_ms / args.steps * 1e3),
         "kernels": {
             "k2_update_fused": {"us": kt["k2_us"], "launches_per_step": wl["E"]},
