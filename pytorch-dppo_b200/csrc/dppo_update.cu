@@ -1772,46 +1772,47 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         __syncthreads();
 
         K2_TICK(14);
-        // ---- backward, policy trunk -------------------------------------------------------------
+        // ---- backward ---------------------------------------------------------------------------
         const bool acc = !first;
         float* stage = S + P.o_stage;
         uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
         heads_dw(go.Wmu, go.bmu, go.Wv, go.bv, d.A, d.H2, d.G2, S + P.o_dmu, P.ldA, S + P.o_dv, S + P.o_h2, P.ldH2,
                  S + P.o_g2, P.ldG2, acc);
         K2_TICK(15);
+        // The two trunks are independent, so every layer routine runs for both of them back to back: its code is
+        // fetched once (the routines together do not fit the 32 KB instruction cache).
         head_dx(hs_new.Wmu, hs_new.ldw, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2);          // h2 <- dz2
         K2_TICK(16);
+        head_dx(hs_new.Wv, 0, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);                          // g2 <- dz2 (value)
+        K2_TICK(17);
         if (P.use_ts && d.H2 <= 128 && d.H2 >= 32 && d.H1 >= 64 && (d.H1 & 3) == 0)
             ph = dw_layer_ts(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc,
                              reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
         else
             dw_layer(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc);
-        K2_TICK(17);
-        ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph,
-                      P.use_ts ? &P.map_dx[0] : nullptr, tmem);  // h1 <- dz1
         K2_TICK(18);
-        if (P.first_ts && d.H1 <= 512)
-            ph = dw_first_ts(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem);
-        else if (d.O <= 24 && d.H1 >= 256 && d.H1 * d.O <= P.SF) dw_layer_smallk(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage);
-        else dw_layer(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc);
-        K2_TICK(19);
-        // ---- backward, value trunk --------------------------------------------------------------
-        K2_TICK(20);
-        head_dx(hs_new.Wv, 0, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);
-        K2_TICK(21);
         if (P.use_ts && d.G2 <= 128 && d.G2 >= 32 && d.G1 >= 64 && (d.G1 & 3) == 0)
             ph = dw_layer_ts(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc,
                              reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
         else
             dw_layer(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc);
-        K2_TICK(22);
+        K2_TICK(19);
+        ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph,
+                      P.use_ts ? &P.map_dx[0] : nullptr, tmem);                                     // h1 <- dz1
+        K2_TICK(20);
         ph = dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph,
-                      P.use_ts ? &P.map_dx[1] : nullptr, tmem);
-        K2_TICK(23);
+                      P.use_ts ? &P.map_dx[1] : nullptr, tmem);                                     // g1 <- dz1 (value)
+        K2_TICK(21);
+        if (P.first_ts && d.H1 <= 512)
+            ph = dw_first_ts(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem);
+        else if (d.O <= 24 && d.H1 >= 256 && d.H1 * d.O <= P.SF) dw_layer_smallk(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage);
+        else dw_layer(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc);
+        K2_TICK(22);
         if (P.first_ts && d.G1 <= 512)
             ph = dw_first_ts(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem);
         else if (d.O <= 24 && d.G1 >= 256 && d.G1 * d.O <= P.SF) dw_layer_smallk(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage);
         else dw_layer(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc);
+        K2_TICK(23);
         K2_TICK(24);
     }
 

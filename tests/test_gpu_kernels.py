@@ -329,6 +329,33 @@ def test_update_epoch0_ratio_is_one(nv):
         assert_close_scaled(got[k], grads[k], 1e-5, k)
 
 
+@pytest.mark.parametrize("flavour_name", ["dppo", "ppo"])
+def test_update_fp32_pipe_path_vs_oracle_and_tensor_path(nv, flavour_name, monkeypatch):
+    """The reference-sized layers have two implementations: tcgen05 through tensor memory (default) and the
+    register-tiled FP32-pipe layers (every other shape; forced here with DPPO_K2_NO_TS).  Both must meet the
+    oracle at 1e-5 and each other."""
+    fl = nv.FLAVOUR_DPPO if flavour_name == "dppo" else nv.FLAVOUR_PPO
+    s = _setup_update(nv, 17, 6, (100, 100, 500, 100), 4096, 3000, 11, fl)
+    dims, off, size, p_pad, p, p_old, obs, act, adv, ret, logp, idx = s
+    ii = torch.tensor(idx)
+    if fl == nv.FLAVOUR_DPPO:
+        terms, grads = orc.dppo_loss_grads(p, p_old, obs[ii], act[ii], ret[ii], adv[ii], 0.2, 0.01)
+    else:
+        terms, grads = orc.ppo_loss_grads(p, obs[ii], act[ii], ret[ii], adv[ii], logp[ii], 0.2, 0.01)
+    G_ts, L_ts = _run_update(nv, fl, *s, ent=0.01)
+    monkeypatch.setenv("DPPO_K2_NO_TS", "1")
+    G_fp, L_fp = _run_update(nv, fl, *s, ent=0.01)
+    monkeypatch.delenv("DPPO_K2_NO_TS")
+    assert not torch.equal(G_ts, G_fp)                   # different arithmetic: the switch did switch
+    got_ts, got_fp = from_flat(G_ts, off, size, dims.shapes()), from_flat(G_fp, off, size, dims.shapes())
+    for k in orc.PARAM_ORDER:
+        assert_close_scaled(got_fp[k], grads[k], 1e-5, k + " (fp32 pipe)")
+        assert_close_scaled(got_ts[k], grads[k], 1e-5, k + " (tensor cores)")
+        assert_close_scaled(got_ts[k], got_fp[k], 1e-5, k + " (paths)")
+    for j in range(3):
+        assert float(L_ts[j]) == pytest.approx(float(L_fp[j]), rel=1e-5, abs=1e-7)
+
+
 def test_update_is_deterministic(nv):
     s = _setup_update(nv, 17, 6, (100, 100, 500, 100), 4096, 4096, 5, nv.FLAVOUR_DPPO)
     G1, L1 = _run_update(nv, nv.FLAVOUR_DPPO, *s)

@@ -14,7 +14,7 @@ for _ in range(3):
 torch.cuda.synchronize()
 buf=(ctypes.c_longlong*64)()
 nv.lib.dppo_debug_k2_clocks(buf)
-names={0:'heads loaded',1:'tile start',2:'zero+gather',3:'old W1',4:'old V1',5:'old W2',6:'old V2',7:'old heads',8:'new W1',9:'new V1',10:'new W2',11:'new V2',12:'new heads',13:'loss',14:'dls',15:'dWmu',16:'hdx mu',17:'dW2',18:'dx W2',19:'dW1',20:'dWv',21:'hdx v',22:'dV2',23:'dx V2',24:'dV1',25:'end tiles'}
+names={0:'heads loaded',1:'tile start',2:'zero+gather',3:'old W1',4:'old V1',5:'old W2',6:'old V2',7:'old heads',8:'new W1',9:'new V1',10:'new W2',11:'new V2',12:'new heads',13:'loss',14:'dls',15:'dW heads',16:'hdx mu',17:'hdx v',18:'dW2',19:'dV2',20:'dx W2',21:'dx V2',22:'dW1',23:'dV1',24:'-',25:'end tiles'}
 prev=buf[0]
 for i in range(1,26):
     print('%-14s %8d cycles'%(names[i],buf[i]-prev)); prev=buf[i]
