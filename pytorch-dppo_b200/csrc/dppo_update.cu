@@ -500,14 +500,20 @@ constexpr int TS_NBARS = 10;                                // raw_full[2] +0, r
 constexpr int TS_PH_RAW = 8, TS_PH_AF = 12, TS_PH_MD = 16;  // parity bits in `ph` (raw_free: TS_PH_RF = 10)
 
 // D[tmem] (+)= A[tmem] * B[smem descriptor]
-__device__ __forceinline__ void ts_mma(uint32_t d, uint32_t a, uint64_t b, uint32_t idesc, uint32_t acc, uint32_t enable) {
-    // executed by a whole converged warp with warp-uniform operands; elect.sync sits next to the MMA so that ptxas sees
-    // a single issuing lane (a predicate that arrives from elsewhere makes it wrap the MMA in a per-thread loop)
+// The issuing warp takes elect.sync ONCE and hands the plain result to every MMA: ptxas recognises that pattern,
+// moves the operands to uniform registers up front and emits the MMAs back to back.  Any predicate derived from it
+// (and-ed with a condition) or produced elsewhere makes it wrap each MMA in a per-thread loop, so conditions are
+// uniform branches around groups of MMAs instead.
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+    return pred;
+}
+__device__ __forceinline__ void ts_mma_e(uint32_t d, uint32_t a, uint64_t b, uint32_t idesc, uint32_t acc, uint32_t elected) {
     asm volatile(
-        "{\n\t.reg .pred p, e, q;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 q, %5, 0;\n\t"
-        "elect.sync _|e, 0xffffffff;\n\tand.pred e, e, q;\n\t"
+        "{\n\t.reg .pred p, e;\n\tsetp.ne.b32 p, %4, 0;\n\tsetp.ne.b32 e, %5, 0;\n\t"
         "@e tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
-        ::"r"(d), "r"(a), "l"(b), "r"(idesc), "r"(acc), "r"(enable) : "memory");
+        ::"r"(d), "r"(a), "l"(b), "r"(idesc), "r"(acc), "r"(elected) : "memory");
 }
 // whole converged warp; one elected lane commits (no divergent branch in the issuing warp)
 __device__ __forceinline__ void ts_commit(uint64_t* bar) {
@@ -698,9 +704,10 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
             const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
             const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
             constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
+            const uint32_t el = elect_one();
             for (int gp = gp0; gp < gp0 + npt; ++gp) {
                 const int s = gp & 1, u = gp >> 1;
-                const uint32_t e1 = (nrb - 2 * (gp - gp0) >= 2) ? 1u : 0u;          // second block of the pair present
+                const bool two = nrb - 2 * (gp - gp0) >= 2;                         // second block of the pair present
                 K2_TR(3, gp, 0);
                 mbar_wait(&a_full[s], par(TS_PH_AF + s, u));
                 K2_TR(3, gp, 1);
@@ -711,13 +718,15 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                 // main terms into the four rotating accumulators, the cross terms (into their hi*lo halves) four MMAs
                 // later: consecutive MMAs never touch the same accumulator
 #pragma unroll
-                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks, ta + 8 * ks, bd0 + ks * KSTEP, idesc64, gp > gp0 ? 1u : 0u, 1u);
+                for (int ks = 0; ks < 4; ++ks) ts_mma_e(tmem + 64 * ks, ta + 8 * ks, bd0 + ks * KSTEP, idesc64, gp > gp0 ? 1u : 0u, el);
 #pragma unroll
-                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks + 32, ta + 32 + 8 * ks, bd0 + ks * KSTEP, idesc32, 1u, 1u);
+                for (int ks = 0; ks < 4; ++ks) ts_mma_e(tmem + 64 * ks + 32, ta + 32 + 8 * ks, bd0 + ks * KSTEP, idesc32, 1u, el);
+                if (two) {
 #pragma unroll
-                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks, ta + 64 + 8 * ks, bd1 + ks * KSTEP, idesc64, 1u, e1);
+                    for (int ks = 0; ks < 4; ++ks) ts_mma_e(tmem + 64 * ks, ta + 64 + 8 * ks, bd1 + ks * KSTEP, idesc64, 1u, el);
 #pragma unroll
-                for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + 64 * ks + 32, ta + 96 + 8 * ks, bd1 + ks * KSTEP, idesc32, 1u, e1);
+                    for (int ks = 0; ks < 4; ++ks) ts_mma_e(tmem + 64 * ks + 32, ta + 96 + 8 * ks, bd1 + ks * KSTEP, idesc32, 1u, el);
+                }
                 ts_commit(&mma_done[s]);
                 K2_TR(3, gp, 2);
             }
@@ -777,6 +786,30 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
     return ph;
 }
 
+// MMAs of the first-layer routines for NT tiles (compile time) and nks k-steps: k-step outer / tile inner, so that
+// consecutive MMAs go to different accumulators (a dependent MMA waits ~90 cycles); plain elected predicate
+template <int NT>
+__device__ __forceinline__ void first_issue(uint32_t tmem, uint64_t bd, int nks, uint32_t el) {
+    const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
+    for (int ks = 0; ks < nks; ++ks)
+#pragma unroll
+        for (int t = 0; t < NT; ++t)
+            ts_mma_e(tmem + 64 * t, tmem + TS_TM_A + 64 * t + 8 * ks, bd + ks * KSTEP, idesc64, ks ? 1u : 0u, el);
+    for (int ks = 0; ks < nks; ++ks)
+#pragma unroll
+        for (int t = 0; t < NT; ++t)
+            ts_mma_e(tmem + 64 * t + 32, tmem + TS_TM_A + 64 * t + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u, el);
+}
+__device__ __forceinline__ void first_issue_all(int ntiles, uint32_t tmem, uint64_t bd, int nks) {
+    const uint32_t el = elect_one();
+    if (ntiles == 1) first_issue<1>(tmem, bd, nks, el);
+    else if (ntiles == 2) first_issue<2>(tmem, bd, nks, el);
+    else if (ntiles == 3) first_issue<3>(tmem, bd, nks, el);
+    else first_issue<4>(tmem, bd, nks, el);
+}
+
 // ---------------------------------------------------------------------------
 // First layers (K = O <= 32 inputs) on the tensor cores.  Up to four tiles of 128 output features are transformed
 // into tensor memory at once (4 x 64 A columns next to 4 x 64 accumulator columns), so there is no pipeline: stage,
@@ -822,24 +855,8 @@ __device__ __noinline__ unsigned fwd_first_ts(const float* Ws, const float* __re
     __syncthreads();
     if (warp == 7) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-        const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         const uint64_t bd = tc_desc(smem_u32(bt));
-        constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
-        // straight-line, k-step outer / tile inner: consecutive MMAs go to different accumulators (a dependent MMA
-        // waits ~90 cycles) and there is no loop branch between them; absent tiles / k-steps are predicated off
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-#pragma unroll
-            for (int t = 0; t < 4; ++t)
-                ts_mma(tmem + 64 * t, tmem + TS_TM_A + 64 * t + 8 * ks, bd + ks * KSTEP, idesc64, ks ? 1u : 0u,
-                       (t < ntiles && ks < nks) ? 1u : 0u);
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-#pragma unroll
-            for (int t = 0; t < 4; ++t)
-                ts_mma(tmem + 64 * t + 32, tmem + TS_TM_A + 64 * t + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u,
-                       (t < ntiles && ks < nks) ? 1u : 0u);
+        first_issue_all(ntiles, tmem, bd, nks);
         ts_commit(&mma_done[0]);
     }
     mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);
@@ -908,22 +925,8 @@ __device__ __noinline__ unsigned dw_first_ts(float* __restrict__ gW, float* __re
     __syncthreads();
     if (warp == 7) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t idesc64 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(64 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-        const uint32_t idesc32 = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         const uint64_t bd = tc_desc(smem_u32(bt));
-        constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-#pragma unroll
-            for (int t = 0; t < 4; ++t)
-                ts_mma(tmem + 64 * t, tmem + TS_TM_A + 64 * t + 8 * ks, bd + ks * KSTEP, idesc64, ks ? 1u : 0u,
-                       t < ntiles ? 1u : 0u);
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-#pragma unroll
-            for (int t = 0; t < 4; ++t)
-                ts_mma(tmem + 64 * t + 32, tmem + TS_TM_A + 64 * t + 32 + 8 * ks, bd + ks * KSTEP, idesc32, 1u,
-                       t < ntiles ? 1u : 0u);
+        first_issue_all(ntiles, tmem, bd, 4);
         ts_commit(&mma_done[0]);
     }
     mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);
@@ -1390,11 +1393,12 @@ __device__ __noinline__ unsigned dw_layer_ts(float* __restrict__ gW, float* __re
         __syncthreads();
         K2_ACC(42);
         if (warp == 7) {
+            const uint32_t el = elect_one();
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem, tmem + TS_TM_A + 8 * ks, bd + ks * KSTEP, idm, ks ? 1u : 0u, 1u);
+            for (int ks = 0; ks < 4; ++ks) ts_mma_e(tmem, tmem + TS_TM_A + 8 * ks, bd + ks * KSTEP, idm, ks ? 1u : 0u, el);
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) ts_mma(tmem + Np, tmem + TS_TM_A + 32 + 8 * ks, bd + ks * KSTEP, idc, 1u, 1u);
+            for (int ks = 0; ks < 4; ++ks) ts_mma_e(tmem + Np, tmem + TS_TM_A + 32 + 8 * ks, bd + ks * KSTEP, idc, 1u, el);
             ts_commit(&mma_done[0]);
         }
         mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);     // every thread sees every phase of this barrier
