@@ -280,6 +280,7 @@ CASES = [
     (376, 17, (256, 256, 256, 256), 700, 512),         # C5: Humanoid shape, 256x256 nets
     (15, 3, (100, 100, 500, 100), 2048, 2048),         # C3: HopperBullet shape
     (17, 6, (128, 128, 128, 128), 1024, 1024),         # 128-wide: every hidden layer on the tcgen05 path
+    (11, 3, (96, 96, 160, 96), 700, 450),              # odd numbers of 32-wide k-blocks (3 and 5) in the tensor-core pipeline
 ]
 
 
