@@ -496,8 +496,8 @@ constexpr int TS_BT_BYTES = 4 * TC_SBO;                     // one 32-row sample
 constexpr int TS_BYTES = 4 * TS_RAW_BYTES + 4 * 2 * TS_BT_BYTES;   // 102 400: two ring slots of two k-blocks each
 constexpr int TS_TM_A = 256;                                // TMEM: 4 x 64 accumulator columns, then 256 A columns
 constexpr int TS_BAR0 = 2;                                  // first pipeline barrier in the barrier array (0, 1: FP32-path stages)
-constexpr int TS_NBARS = 12;                                // raw_full[4] +0, raw_free[4] +4, mma_done[2] +8, a_full[2] +10
-constexpr int TS_PH_RAW = 8, TS_PH_RF = 12, TS_PH_AF = 16, TS_PH_MD = 18;   // first parity bit of each group in `ph`
+constexpr int TS_NBARS = 10;                                // raw_full[2] +0, raw_free[2] +2, a_full[2] +4, mma_done[2] +8
+constexpr int TS_PH_RAW = 8, TS_PH_AF = 12, TS_PH_MD = 16;  // parity bits in `ph` (raw_free: TS_PH_RF = 10)
 
 // D[tmem] (+)= A[tmem] * B[smem descriptor]
 // The issuing warp takes elect.sync ONCE and hands the plain result to every MMA: ptxas recognises that pattern,
@@ -582,12 +582,13 @@ __device__ __forceinline__ void ts_stage_samples(unsigned char* bh, const float*
 //   warps 4,5  samples:   one block of the pair each (activations -> [hi | lo] K-major tiles)
 //   warp 6     TMA producer: refills a slot as soon as the transform warps have consumed it (raw_free)
 //   warp 7     MMA issuer (whole warp, uniform operands, elected lane), one commit per pair
-// Barriers (index from TS_BAR0; parity bit in `ph`):  raw_full[4] +0 (bits 8-11)  raw_free[4] +4 (bits 12-15), one per 16 KB tile
+// Barriers (index from TS_BAR0; parity bit in `ph`):  raw_full[2] +0 (bits 8,9)   raw_free[2] +2 (bits 10,11)
 //                                                      a_full[2]  +4 (bits 12,13)  mma_done[2] +8 (bits 16,17)
 // DX = false: out[m][n] = tanh(sum_k in[m][k] W[n][k] + b[n]); map box 32 (k) x 128 (n), SWIZZLE_128B; one tile.
 // DX = true : act[m][k] <- (sum_n dOut[m][n] W[n][k]) (1 - act[m][k]^2); map box 128 (k) x 32 (n), no swizzle;
 //             tiles of 128 k, the rings run across tiles, the accumulators are drained between tiles.
 // ---------------------------------------------------------------------------
+constexpr int TS_PH_RF = 10;
 template <bool DX>
 __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* __restrict__ bias, int N, int K,
                                           const float* bsrc, int ldb, float* dst, int ldo, unsigned char* ts, uint64_t* bars,
@@ -599,22 +600,22 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
     const int ntiles = DX ? (K + 127) >> 7 : 1;
     const int NP = npt * ntiles;                            // pairs in all
     uint64_t* raw_full = bars + TS_BAR0;
-    uint64_t* raw_free = raw_full + 4;
+    uint64_t* raw_free = raw_full + 2;
+    uint64_t* a_full = raw_full + 4;
     uint64_t* mma_done = raw_full + 8;
-    uint64_t* a_full = raw_full + 10;
     unsigned char* raw = ts;
     unsigned char* bst = ts + 4 * TS_RAW_BYTES;
     float bb = 0.f;                                         // forward: bias of my epilogue feature, fetched now
     if (!DX) { const int n = 32 * (warp & 3) + lane; bb = n < N ? __ldg(bias + n) : 0.f; }
     // parity of the u-th use (u = 0, 1, ...) of a barrier whose tracked bit is `bit`
     auto par = [&](int bit, int u) -> unsigned { return ((ph >> bit) ^ (unsigned)u) & 1u; };
-    auto tma_tile = [&](int gp, int i) {                    // (whole warp 6) raw tile i of pair gp into tile slot 2 (gp & 1) + i
-        const int j = 2 * (gp & 1) + i, mt = gp / npt, blk = 2 * (gp - mt * npt) + i;
-        const uint32_t d0 = smem_u32(raw + j * TS_RAW_BYTES), bar = smem_u32(&raw_full[j]);
-        // a block past the end of the reduction is loaded all the same (zero-filled, never used): every tile barrier
-        // then sees one phase per pair
-        if (DX) tma_pair_elect(d0, d0, map, 128 * mt, TC_KB * blk, 0, 0, bar, TS_RAW_BYTES, 0u);
-        else tma_pair_elect(d0, d0, map, TC_KB * blk, 0, 0, 0, bar, TS_RAW_BYTES, 0u);
+    auto tma_pair = [&](int gp) {                           // (whole warp 6) both raw tiles of pair gp into slot gp & 1
+        const int s = gp & 1, mt = gp / npt, p = gp - mt * npt;
+        const uint32_t two = (nrb - 2 * p >= 2) ? 1u : 0u;
+        const uint32_t d0 = smem_u32(raw + (2 * s) * TS_RAW_BYTES), bar = smem_u32(&raw_full[s]);
+        const int blk = 2 * p;
+        if (DX) tma_pair_elect(d0, d0 + TS_RAW_BYTES, map, 128 * mt, TC_KB * blk, 128 * mt, TC_KB * (blk + 1), bar, (1u + two) * TS_RAW_BYTES, two);
+        else tma_pair_elect(d0, d0 + TS_RAW_BYTES, map, TC_KB * blk, 0, TC_KB * (blk + 1), 0, bar, (1u + two) * TS_RAW_BYTES, two);
     };
     __syncthreads();                                        // previous users of the staging region are done
 #ifdef DPPO_K2_TRACE
@@ -622,8 +623,8 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
     const long long trace_t0 = clock64();
 #endif
     if (warp == 6) {
-        tma_tile(0, 0); tma_tile(0, 1);
-        if (NP > 1) { tma_tile(1, 0); tma_tile(1, 1); }
+        tma_pair(0);
+        if (NP > 1) tma_pair(1);
     }
     for (int mt = 0; mt < ntiles; ++mt) {
         const int gp0 = mt * npt;
@@ -634,11 +635,11 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                 const int s = gp & 1, u = gp >> 1;
                 const int nb2 = min(2, nrb - 2 * (gp - gp0));
                 if (warp == 0) K2_TR(0, gp, 0);
+                mbar_wait(&raw_full[s], par(TS_PH_RAW + s, u));
+                if (warp == 0) K2_TR(0, gp, 1);
                 const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A + 128 * s;
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
-                    mbar_wait(&raw_full[2 * s + i], par(TS_PH_RAW + 2 * s + i, u));
-                    if (warp == 0 && i == 0) K2_TR(0, gp, 1);
                     if (i < nb2) {
                         uint32_t hi[32], lo[32];
                         const unsigned char* tile = raw + (2 * s + i) * TS_RAW_BYTES;
@@ -655,24 +656,19 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                                 ts_split(x.z, hi[4 * c + 2], lo[4 * c + 2]); ts_split(x.w, hi[4 * c + 3], lo[4 * c + 3]);
                             }
                         }
-                        __syncwarp();                       // every raw value of the tile has been consumed by a split:
-                        if (lane == 0) mbar_arrive(&raw_free[2 * s + i]);   // the producer may refill it
                         if (i == 0) {                       // the slot's previous MMAs have read these A columns
                             if (warp == 0) K2_TR(0, gp, 2);
                             if (gp >= 2) mbar_wait(&mma_done[s], par(TS_PH_MD + s, u - 1));
                             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                             if (warp == 0) K2_TR(0, gp, 3);
                         }
-                        if (warp == 0 && i == 1) K2_TR(0, gp, 7);
                         tmem_st32(ta + 64 * i, hi);
                         tmem_st32(ta + 64 * i + 32, lo);
-                        if (warp == 0 && i == 0) K2_TR(0, gp, 6);
-                    } else {
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&raw_free[2 * s + i]);   // absent block: release its (unused) tile
                     }
                 }
                 if (warp == 0) K2_TR(0, gp, 4);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&raw_free[s]);   // every raw value of the slot has been consumed by a split
                 asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
@@ -698,12 +694,9 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
             for (int gp = gp0; gp < gp0 + npt; ++gp)
                 if (gp + 2 < NP) {
                     K2_TR(2, gp, 0);
-                    for (int i = 0; i < 2; ++i) {
-                        const int j = 2 * (gp & 1) + i;
-                        mbar_wait(&raw_free[j], par(TS_PH_RF + j, gp >> 1));
-                        if (i == 0) K2_TR(2, gp, 1);
-                        tma_tile(gp + 2, i);
-                    }
+                    mbar_wait(&raw_free[gp & 1], par(TS_PH_RF + (gp & 1), gp >> 1));
+                    K2_TR(2, gp, 1);
+                    tma_pair(gp + 2);
                     K2_TR(2, gp, 2);
                 }
         } else {
@@ -788,7 +781,7 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
         const unsigned uses = (unsigned)(((NP + 1 - s) >> 1) & 1);
-        ph ^= (uses * 3u << (TS_PH_RAW + 2 * s)) | (uses * 3u << (TS_PH_RF + 2 * s)) | (uses << (TS_PH_AF + s)) | (uses << (TS_PH_MD + s));
+        ph ^= (uses << (TS_PH_RAW + s)) | (uses << (TS_PH_RF + s)) | (uses << (TS_PH_AF + s)) | (uses << (TS_PH_MD + s));
     }
     return ph;
 }
@@ -1565,13 +1558,11 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         uint64_t* b = reinterpret_cast<uint64_t*>(S + P.o_bars);
         mbar_init(&b[0], 1);                               // weight stage buffers (TMA bulk copies)
         mbar_init(&b[1], 1);
-        for (int i = 0; i < 4; ++i) {
-            mbar_init(&b[TS_BAR0 + i], 1);                  // raw_full, one per raw tile (TMA tx)
-            mbar_init(&b[TS_BAR0 + 4 + i], 4);              // raw_free: the four transform warps
-        }
         for (int i = 0; i < 2; ++i) {
+            mbar_init(&b[TS_BAR0 + i], 1);                  // raw_full (TMA tx)
+            mbar_init(&b[TS_BAR0 + 2 + i], 4);              // raw_free: the four transform warps
+            mbar_init(&b[TS_BAR0 + 4 + i], 6);              // a_full: four transform warps + the two sample warps
             mbar_init(&b[TS_BAR0 + 8 + i], 1);              // mma_done (tcgen05.commit)
-            mbar_init(&b[TS_BAR0 + 10 + i], 6);             // a_full: four transform warps + the two sample warps
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }

@@ -270,3 +270,30 @@ def test_update_stream_matches_step_by_step():
     assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1]) and torch.equal(res[0][2], res[1][2])
     for a, b in zip(res[0][3], res[1][3]):
         assert torch.equal(a, b)
+
+
+@pytest.mark.gpu
+def test_engine_is_bit_repeatable():
+    """Two identical runs of the engine (CUDA-graph replay, K2 and K3 back to back over several rollouts) must give
+    bit-identical parameters and Adam state.  A kernel-level repeat of K2 alone (one launch, then a synchronise) did
+    NOT expose a race in the tensor-core pipeline that this did: keep it at the engine level."""
+    import b200_native as nv
+    from b200_engine import RolloutBuffer, UpdateEngine
+    from model import Model, Shared_obs_stats
+    from synthetic import make_rollout
+    T, B, E, n = 2048, 256, 3, 5
+    for rep in range(3):
+        res = []
+        for _ in range(2):
+            torch.manual_seed(1)
+            m = Model(17, 6, device=DEV)
+            stats = Shared_obs_stats(17)
+            hosts = [make_rollout(m, stats, T, seed=40 + i, flavour=nv.FLAVOUR_DPPO, seg_len=500)[0] for i in range(3)]
+            dev = RolloutBuffer(T, 17, 6, DEV)
+            eng = UpdateEngine(m, nv.FLAVOUR_DPPO, B, E, 3e-4)
+            rng = random.Random(4)
+            for i in range(n):
+                eng.update_from_host(hosts[i % 3], dev, obs_stats=stats, rng=rng)
+            torch.cuda.synchronize()
+            res.append((m.flat.clone(), eng.m.clone()))
+        assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1]), "repeat %d differs" % rep
