@@ -312,7 +312,7 @@ def main():
         "unit": "GB/s", "frac": k2_bytes / k2_s / 1e9 / hbm_peak, "traffic": traffic, "peak_source": peak_src,
         "note": "K2 does %.0f FLOP per algorithmic byte, so HBM is not its bound; its layers run on the tensor cores as "
                 "3xTF32 (three MMA flops per algorithmic flop) with 28 samples = 32 MMA columns per SM, and the kernel is "
-                "latency bound (eight warps per SM, profiles/r01e_k2_summary.md): see 'compute' and 'tensor'"
+                "latency bound (eight warps per SM, profiles/r01f_k2_summary.md): see 'compute' and 'tensor'"
                 % (k2_flops / k2_bytes),
         "compute": {"bound": "fp32_fma", "achieved": k2_flops / k2_s / 1e12, "peak": fp32_peak, "unit": "TFLOP/s",
                     "frac": k2_flops / k2_s / 1e12 / fp32_peak, "peak_source": "dppo_fp32_probe, measured in this run",
