@@ -668,7 +668,9 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                 }
                 if (warp == 0) K2_TR(0, gp, 4);
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&raw_free[s]);   // every raw value of the slot has been consumed by a split
+                // the release stays HERE, after both tiles' tcgen05.st have been issued: arriving right after a tile's
+                // split (when its LDS results are already consumed) made the engine non-repeatable - see DESIGN.md, K2
+                if (lane == 0) mbar_arrive(&raw_free[s]);
                 asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();
