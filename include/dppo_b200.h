@@ -78,9 +78,12 @@ int dppo_gae_scan(const float* rewards, const float* values, const float* boot, 
  * look-back chain lives in a ~12 KB array inside the library image, resident on every
  * GPU that loads the library.  T <= DPPO_GAE_NOALLOC_MAX_T, otherwise
  * DPPO_E_NOALLOC_LIMIT.  The first call on a device resolves the array's device address:
- * make it before any stream capture.  Allocates and frees nothing.  All calls on a
- * device share the array (flags are re-cleared on `stream` each call): calls that may
- * overlap on the GPU race and must be serialised by the caller. */
+ * make it before any stream capture.  Allocates and frees nothing.  The array is used
+ * only when the scan has to chain its tiles (gamma*lam >= ~0.987; with a faster decay,
+ * e.g. the reference's 0.99*0.95, tiles are independent and need no scratch).  All calls
+ * on a device share the array (in the chained mode its ticket and tile flags are
+ * re-cleared on `stream` each call): calls that may overlap on the GPU race and must be
+ * serialised by the caller. */
 #define DPPO_GAE_NOALLOC_MAX_T 4194304
 int dppo_gae_scan_noalloc(const float* rewards, const float* values, const float* boot, const uint8_t* seg_end,
                           float* adv, float* ret, int64_t T, double gamma, double lam, void* stream);
@@ -123,6 +126,14 @@ int dppo_update_fused(int flavour, const dppo_dims* d,
                       const float* theta, const float* theta_old,
                       float clip, float ent_coeff,
                       float* partials, float* loss_partials, void* stream);
+/* Which layer routines dppo_update_fused uses: DPPO_K2_PATH_AUTO (default) puts every eligible layer on the
+ * tensor cores (tcgen05, 3xTF32) and the rest on the FP32 pipe; DPPO_K2_PATH_FP32 forces the FP32-pipe
+ * routines for all layers (A/B runs, tests).  Process-wide; the environment variable DPPO_K2_NO_TS=1, read
+ * once when the library is first used, selects DPPO_K2_PATH_FP32 as the initial value.  Returns the
+ * previous setting, or DPPO_E_BADARG. */
+#define DPPO_K2_PATH_AUTO 0
+#define DPPO_K2_PATH_FP32 1
+int dppo_update_set_path(int path);
 
 /* ---- K3: gradient sum + [global-norm clip] + Adam ------------------------
  * Replaces Shared_grad_buffers.add_gradient/reset (model.py:53-59), the
@@ -170,6 +181,11 @@ int dppo_comm_local_handle(dppo_comm* c, void* handle_host);
 int dppo_comm_open_peers(dppo_comm* c, const void* handles_host);
 int dppo_comm_create_loopback(int world, int P_pad, dppo_comm** out_array);
 int dppo_comm_destroy(dppo_comm* c);
+/* A rank that waits for peers which never push (a dead process, unequal numbers of calls) gives up after a few
+ * seconds of polling and records it; dppo_comm_check returns DPPO_E_COMM from then on (0 otherwise).  It
+ * synchronises the device.  The reference has no such detection: a dead worker deadlocks the chief
+ * (chief.py:13) and the other workers (train.py:174-175). */
+int dppo_comm_check(dppo_comm* c);
 int dppo_allreduce_adam(dppo_comm* c, const float* partials, int nparts, float* gshared,
                         float* theta, float* theta_prev, float* m, float* v, int P_pad,
                         int step, double lr, double beta1, double beta2, double eps,

@@ -3,6 +3,7 @@ K1 -> E x (K2 -> K3) sequence, captured once in a CUDA graph and replayed per
 rollout.  torch supplies device memory and streams; all arithmetic is in
 libdppo_b200.so (b200_native).  There is no CPU path."""
 import random
+from collections import OrderedDict
 
 import torch
 
@@ -87,8 +88,32 @@ class UpdateEngine:
         self.loss_host = torch.zeros(self.E, 4, pin_memory=True)
         self._adam_scratch = torch.empty(max(nv.reduce_adam_scratch_bytes(self.P_pad), 16), dtype=torch.uint8, device=dev)
         self._gae_scratch = None
-        self._graphs = {}
+        self._graphs = OrderedDict()             # captured cycles, see _graph_key; at most MAX_GRAPHS, oldest evicted
+        self._rollout = None                     # the engine's own rollout buffer (rollout_buffer())
         self.launches_per_cycle = 0
+
+    MAX_GRAPHS = 4
+
+    def rollout_buffer(self, T):
+        """The engine's persistent rollout buffer of T steps.  Training loops fill THIS buffer every outer
+        iteration (train.collect_rollout(out=...)) instead of allocating a new one: its addresses stay fixed, so
+        the cycle captured for it is replayed for as long as the loop runs."""
+        if self._rollout is None or self._rollout.T != T:
+            self._rollout = RolloutBuffer(T, self.dims.O, self.dims.A, self.device)
+        return self._rollout
+
+    def _graph_key(self, buf, gshared, obs_stats, with_gae):
+        """A captured cycle bakes in device ADDRESSES, so that is what identifies it: every rollout column, the
+        shared gradient bucket, the statistics vectors and the scratch buffers.  (Python object ids are reused
+        once an object is freed; a new buffer with a recycled id must never hit an old graph.)"""
+        ptrs = [getattr(buf, f).data_ptr() for f in RolloutBuffer.FIELDS]
+        ptrs.append(0 if gshared is None else gshared.data_ptr())
+        if obs_stats is not None:
+            ptrs += [t.data_ptr() for t in (obs_stats.n, obs_stats.mean, obs_stats.mean_diff, obs_stats.var,
+                                            obs_stats._scratch_for(buf.T))]
+        if with_gae:
+            ptrs.append(self._gae_scratch.data_ptr())
+        return (buf.T, bool(with_gae), obs_stats is not None) + tuple(ptrs)
 
     # ---- K1 ---------------------------------------------------------------------------------
     def gae(self, buf):
@@ -160,15 +185,17 @@ class UpdateEngine:
         if not use_graph or (self.comm is not None and self.comm.mode == "nccl"):
             self.launches_per_cycle = self._launch_epochs(buf, gshared, obs_stats, with_gae)
         else:
-            key = (id(buf), None if gshared is None else gshared.data_ptr(), id(obs_stats), with_gae)
-            if key not in self._graphs:
+            # scratch buffers are allocated (or grown) outside the capture; their addresses are part of the key
+            if with_gae and (self._gae_scratch is None or self._gae_scratch.numel() < nv.gae_scratch_bytes(buf.T)):
+                self._gae_scratch = torch.empty(nv.gae_scratch_bytes(buf.T), dtype=torch.uint8, device=self.device)
+            key = self._graph_key(buf, gshared, obs_stats, with_gae)
+            if key in self._graphs:
+                self._graphs.move_to_end(key)
+            else:
                 # warm-up launch outside capture (sets kernel attributes), on scratch copies of the state
                 state = [self.theta, self.theta_old, self.m, self.v]
                 if obs_stats is not None:
                     state += [obs_stats.n, obs_stats.mean, obs_stats.mean_diff, obs_stats.var]
-                    obs_stats._scratch_for(buf.T)                  # allocate outside the capture
-                if with_gae and (self._gae_scratch is None or self._gae_scratch.numel() < nv.gae_scratch_bytes(buf.T)):
-                    self._gae_scratch = torch.empty(nv.gae_scratch_bytes(buf.T), dtype=torch.uint8, device=self.device)
                 saved = [t.clone() for t in state]
                 gsaved = None if gshared is None else gshared.clone()
                 self._launch_epochs(buf, gshared, obs_stats, with_gae)
@@ -182,8 +209,11 @@ class UpdateEngine:
                     n = self._launch_epochs(buf, gshared, obs_stats, with_gae)
                 for t, s in zip(state, saved):
                     t.copy_(s)                                     # capture does not execute, but be explicit
-                self._graphs[key] = (g, n)
-            g, n = self._graphs[key]
+                # the entry keeps the tensors whose addresses the graph holds alive for as long as it exists
+                self._graphs[key] = (g, n, buf, gshared, obs_stats, self._gae_scratch)
+                while len(self._graphs) > self.MAX_GRAPHS:
+                    self._graphs.popitem(last=False)
+            g, n = self._graphs[key][:2]
             g.replay()
             self.launches_per_cycle = n
         self.step += self.E

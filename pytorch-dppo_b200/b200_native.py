@@ -71,6 +71,8 @@ def _load():
         "dppo_comm_open_peers": (i32, [vp, vp]),
         "dppo_comm_create_loopback": (i32, [i32, i32, c.POINTER(vp)]),
         "dppo_comm_destroy": (i32, [vp]),
+        "dppo_comm_check": (i32, [vp]),
+        "dppo_update_set_path": (i32, [i32]),
         "dppo_allreduce_adam": (i32, [vp, vp, i32, vp, vp, vp, vp, vp, i32, i32, dbl, dbl, dbl, dbl, vp, vp, vp, vp, vp]),
         "dppo_allreduce_adam_loopback": (i32, [c.POINTER(vp), i32, c.POINTER(vp), c.POINTER(i32), c.POINTER(vp),
                                                c.POINTER(vp), c.POINTER(vp), c.POINTER(vp), c.POINTER(vp), i32, i32,
@@ -171,6 +173,17 @@ def update_fused(flavour, dims, obs, act, adv, ret, logp_old, idx, theta, theta_
                                 _stream()))
 
 
+K2_PATH_AUTO, K2_PATH_FP32 = 0, 1
+
+
+def update_set_path(path):
+    """Layer routines of K2: K2_PATH_AUTO (tensor cores where eligible) or K2_PATH_FP32.  Returns the previous setting."""
+    prev = lib.dppo_update_set_path(path)
+    if prev < 0:
+        check(prev)
+    return prev
+
+
 def reduce_adam_scratch_bytes(P_pad):
     return lib.dppo_reduce_adam_scratch_bytes(P_pad)
 
@@ -251,6 +264,11 @@ def comm_open_peers(comm, handles):
 
 def comm_destroy(comm):
     lib.dppo_comm_destroy(comm)
+
+
+def comm_check(comm):
+    """Raises DppoError once a poll of this communicator has timed out (a peer never pushed)."""
+    check(lib.dppo_comm_check(comm))
 
 
 def allreduce_adam(comm, partials, nparts, gshared, theta, theta_prev, m, v, step, lr, beta1=0.9, beta2=0.999,

@@ -22,8 +22,12 @@
 //   later, after its reader has pushed the epoch in between (which it does after reading).
 //
 // CTAs walk the column blocks in index order on every GPU and push ALL their blocks before they
-// poll any, so a poll only ever waits for pushes that depend on nothing: no deadlock regardless
-// of how many CTAs are resident.
+// poll any, so a poll only ever waits for pushes that depend on nothing.  That argument needs every
+// rank's CTAs to actually run: the grid is capped at what is co-resident on this GPU (occupancy x SMs),
+// and a rank that never shows up (a dead process, an unequal number of calls) cannot be waited out -
+// every poll therefore carries a clock64() budget (CM_SPIN_BUDGET cycles, a few seconds); when it runs
+// out the CTA records DPPO_E_COMM in the communicator's error word, stops polling and the results of that
+// call are undefined.  dppo_comm_check() reads the word (it synchronises the device).
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
@@ -34,6 +38,7 @@ namespace {
 constexpr int CM_MAX_WORLD = 8;
 constexpr int CM_THREADS = 256;            // 8 warps: partial groups
 constexpr int CM_RQ = 32;                  // float4 columns per block
+constexpr long long CM_SPIN_BUDGET = 8000000000LL;   // clock64() cycles a poll may wait (~4 s at 1.9 GHz)
 
 struct AdamScalars { float w1, b2, a2, bc2_sqrt, eps, alpha; };
 
@@ -42,12 +47,13 @@ struct CommDev {                            // everything a kernel needs, by val
     uint4* recv[CM_MAX_WORLD];              // recv[r]: rank r's receive buffer [2][world][n4][2] LL words (peer-mapped)
     unsigned* epoch;                        // this rank: completed epochs
     unsigned* done;                         // this rank: CTAs finished in the current launch
+    unsigned* err;                          // this rank: non-zero once a poll has timed out
 };
 
 }  // namespace
 
 struct dppo_comm {
-    int rank, world, P_pad, n4, gblocks, loopback;
+    int rank, world, P_pad, n4, gblocks, loopback, grid;
     void* base;                             // this rank's allocation
     size_t bytes, recv_bytes, flag_bytes;
     void* peer_base[CM_MAX_WORLD];          // mapped bases (peer_base[rank] == base)
@@ -137,18 +143,31 @@ __global__ void __launch_bounds__(CM_THREADS) allreduce_adam_kernel(const Launch
         }
     }
     // ---- phase 2: poll every rank's slice, sum in rank order, Adam -----------------------------------
+    // warp r (< world) polls rank r's slice of the column block - the W round trips to the words that the
+    // peers wrote run side by side instead of one after the other - and parks it in shared memory; warp 0
+    // then adds the W slices in rank order and runs Adam.
     for (int jb = blockIdx.x; jb < C.gblocks; jb += gridDim.x) {
         const int i = jb * CM_RQ + lane;
-        if (g != 0 || i >= n4) continue;                  // no block-wide barrier below this line
+        __syncthreads();                                  // red[] of phase 1 / of the previous column block consumed
+        if (g < C.world && i < n4) {
+            const uint4* q = C.recv[C.rank] + (((size_t)par * C.world + g) * n4 + i) * 2;
+            uint4 lo = ld_ll(q), hi = ld_ll(q + 1);
+            if (lo.y != epoch || lo.w != epoch || hi.y != epoch || hi.w != epoch) {
+                const long long t0 = clock64();
+                while (true) {
+                    lo = ld_ll(q); hi = ld_ll(q + 1);
+                    if (lo.y == epoch && lo.w == epoch && hi.y == epoch && hi.w == epoch) break;
+                    if (clock64() - t0 > CM_SPIN_BUDGET) { atomicExch(C.err, 1u); break; }
+                }
+            }
+            red[g][lane] = make_float4(__uint_as_float(lo.x), __uint_as_float(lo.z), __uint_as_float(hi.x), __uint_as_float(hi.z));
+        }
+        __syncthreads();
+        if (g != 0 || i >= n4) continue;
         float4 G = make_float4(0.f, 0.f, 0.f, 0.f);
-        const uint4* slot = C.recv[C.rank] + ((size_t)par * C.world * n4 + i) * 2;
         for (int r = 0; r < C.world; ++r) {
-            const uint4* q = slot + (size_t)r * n4 * 2;
-            uint4 lo, hi;
-            do { lo = ld_ll(q); } while (lo.y != epoch || lo.w != epoch);
-            do { hi = ld_ll(q + 1); } while (hi.y != epoch || hi.w != epoch);
-            G.x = __fadd_rn(G.x, __uint_as_float(lo.x)); G.y = __fadd_rn(G.y, __uint_as_float(lo.z));
-            G.z = __fadd_rn(G.z, __uint_as_float(hi.x)); G.w = __fadd_rn(G.w, __uint_as_float(hi.z));
+            const float4 x = red[r][lane];
+            G.x = __fadd_rn(G.x, x.x); G.y = __fadd_rn(G.y, x.y); G.z = __fadd_rn(G.z, x.z); G.w = __fadd_rn(G.w, x.w);
         }
         if (A.gshared) {                                  // shared bucket content on top (as dppo_adam.cu)
             const float4 s0 = A.gshared[i];
@@ -203,11 +222,19 @@ void fill_dev(dppo_comm* c) {
     }
     c->dev.epoch = (unsigned*)((char*)c->base + c->recv_bytes + c->flag_bytes);
     c->dev.done = c->dev.epoch + 1;
+    c->dev.err = c->dev.epoch + 2;
 }
 
-int grid_for(const dppo_comm* c) {
-    const int cap = dppo_sm_count() * 4;
-    return c->gblocks < cap ? c->gblocks : cap;
+// every CTA of the launch must be resident at once (a CTA polls words that the same-numbered CTA of each
+// peer pushes; CTAs are dispatched in index order, so equal grids of co-resident CTAs cannot wait on a CTA
+// that has not started)
+int grid_for(const dppo_comm* c, int* out) {
+    int per_sm = 0;
+    DPPO_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, allreduce_adam_kernel, CM_THREADS, 0));
+    const int cap = per_sm * dppo_sm_count();
+    if (cap < 1) return DPPO_E_TOOLARGE;
+    *out = c->gblocks < cap ? c->gblocks : cap;
+    return 0;
 }
 
 }  // namespace
@@ -306,14 +333,23 @@ extern "C" int dppo_allreduce_adam(dppo_comm* c, const float* partials, int npar
                                    const float* loss_partials, float* loss_out, void* stream) {
     if (!c || c->loopback) return DPPO_E_COMM;
     if (step < 1 && !scalars_dev) return DPPO_E_BADARG;
-    static LaunchArgs L;
-    const int rc = fill_rank_args(L.r[0], c, partials, nparts, gshared, theta, theta_prev, m, v, P_pad, scalars_dev,
-                                  grad_out, loss_partials, loss_out);
+    LaunchArgs L;                                             // by value into the launch: nothing shared between calls
+    int rc = fill_rank_args(L.r[0], c, partials, nparts, gshared, theta, theta_prev, m, v, P_pad, scalars_dev,
+                            grad_out, loss_partials, loss_out);
     if (rc) return rc;
     L.s = make_scalars(step < 1 ? 1 : step, lr, beta1, beta2, eps);
-    allreduce_adam_kernel<<<dim3(grid_for(c), 1), CM_THREADS, 0, (cudaStream_t)stream>>>(L);
+    if (c->grid == 0 && (rc = grid_for(c, &c->grid)) != 0) return rc;
+    allreduce_adam_kernel<<<dim3(c->grid, 1), CM_THREADS, 0, (cudaStream_t)stream>>>(L);
     DPPO_LAUNCH_CHECK();
     return 0;
+}
+
+// 0 while no poll of this communicator has timed out, DPPO_E_COMM afterwards (sticky).  Synchronises the device.
+extern "C" int dppo_comm_check(dppo_comm* c) {
+    if (!c || !c->dev.err) return DPPO_E_BADARG;
+    unsigned e = 0;
+    DPPO_CUDA_TRY(cudaMemcpy(&e, c->dev.err, sizeof(e), cudaMemcpyDeviceToHost));
+    return e ? DPPO_E_COMM : 0;
 }
 
 // All `world` virtual ranks in one cooperative launch on the current GPU (tests).  Arrays are
@@ -324,7 +360,7 @@ extern "C" int dppo_allreduce_adam_loopback(dppo_comm** comms, int world, const 
                                             int step, double lr, double beta1, double beta2, double eps,
                                             float* const* grad_out, void* stream) {
     if (!comms || world < 1 || world > CM_MAX_WORLD || step < 1) return DPPO_E_BADARG;
-    static LaunchArgs L;
+    LaunchArgs L;
     for (int r = 0; r < world; ++r) {
         if (!comms[r] || !comms[r]->loopback || comms[r]->world != world) return DPPO_E_COMM;
         const int rc = fill_rank_args(L.r[r], comms[r], partials[r], nparts[r], gshared ? gshared[r] : nullptr, theta[r],

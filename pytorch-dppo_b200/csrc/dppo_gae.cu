@@ -25,7 +25,7 @@ namespace {
 
 constexpr int GAE_THREADS = 512;
 constexpr int GAE_K = 8;                          // steps per thread
-constexpr int GAE_TILE = GAE_THREADS * GAE_K;     // 2048 steps per CTA
+constexpr int GAE_TILE = GAE_THREADS * GAE_K;     // 4096 steps per CTA
 
 struct Aff { float a, b; };                       // x -> b + a*x
 // (f o g)(x) = f.b + f.a*(g.b + g.a*x)
@@ -258,7 +258,7 @@ extern "C" int dppo_gae_scan(const float* rewards, const float* values, const fl
 // ---------------------------------------------------------------------------
 // dppo_gae_scan_noalloc - the same scan for callers that cannot hand us scratch.
 //
-// dppo_gae_scan needs a few bytes per 2048-step tile for the look-back chain, and
+// dppo_gae_scan needs a few bytes per 4096-step tile for the look-back chain, and
 // it expects the caller to allocate them.  Some callers cannot: a host program
 // that was given a fixed set of device buffers by someone else's allocator and
 // has no allocator of its own; a control loop that must not call cudaMalloc
@@ -274,10 +274,15 @@ extern "C" int dppo_gae_scan(const float* rewards, const float* values, const fl
 //     (cudaGetSymbolAddress, with that device current) and caches it.  Make that
 //     first call outside of any stream capture.
 //   * Nothing is allocated or freed, here or in anything this calls.
-//   * All calls on a device share the one array.  The flags that must start at
-//     zero are cleared on `stream` at the start of every call; everything else is
-//     overwritten before it is read.  Two calls that can overlap on the GPU
-//     (different streams, no dependency between them) race on it - serialise them.
+//   * The array is used only when the scan chains its tiles, i.e. when gamma*lam
+//     is too close to 1 for independent tiles (gae_halo() == 0, |gamma*lam| >= ~0.987).
+//     With a faster decay (the reference's 0.99*0.95) the tiles need no scratch at
+//     all and the array is left alone.
+//   * All calls on a device share the one array.  In the chained mode the ticket
+//     and the tile flags, which must start at zero, are cleared on `stream` at the
+//     start of every call; the carries are overwritten before they are read.  Two
+//     calls that can overlap on the GPU (different streams, no dependency between
+//     them) race on it - serialise them.
 // ---------------------------------------------------------------------------
 #define DPPO_GAE_NOALLOC_MAX_TILES ((DPPO_GAE_NOALLOC_MAX_T + GAE_TILE - 1) / GAE_TILE)
 #define DPPO_GAE_NOALLOC_FLAG_BYTES ((sizeof(int) * (1 + DPPO_GAE_NOALLOC_MAX_TILES) + 15) / 16 * 16)

@@ -23,6 +23,7 @@
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 #include <cuda.h>
 #include "common.cuh"
 
@@ -1850,6 +1851,13 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
 }
 
+// layer-routine selection (dppo_update_set_path); the environment is consulted once, for the initial value
+int g_k2_path = -1;
+int k2_path() {
+    if (g_k2_path < 0) g_k2_path = getenv("DPPO_K2_NO_TS") != nullptr ? DPPO_K2_PATH_FP32 : DPPO_K2_PATH_AUTO;
+    return g_k2_path;
+}
+
 int fill_layout(const dppo_dims& d, Layout& L) {
     const int sizes[DPPO_N_PARAMS] = {d.A, d.H1 * d.O, d.H1, d.H2 * d.H1, d.H2, d.G1 * d.O, d.G1,
                                       d.G2 * d.G1, d.G2, d.A * d.H2, d.A, d.G2, 1};
@@ -1925,7 +1933,7 @@ int plan(UpdArgs& P) {
     P.smem_floats = o;
     P.small_first = (d.O <= 32 && ((d.H1 * d.O + 3) & ~3) + d.G1 * d.O <= 2 * sf) ? 1 : 0;
     P.first_ts = (P.small_first && ((((d.H1 * d.O + 3) & ~3) + d.G1 * d.O + 31) & ~31) + 2 * TS_BT_BYTES / 4 <= 2 * sf &&
-                  getenv("DPPO_K2_NO_TS") == nullptr) ? 1 : 0;
+                  k2_path() == DPPO_K2_PATH_AUTO) ? 1 : 0;
     return o;
 }
 
@@ -1960,16 +1968,66 @@ bool make_wmap(CUtensorMap* map, const float* W, int rows, int cols, int box_c, 
 }
 bool ts_eligible(int N, int K) { return N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0; }
 
+// The six tensor maps depend only on (device, theta, theta_old, dims): encoded once per combination and kept.
+// An engine alternates between at most two (theta_old = theta in epoch 0, the lagging copy afterwards).
+struct MapEntry {
+    int dev;
+    const float *theta, *theta_old;
+    dppo_dims d;
+    bool ok;
+    CUtensorMap fwd[2][2], dx[2];
+};
+constexpr int MAP_CACHE = 16;
+MapEntry g_maps[MAP_CACHE];
+int g_maps_used = 0, g_maps_next = 0;
+
+const MapEntry* wide_layer_maps(int dev, const float* theta, const float* theta_old, const dppo_dims& d, const Layout& lay) {
+    for (int i = 0; i < g_maps_used; ++i) {
+        const MapEntry& e = g_maps[i];
+        if (e.dev == dev && e.theta == theta && e.theta_old == theta_old && memcmp(&e.d, &d, sizeof(d)) == 0) return &e;
+    }
+    MapEntry& e = g_maps[g_maps_next];
+    g_maps_next = (g_maps_next + 1) % MAP_CACHE;
+    if (g_maps_used < MAP_CACHE) ++g_maps_used;
+    e.dev = dev; e.theta = theta; e.theta_old = theta_old; e.d = d;
+    bool ok = true;
+    for (int net = 0; net < 2 && ok; ++net) {
+        const float* t = net == 0 ? theta : (theta_old ? theta_old : theta);
+        if (ts_eligible(d.H2, d.H1))
+            ok = ok && make_wmap(&e.fwd[net][0], t + lay.off[3], d.H2, d.H1, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (ts_eligible(d.G2, d.G1))
+            ok = ok && make_wmap(&e.fwd[net][1], t + lay.off[7], d.G2, d.G1, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+    }
+    if (ts_eligible(d.H2, d.H1))
+        ok = ok && make_wmap(&e.dx[0], theta + lay.off[3], d.H2, d.H1, 128, TC_KB, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (ts_eligible(d.G2, d.G1))
+        ok = ok && make_wmap(&e.dx[1], theta + lay.off[7], d.G2, d.G1, 128, TC_KB, CU_TENSOR_MAP_SWIZZLE_NONE);
+    e.ok = ok;
+    return &e;
+}
+
+constexpr int MAX_DEVICES = 64;
+
 }  // namespace
 
+// per-device caches below are indexed by the CUDA device ordinal: one host thread per device, any number of
+// devices per process
 int dppo_sm_count() {
-    static int sms = 0;
-    if (sms == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+    static int sms[MAX_DEVICES] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEVICES) return 148;
+    if (sms[dev] == 0) {
+        if (cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms[dev] <= 0)
+            sms[dev] = 148;
     }
-    return sms;
+    return sms[dev];
+}
+
+extern "C" int dppo_update_set_path(int path) {
+    if (path != DPPO_K2_PATH_AUTO && path != DPPO_K2_PATH_FP32) return DPPO_E_BADARG;
+    const int prev = k2_path();
+    g_k2_path = path;
+    return prev;
 }
 
 extern "C" int dppo_param_layout(const dppo_dims* d, int* offsets_host, int* sizes_host) {
@@ -2029,26 +2087,22 @@ extern "C" int dppo_update_fused(int flavour, const dppo_dims* d, const float* o
     const size_t smem = sizeof(float) * (size_t)P.smem_floats;
     if (smem > 227 * 1024 || P.SF < UPD_STAGE_MIN) return DPPO_E_TOOLARGE;
     // tensor-core path of the wide layers: needs the 100 KB staging region and tensor maps of the weights
+    int dev = 0;
+    DPPO_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) return DPPO_E_BADARG;
     P.use_ts = 0;
-    if ((size_t)2 * P.SF * sizeof(float) >= (size_t)TS_BYTES && getenv("DPPO_K2_NO_TS") == nullptr) {
-        bool ok = true;
-        for (int net = 0; net < 2 && ok; ++net) {
-            const float* t = net == 0 ? theta : (theta_old ? theta_old : theta);
-            if (ts_eligible(d->H2, d->H1))
-                ok = ok && make_wmap(&P.map_fwd[net][0], t + P.lay.off[3], d->H2, d->H1, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
-            if (ts_eligible(d->G2, d->G1))
-                ok = ok && make_wmap(&P.map_fwd[net][1], t + P.lay.off[7], d->G2, d->G1, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+    if ((size_t)2 * P.SF * sizeof(float) >= (size_t)TS_BYTES && k2_path() == DPPO_K2_PATH_AUTO) {
+        const MapEntry* e = wide_layer_maps(dev, theta, theta_old, *d, P.lay);
+        if (e->ok) {
+            memcpy(P.map_fwd, e->fwd, sizeof(P.map_fwd));
+            memcpy(P.map_dx, e->dx, sizeof(P.map_dx));
+            P.use_ts = 1;
         }
-        if (ts_eligible(d->H2, d->H1))
-            ok = ok && make_wmap(&P.map_dx[0], theta + P.lay.off[3], d->H2, d->H1, 128, TC_KB, CU_TENSOR_MAP_SWIZZLE_NONE);
-        if (ts_eligible(d->G2, d->G1))
-            ok = ok && make_wmap(&P.map_dx[1], theta + P.lay.off[7], d->G2, d->G1, 128, TC_KB, CU_TENSOR_MAP_SWIZZLE_NONE);
-        P.use_ts = ok ? 1 : 0;
     }
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
+    static size_t smem_set[MAX_DEVICES] = {0};                  // the attribute is per device
+    if (smem > smem_set[dev]) {
         DPPO_CUDA_TRY(cudaFuncSetAttribute(update_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        smem_set = smem;
+        smem_set[dev] = smem;
     }
     update_fused_kernel<<<nparts, UPD_THREADS, smem, (cudaStream_t)stream_>>>(P);
     DPPO_LAUNCH_CHECK();

@@ -53,9 +53,10 @@ def train(env, model, optimizer, shared_obs_stats):
 
     for t in range(p.time_horizon):
         buf, state, episode_length = collect_rollout(env, model, shared_obs_stats, _Roll, state, episode_length,
-                                                     std_is_variance=False)           # ppo.py:93
+                                                     std_is_variance=False,           # ppo.py:93
+                                                     out=engine.rollout_buffer(p.num_steps))
         engine.gae(buf)
         engine.draw_indices(buf.T)
-        losses = engine.run_epochs(buf)
+        losses = engine.run_epochs(buf, use_graph=getattr(p, "use_graph", True))
         print('horizon', t, 'loss', losses[-1, :3].tolist())
     return engine

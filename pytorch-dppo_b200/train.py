@@ -84,11 +84,12 @@ def _make_env(params):
     return gym.make(params.env_name)
 
 
-def collect_rollout(env, model, shared_obs_stats, params, state, episode_length, std_is_variance=True):
+def collect_rollout(env, model, shared_obs_stats, params, state, episode_length, std_is_variance=True, out=None):
     """train.py:69-124 for ONE exploration phase: steps the env until at least
     ``exploration_size`` steps are stored, returns a RolloutBuffer holding the last
     ``exploration_size`` of them (raw states are normalised per step through
-    Shared_obs_stats as at train.py:84-85)."""
+    Shared_obs_stats as at train.py:84-85).  ``out``: a RolloutBuffer of that length to
+    fill (the engine's persistent one, UpdateEngine.rollout_buffer) instead of a new one."""
     dev = model.device
     cols = dict(obs=[], act=[], rew=[], val=[], boot=[], seg_end=[], logp=[])
     w = -1
@@ -124,7 +125,9 @@ def collect_rollout(env, model, shared_obs_stats, params, state, episode_length,
         cols["seg_end"] += [0] * (n_seg - 1) + [1]
         cols["boot"] += [0.0] * (n_seg - 1) + [boot]
     T = params.exploration_size
-    buf = RolloutBuffer(T, model.dims.O, model.dims.A, dev)
+    buf = out if out is not None else RolloutBuffer(T, model.dims.O, model.dims.A, dev)
+    if buf.T != T:
+        raise nv.DppoError("collect_rollout: out holds %d steps, the rollout has %d" % (buf.T, T))
     buf.obs.copy_(torch.cat(cols["obs"], 0)[-T:]); buf.act.copy_(torch.cat(cols["act"], 0)[-T:])
     buf.val.copy_(torch.cat(cols["val"], 0)[-T:]); buf.logp.copy_(torch.cat(cols["logp"], 0)[-T:])
     buf.rew.copy_(torch.tensor(cols["rew"][-T:])); buf.boot.copy_(torch.tensor(cols["boot"][-T:]))
@@ -148,11 +151,13 @@ def train(rank, params, traffic_light, counter, shared_model, shared_grad_buffer
     outer = 0
     while getattr(params, "max_outer_iters", None) is None or outer < params.max_outer_iters:
         outer += 1
-        buf, state, episode_length = collect_rollout(env, model, shared_obs_stats, params, state, episode_length)
+        buf, state, episode_length = collect_rollout(env, model, shared_obs_stats, params, state, episode_length,
+                                                     out=engine.rollout_buffer(params.exploration_size))
         engine.gae(buf)                                                      # train.py:108-122
         engine.draw_indices(buf.T)                                           # train.py:140, all epochs
         if fused:
-            engine.run_epochs(buf, gshared=shared_grad_buffers.flat)         # train.py:133-175 + chief.py:13-20
+            engine.run_epochs(buf, gshared=shared_grad_buffers.flat,         # train.py:133-175 + chief.py:13-20
+                              use_graph=getattr(params, "use_graph", True))
             for _ in range(params.num_epoch):
                 counter.increment()
                 counter.reset()

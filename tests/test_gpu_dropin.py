@@ -121,6 +121,89 @@ def test_ppo_train_runs():
     assert eng.step == 8 and torch.isfinite(model.flat).all() and not torch.equal(model.flat, before)
 
 
+def _train_dppo_n(outer, use_graph):
+    import random
+    from model import Model, Shared_grad_buffers, Shared_obs_stats
+    from train import train
+    from utils import Counter, TrafficLight
+    O, A = 5, 2
+    torch.manual_seed(1)
+    random.seed(11)                                              # the reference never seeds random.sample; we do, to compare
+    model = Model(O, A, device=DEV)
+    sgb, stats = Shared_grad_buffers(model), Shared_obs_stats(O)
+    p = _params(O, A)
+    p.max_outer_iters, p.use_graph = outer, use_graph
+    p.engine = None
+    train(0, p, TrafficLight(), Counter(), model, sgb, stats, torch.zeros(1))
+    torch.cuda.synchronize()
+    return model.flat.clone(), stats.mean.clone()
+
+
+def test_train_six_outer_iterations_graph_replay_equals_plain_launches():
+    """The loop of train.py:60-178 run for six outer iterations.  Every iteration refills the engine's one rollout
+    buffer, so the cycle captured in the first iteration is replayed on the right memory in all later ones; the
+    result must be bit-identical to the same run with plain kernel launches."""
+    a = _train_dppo_n(6, True)
+    b = _train_dppo_n(6, False)
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+
+
+def test_ppo_train_six_horizons_graph_replay_equals_plain_launches():
+    import random
+    import torch.optim as optim
+    import ppo as ppo_mod
+    from model import Model, Shared_obs_stats
+    O, A = 6, 3
+    res = []
+    for use_graph in (True, False):
+        torch.manual_seed(1)
+        random.seed(12)
+        model = Model(O, A, device=DEV)
+        p = ppo_mod.Params()
+        p.batch_size, p.num_epoch, p.num_steps, p.time_horizon, p.use_graph = 32, 4, 96, 6, use_graph
+        ppo_mod.params = p
+        try:
+            eng = ppo_mod.train(FakeEnv(O, A, 9), model, optim.Adam(model.parameters(), lr=p.lr), Shared_obs_stats(O))
+        finally:
+            ppo_mod.params = None
+        torch.cuda.synchronize()
+        assert eng.step == 24
+        res.append((model.flat.clone(), eng.m.clone()))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+
+
+def test_graph_cache_is_keyed_by_addresses_not_object_ids():
+    """A NEW RolloutBuffer per outer iteration (what a caller that ignores rollout_buffer() does): Python reuses
+    the ids of freed objects, the allocator reuses or moves their memory.  Every cycle must still run on the
+    buffer that was passed in - compared with plain launches - and the cache must stay bounded."""
+    import random
+    import b200_native as nv
+    from b200_engine import RolloutBuffer, UpdateEngine
+    from model import Model
+    T, B, E, O, A = 1024, 128, 2, 17, 6
+    res = []
+    for use_graph in (True, False):
+        torch.manual_seed(1)
+        m = Model(O, A, device=DEV)
+        eng = UpdateEngine(m, nv.FLAVOUR_DPPO, B, E, 3e-4)
+        rng = random.Random(2)
+        g = torch.Generator().manual_seed(5)
+        keep = []
+        for it in range(8):
+            buf = RolloutBuffer(T, O, A, DEV)
+            buf.obs.copy_(torch.randn(T, O, generator=g)); buf.act.copy_(torch.randn(T, A, generator=g))
+            buf.adv.copy_(torch.randn(T, generator=g)); buf.ret.copy_(torch.randn(T, generator=g))
+            if it % 3 == 0:
+                keep.append(torch.empty(T * (it + 1), device=DEV))    # perturb the allocator's free lists
+            eng.draw_indices(T, rng)
+            eng.run_epochs(buf, use_graph=use_graph)
+            del buf
+        torch.cuda.synchronize()
+        assert len(eng._graphs) <= eng.MAX_GRAPHS
+        res.append(m.flat.clone())
+    assert torch.equal(res[0], res[1])
+
+
 def test_obs_stats_single_step_api_matches_reference_semantics():
     from model import Shared_obs_stats
     s = Shared_obs_stats(3)

@@ -281,6 +281,11 @@ CASES = [
     (15, 3, (100, 100, 500, 100), 2048, 2048),         # C3: HopperBullet shape
     (17, 6, (128, 128, 128, 128), 1024, 1024),         # 128-wide: every hidden layer on the tcgen05 path
     (11, 3, (96, 96, 160, 96), 700, 450),              # odd numbers of 32-wide k-blocks (3 and 5) in the tensor-core pipeline
+    # the exact shapes bench.py times (BASELINE configs): tile size and CTA count as in the benchmark
+    (17, 6, (100, 100, 500, 100), 65536, 4096),        # C4: TM = 28, 147 CTAs
+    (376, 17, (256, 256, 256, 256), 32768, 4096),      # C5 at its full minibatch
+    (4, 1, (64, 64, 64, 64), 2048, 64),                # C1 with BASELINE's 64x64 nets
+    (17, 6, (64, 64, 64, 64), 2048, 2048),             # C2 with 64x64 nets
 ]
 
 
@@ -331,10 +336,10 @@ def test_update_epoch0_ratio_is_one(nv):
 
 
 @pytest.mark.parametrize("flavour_name", ["dppo", "ppo"])
-def test_update_fp32_pipe_path_vs_oracle_and_tensor_path(nv, flavour_name, monkeypatch):
+def test_update_fp32_pipe_path_vs_oracle_and_tensor_path(nv, flavour_name):
     """The reference-sized layers have two implementations: tcgen05 through tensor memory (default) and the
-    register-tiled FP32-pipe layers (every other shape; forced here with DPPO_K2_NO_TS).  Both must meet the
-    oracle at 1e-5 and each other."""
+    register-tiled FP32-pipe layers (every other shape; forced here with dppo_update_set_path).  Both must meet
+    the oracle at 1e-5 and each other."""
     fl = nv.FLAVOUR_DPPO if flavour_name == "dppo" else nv.FLAVOUR_PPO
     s = _setup_update(nv, 17, 6, (100, 100, 500, 100), 4096, 3000, 11, fl)
     dims, off, size, p_pad, p, p_old, obs, act, adv, ret, logp, idx = s
@@ -344,9 +349,11 @@ def test_update_fp32_pipe_path_vs_oracle_and_tensor_path(nv, flavour_name, monke
     else:
         terms, grads = orc.ppo_loss_grads(p, obs[ii], act[ii], ret[ii], adv[ii], logp[ii], 0.2, 0.01)
     G_ts, L_ts = _run_update(nv, fl, *s, ent=0.01)
-    monkeypatch.setenv("DPPO_K2_NO_TS", "1")
-    G_fp, L_fp = _run_update(nv, fl, *s, ent=0.01)
-    monkeypatch.delenv("DPPO_K2_NO_TS")
+    prev = nv.update_set_path(nv.K2_PATH_FP32)
+    try:
+        G_fp, L_fp = _run_update(nv, fl, *s, ent=0.01)
+    finally:
+        nv.update_set_path(prev)
     assert not torch.equal(G_ts, G_fp)                   # different arithmetic: the switch did switch
     got_ts, got_fp = from_flat(G_ts, off, size, dims.shapes()), from_flat(G_fp, off, size, dims.shapes())
     for k in orc.PARAM_ORDER:

@@ -27,15 +27,48 @@ def unpadded(flat, offsets, sizes):
     return torch.cat([flat[offsets[i]:offsets[i] + sizes[i]] for i in range(len(sizes))])
 
 
-def assert_close_scaled(got, ref, rel=1e-5, name=""):
-    """max |got-ref| <= rel * max |ref|  (per-tensor tolerance)."""
+# Two criteria:
+#   per tensor     max|got-ref| <= rel * max|ref|                                   (north_star's 1e-5 relative)
+#   element-wise   |got_i-ref_i| <= ELEM_RTOL*|ref_i| + elem_atol * max|ref|        (survey: elem_atol = 1e-8)
+# Every comparison records the smallest elem_atol that would pass (CLOSENESS); conftest writes the table to
+# gpurun_out/closeness_report.json so the tensors that need more than 1e-8 are listed with their numbers.
+# Which ones do, and why: results of long fp32 reductions (gradients, means) whose terms cancel.  An entry that is
+# 1e-3 of the tensor's largest carries the absolute rounding error of the whole reduction (~1e-7 * scale), i.e.
+# 1e-4 relative to itself - for the reference's own fp32 run just as for ours (test_elementwise_floor_of_the_reference
+# measures the reference against its fp64 self).  ELEM_ATOL_REDUCTION is the bound asserted for those.
+ELEM_RTOL = 1e-5
+ELEM_ATOL_SURVEY = 1e-8
+ELEM_ATOL_REDUCTION = 2e-6
+CLOSENESS = []
+
+
+def closeness(got, ref):
     got = torch.as_tensor(got, dtype=torch.float64).reshape(-1)
     ref = torch.as_tensor(ref, dtype=torch.float64).reshape(-1)
-    assert got.shape == ref.shape, (name, got.shape, ref.shape)
-    assert torch.isfinite(got).all(), name
-    scale = float(ref.abs().max()) if ref.numel() else 0.0
-    err = float((got - ref).abs().max()) if ref.numel() else 0.0
-    assert err <= rel * max(scale, 1e-30), "%s: max err %.3e > %.1e * scale %.3e" % (name, err, rel, scale)
+    if ref.numel() == 0:
+        return dict(scale=0.0, max_err=0.0, rel=0.0, elem_atol_needed=0.0, n=0, n_beyond_survey=0)
+    scale = float(ref.abs().max())
+    d = (got - ref).abs()
+    excess = (d - ELEM_RTOL * ref.abs()).clamp_(min=0.0)
+    s = max(scale, 1e-30)
+    return dict(scale=scale, max_err=float(d.max()), rel=float(d.max()) / s, elem_atol_needed=float(excess.max()) / s,
+                n=int(ref.numel()), n_beyond_survey=int((excess > ELEM_ATOL_SURVEY * s).sum()))
+
+
+def assert_close_scaled(got, ref, rel=1e-5, name="", elem_atol=None):
+    """Per-tensor bound always; the element-wise bound too when ``elem_atol`` is given."""
+    got_t = torch.as_tensor(got, dtype=torch.float64).reshape(-1)
+    ref_t = torch.as_tensor(ref, dtype=torch.float64).reshape(-1)
+    assert got_t.shape == ref_t.shape, (name, got_t.shape, ref_t.shape)
+    assert torch.isfinite(got_t).all(), name
+    c = closeness(got_t, ref_t)
+    CLOSENESS.append(dict(name=name, **c))
+    assert c["max_err"] <= rel * max(c["scale"], 1e-30), \
+        "%s: max err %.3e > %.1e * scale %.3e" % (name, c["max_err"], rel, c["scale"])
+    if elem_atol is not None:
+        assert c["elem_atol_needed"] <= elem_atol, \
+            "%s: element-wise |d| <= %.0e|ref| + atol*scale needs atol %.3e > %.1e (scale %.3e, %d of %d beyond 1e-8)" % (
+                name, ELEM_RTOL, c["elem_atol_needed"], elem_atol, c["scale"], c["n_beyond_survey"], c["n"])
 
 
 def synth_batch(O, A, T, seed=0):
