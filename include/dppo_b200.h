@@ -102,6 +102,23 @@ int dppo_welford(const float* obs, float* out, int64_t T, int O,
                  float* n, float* mean, float* mean_diff, float* var,
                  void* scratch, size_t scratch_bytes, void* stream);
 
+/* Statistics shared by W workers (the reference has ONE Shared_obs_stats object in shared memory that every
+ * worker updates, main.py:54, train.py:84-85).  Here every worker holds a replica and the rollouts of one outer
+ * iteration enter in RANK ORDER: worker r's rows are normalised with the statistics of everything before this
+ * iteration, plus the whole rollouts of workers 0..r-1, plus its own rows so far; afterwards every replica holds
+ * the statistics of all W rollouts.  Three steps per rollout:
+ *   dppo_welford_totals  this worker's (rows, S1[O], S2[O]) relative to the current mean -> totals[1+2*O] (doubles)
+ *   all-gather of the W vectors in rank order (dppo_comm_allgather, or any collective) -> totals_all[W][1+2*O]
+ *   dppo_welford_shared  as dppo_welford, with the other workers' totals taken into account
+ * world == 1 reproduces dppo_welford exactly in the normalised rows; the final state comes from the totals. */
+size_t dppo_welford_totals_scratch_bytes(int64_t T, int O);
+int dppo_welford_totals(const float* obs, int64_t T, int O, const float* mean, double* totals,
+                        void* scratch, size_t scratch_bytes, void* stream);
+int dppo_welford_shared(const float* obs, float* out, int64_t T, int O,
+                        float* n, float* mean, float* mean_diff, float* var,
+                        const double* totals_all, int rank, int world,
+                        void* scratch, size_t scratch_bytes, void* stream);
+
 /* ---- K2: fused minibatch gather + actor-critic forward/backward + losses --
  * Replaces ReplayMemory.sample (train.py:31-33) + train.py:140-166 (flavour
  * DPPO) or ppo.py:147-172 (flavour PPO) + Model.forward (model.py:35-45) and
@@ -197,6 +214,13 @@ int dppo_allreduce_adam_loopback(dppo_comm** comms, int world, const float* cons
                                  int step, double lr, double beta1, double beta2, double eps,
                                  float* const* grad_out, void* stream);
 int dppo_reduce_partials(const float* partials, int nparts, float* out, int P_pad, void* stream);
+/* Small all-gather over the same peer channel (no NCCL): every rank contributes `count` doubles
+ * (count <= 8193), dst[W][count] receives all ranks' vectors in rank order.  Every rank must call it the same
+ * number of times.  Used for the shared observation statistics above (Shared_obs_stats in shared memory,
+ * main.py:54, model.py:61-66). */
+int dppo_comm_allgather(dppo_comm* c, const double* src, double* dst, int count, void* stream);
+int dppo_comm_allgather_loopback(dppo_comm** comms, int world, const double* const* src, double* const* dst,
+                                 int count, void* stream);
 
 /* ---- a4: minibatch positions (HOST function, no GPU work) ------------------
  * Replaces ``random.sample(self.memory, batch_size)`` (train.py:31-33 /

@@ -62,6 +62,17 @@ class PeerComm:
                        scalars_dev=eng.scalars_dev[k])
         return 2
 
+    def allgather(self, src, dst):
+        """Every rank's ``src`` (float64 vector) into ``dst`` (W, len) in rank order - the observation statistics that
+        the reference's workers share through one shm object (main.py:54).  Returns the number of kernels launched."""
+        if self.mode == "p2p":
+            if self.handle is None:
+                raise nv.DppoError("PeerComm.allgather before the communicator was set up (build the UpdateEngine first)")
+            nv.comm_allgather(self.handle, src, dst)
+        else:
+            dist.all_gather_into_tensor(dst, src, group=self.group)
+        return 1
+
     def describe(self):
         return {"mode": self.mode, "world": self.world,
                 "kernel": "dppo_allreduce_adam (push over NVLink peer memory + flags, fused with Adam)"

@@ -66,6 +66,8 @@ class UpdateEngine:
         self.lr, self.clip, self.ent_coeff, self.max_grad_norm = lr, clip, ent_coeff, max_grad_norm
         self.gamma, self.gae_param, self.betas, self.eps = gamma, gae_param, betas, eps
         self.comm = comm
+        if comm is not None:
+            comm._ensure(self.P_pad)                 # collective: every rank builds its engine at the same point
         dev = model.flat.device
         self.device = dev
         self.theta = model.flat
@@ -111,6 +113,8 @@ class UpdateEngine:
         if obs_stats is not None:
             ptrs += [t.data_ptr() for t in (obs_stats.n, obs_stats.mean, obs_stats.mean_diff, obs_stats.var,
                                             obs_stats._scratch_for(buf.T))]
+            if self.comm is not None and self.comm.world > 1:
+                ptrs += [t.data_ptr() for t in obs_stats._shared_for(buf.T, self.comm.world)]
         if with_gae:
             ptrs.append(self._gae_scratch.data_ptr())
         return (buf.T, bool(with_gae), obs_stats is not None) + tuple(ptrs)
@@ -135,8 +139,8 @@ class UpdateEngine:
     def _launch_epochs(self, buf, gshared, obs_stats=None, with_gae=False):
         n = 0
         if obs_stats is not None:                              # K4: raw observations -> normalised states
-            obs_stats.observes_batch(buf.raw_obs, out=buf.obs)
-            n += 3
+            obs_stats.observes_batch(buf.raw_obs, out=buf.obs, comm=self.comm)
+            n += 1 if self.comm is None or self.comm.world == 1 else 4
         if with_gae:                                           # K1
             self.gae(buf)
             n += 1
@@ -232,7 +236,7 @@ class UpdateEngine:
             fields.append("logp")
         h2d = dev.copy_from(host, fields)
         if obs_stats is not None:
-            obs_stats.observes_batch(dev.raw_obs, out=dev.obs)
+            obs_stats.observes_batch(dev.raw_obs, out=dev.obs, comm=self.comm)
         self.gae(dev)
         # the host draws the minibatch positions while the GPU is busy with the copies, K4 and K1
         if self._prefetched == (dev.T, id(rng)):

@@ -61,6 +61,11 @@ def _load():
         "dppo_gae_scan_noalloc": (i32, [vp, vp, vp, vp, vp, vp, i64, dbl, dbl, vp]),
         "dppo_welford_scratch_bytes": (sz, [i64, i32]),
         "dppo_welford": (i32, [vp, vp, i64, i32, vp, vp, vp, vp, vp, sz, vp]),
+        "dppo_welford_totals_scratch_bytes": (sz, [i64, i32]),
+        "dppo_welford_totals": (i32, [vp, i64, i32, vp, vp, vp, sz, vp]),
+        "dppo_welford_shared": (i32, [vp, vp, i64, i32, vp, vp, vp, vp, vp, i32, i32, vp, sz, vp]),
+        "dppo_comm_allgather": (i32, [vp, vp, vp, i32, vp]),
+        "dppo_comm_allgather_loopback": (i32, [c.POINTER(vp), i32, c.POINTER(vp), c.POINTER(vp), i32, vp]),
         "dppo_update_nparts": (i32, [dp, i32]),
         "dppo_update_partials_bytes": (sz, [dp, i32]),
         "dppo_update_fused": (i32, [i32, dp, vp, vp, vp, vp, vp, vp, i32, vp, vp, flt, flt, vp, vp, vp]),
@@ -156,6 +161,38 @@ def welford(obs, out, n, mean, mean_diff, var, scratch):
     T, O = obs.shape
     check(lib.dppo_welford(_ptr(obs), _ptr(out), T, O, _ptr(n), _ptr(mean), _ptr(mean_diff), _ptr(var),
                            _ptr(scratch, torch.uint8), scratch.numel(), _stream()))
+
+
+def welford_totals_scratch_bytes(T, O):
+    return lib.dppo_welford_totals_scratch_bytes(T, O)
+
+
+def welford_totals(obs, mean, totals, scratch):
+    """This worker's (rows, S1[O], S2[O]) relative to ``mean`` into ``totals`` (1+2*O doubles)."""
+    T, O = obs.shape
+    check(lib.dppo_welford_totals(_ptr(obs), T, O, _ptr(mean), _ptr(totals, torch.float64),
+                                  _ptr(scratch, torch.uint8), scratch.numel(), _stream()))
+
+
+def welford_shared(obs, out, n, mean, mean_diff, var, totals_all, rank, scratch):
+    """K4 with statistics shared by the workers in rank order; ``totals_all`` is (W, 1+2*O) float64."""
+    T, O = obs.shape
+    check(lib.dppo_welford_shared(_ptr(obs), _ptr(out), T, O, _ptr(n), _ptr(mean), _ptr(mean_diff), _ptr(var),
+                                  _ptr(totals_all, torch.float64), rank, totals_all.shape[0],
+                                  _ptr(scratch, torch.uint8), scratch.numel(), _stream()))
+
+
+def comm_allgather(comm, src, dst):
+    check(lib.dppo_comm_allgather(comm, _ptr(src, torch.float64), _ptr(dst, torch.float64), src.numel(), _stream()))
+
+
+def comm_allgather_loopback(comms, srcs, dsts):
+    W = len(comms)
+    vp = ctypes.c_void_p
+    cc = (vp * W)(*[c.value for c in comms])
+    s = (vp * W)(*[_ptr(t, torch.float64) for t in srcs])
+    d = (vp * W)(*[_ptr(t, torch.float64) for t in dsts])
+    check(lib.dppo_comm_allgather_loopback(cc, W, s, d, srcs[0].numel(), _stream()))
 
 
 def update_nparts(dims, B):

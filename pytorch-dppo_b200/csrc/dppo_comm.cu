@@ -38,6 +38,7 @@ namespace {
 constexpr int CM_MAX_WORLD = 8;
 constexpr int CM_THREADS = 256;            // 8 warps: partial groups
 constexpr int CM_RQ = 32;                  // float4 columns per block
+constexpr int CM_AG_MAX = 1 + 2 * 4096;    // doubles per rank in dppo_comm_allgather (rows + 2 sums per observation column)
 constexpr long long CM_SPIN_BUDGET = 8000000000LL;   // clock64() cycles a poll may wait (~4 s at 1.9 GHz)
 
 struct AdamScalars { float w1, b2, a2, bc2_sqrt, eps, alpha; };
@@ -48,6 +49,8 @@ struct CommDev {                            // everything a kernel needs, by val
     unsigned* epoch;                        // this rank: completed epochs
     unsigned* done;                         // this rank: CTAs finished in the current launch
     unsigned* err;                          // this rank: non-zero once a poll has timed out
+    uint4* ag[CM_MAX_WORLD];                // ag[r]: rank r's all-gather buffer [2][world][CM_AG_MAX] LL words (peer-mapped)
+    unsigned* ag_epoch;                     // this rank: completed all-gathers
 };
 
 }  // namespace
@@ -211,7 +214,7 @@ AdamScalars make_scalars(int step, double lr, double beta1, double beta2, double
 
 size_t layout(dppo_comm* c) {
     c->recv_bytes = align_up(sizeof(uint4) * 2 * 2 * (size_t)c->world * c->n4, 256);    // LL: 2x the payload
-    c->flag_bytes = 0;
+    c->flag_bytes = align_up(sizeof(uint4) * 2 * (size_t)c->world * CM_AG_MAX, 256);   // the small all-gather's slots
     return c->recv_bytes + c->flag_bytes + 256;
 }
 
@@ -219,10 +222,12 @@ void fill_dev(dppo_comm* c) {
     c->dev.rank = c->rank; c->dev.world = c->world; c->dev.n4 = c->n4; c->dev.gblocks = c->gblocks;
     for (int r = 0; r < c->world; ++r) {
         c->dev.recv[r] = (uint4*)c->peer_base[r];
+        c->dev.ag[r] = (uint4*)((char*)c->peer_base[r] + c->recv_bytes);
     }
     c->dev.epoch = (unsigned*)((char*)c->base + c->recv_bytes + c->flag_bytes);
     c->dev.done = c->dev.epoch + 1;
     c->dev.err = c->dev.epoch + 2;
+    c->dev.ag_epoch = c->dev.epoch + 3;
 }
 
 // every CTA of the launch must be resident at once (a CTA polls words that the same-numbered CTA of each
@@ -377,6 +382,74 @@ extern "C" int dppo_allreduce_adam_loopback(dppo_comm** comms, int world, const 
     void* args[] = {(void*)&L};
     DPPO_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)allreduce_adam_kernel, dim3(gx, world), dim3(CM_THREADS), args,
                                               0, (cudaStream_t)stream));
+    return 0;
+}
+
+// ---- small all-gather over the same peer channel: every rank contributes `count` doubles and receives all
+// ranks' vectors in rank order.  Used once per rollout for the observation statistics that the reference's
+// workers share (one Shared_obs_stats object in shared memory, main.py:54): each worker's (rows, S1, S2).
+// One CTA per rank; a double travels as ONE 16-byte LL word {lo, epoch, hi, epoch}. ----
+struct AgArgs {
+    CommDev c[CM_MAX_WORLD];
+    const double* src[CM_MAX_WORLD];
+    double* dst[CM_MAX_WORLD];
+    int count;
+};
+__global__ void __launch_bounds__(CM_THREADS) allgather_kernel(const AgArgs A) {
+    const CommDev& C = A.c[blockIdx.x];
+    const unsigned epoch = *reinterpret_cast<volatile unsigned*>(C.ag_epoch) + 1u;
+    const int par = epoch & 1u;
+    const unsigned long long* src = reinterpret_cast<const unsigned long long*>(A.src[blockIdx.x]);
+    for (int i = threadIdx.x; i < A.count; i += CM_THREADS) {
+        const unsigned long long x = src[i];
+        for (int r = 0; r < C.world; ++r) {
+            uint4* d = C.ag[r] + ((size_t)par * C.world + C.rank) * CM_AG_MAX + i;
+            asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(d), "r"((unsigned)x), "r"(epoch),
+                         "r"((unsigned)(x >> 32)), "r"(epoch) : "memory");
+        }
+    }
+    unsigned long long* dst = reinterpret_cast<unsigned long long*>(A.dst[blockIdx.x]);
+    for (int e = threadIdx.x; e < A.count * C.world; e += CM_THREADS) {
+        const int r = e / A.count, i = e - r * A.count;
+        const uint4* q = C.ag[C.rank] + ((size_t)par * C.world + r) * CM_AG_MAX + i;
+        uint4 v = ld_ll(q);
+        if (v.y != epoch || v.w != epoch) {
+            const long long t0 = clock64();
+            while (true) {
+                v = ld_ll(q);
+                if (v.y == epoch && v.w == epoch) break;
+                if (clock64() - t0 > CM_SPIN_BUDGET) { atomicExch(C.err, 1u); break; }
+            }
+        }
+        dst[e] = (unsigned long long)v.x | ((unsigned long long)v.z << 32);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { __threadfence(); *reinterpret_cast<volatile unsigned*>(C.ag_epoch) = epoch; }
+}
+
+extern "C" int dppo_comm_allgather(dppo_comm* c, const double* src, double* dst, int count, void* stream) {
+    if (!c || c->loopback || !src || !dst || count < 1) return DPPO_E_BADARG;
+    if (count > CM_AG_MAX) return DPPO_E_TOOLARGE;
+    if (!c->dev.ag[c->world - 1] || !c->dev.ag[0]) return DPPO_E_COMM;
+    AgArgs A;
+    A.c[0] = c->dev; A.src[0] = src; A.dst[0] = dst; A.count = count;
+    allgather_kernel<<<1, CM_THREADS, 0, (cudaStream_t)stream>>>(A);
+    DPPO_LAUNCH_CHECK();
+    return 0;
+}
+// all virtual ranks of a loopback communicator set in one launch (tests): src[r] / dst[r] per rank
+extern "C" int dppo_comm_allgather_loopback(dppo_comm** comms, int world, const double* const* src, double* const* dst,
+                                            int count, void* stream) {
+    if (!comms || world < 1 || world > CM_MAX_WORLD || !src || !dst || count < 1) return DPPO_E_BADARG;
+    if (count > CM_AG_MAX) return DPPO_E_TOOLARGE;
+    AgArgs A;
+    for (int r = 0; r < world; ++r) {
+        if (!comms[r] || !comms[r]->loopback || comms[r]->world != world) return DPPO_E_COMM;
+        A.c[r] = comms[r]->dev; A.src[r] = src[r]; A.dst[r] = dst[r];
+    }
+    A.count = count;
+    allgather_kernel<<<world, CM_THREADS, 0, (cudaStream_t)stream>>>(A);      // <= 8 CTAs: always co-resident
+    DPPO_LAUNCH_CHECK();
     return 0;
 }
 

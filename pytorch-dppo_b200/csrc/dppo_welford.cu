@@ -1,4 +1,4 @@
-// K4 - running observation statistics + normalisation over a whole rollout.
+// K4 - running observation statistics + normalisation over a whole rollout, ONE pass over HBM.
 //
 // Reference: Shared_obs_stats.observes / normalize (model.py:68-80), called
 // once per environment step (train.py:84-85): n += 1; mean += (x-mean)/n;
@@ -13,181 +13,232 @@
 // sums are carried in fp64, mean_t / M2_t are rounded to fp32 and the
 // normalisation is the reference's fp32 arithmetic.
 //
-// Three launches: (a) per-tile column sums, (b) exclusive scan of the tile sums per column + new
-// state, (c) per-row prefix + normalise.  obs is read in (a) and (c): the second read is an L2 hit
-// while the rollout is smaller than L2 (every named config), else HBM sees 12*O B/row.
+// One launch.  A CTA owns a tile of R rows x CB columns (32 KB of fp32; CB = O for O <= 32, else column
+// blocks of 32), reads it from HBM once into shared memory, forms its column sums, obtains the sums of all
+// rows above it from the tiles before it, normalises the tile in shared memory and streams it out: 8*O
+// bytes per row of HBM traffic.  Tiles are handed out by an atomic ticket, so every tile above a running
+// tile has started and publishes its sums without depending on anything below it (no deadlock whatever
+// the residency).
+//
+// The prefix over the tiles of a column block is DETERMINISTIC: fp64 addition is not associative, so the
+// classic decoupled look-back (which adds whatever mix of aggregates and prefixes it happens to find) would
+// make results depend on timing.  Instead the tiles form a fixed two-level hierarchy - blocks of 16 tiles,
+// super-blocks of 16 blocks - and every tile adds, in a fixed order,
+//     P[a]            the sums of everything before super-block a   (published by the last tile of a-1)
+//   + B[a][0..b-1]    the sums of the blocks before its block       (each published by the block's last tile)
+//   + A[..][0..c-1]   the sums of the tiles before it in its block  (each published by its tile)
+// The only serial chain is P: one link per 256 tiles (~34 links for a 570 MB rollout), far faster than
+// the tiles stream.  Every wait is on a flag with acquire/release semantics; at most 31 payloads are read.
 #include "common.cuh"
 
 namespace {
 
 constexpr int WF_THREADS = 256;
-constexpr int WF_TILE_ELEMS = 8192;                 // 32 KB of fp32 per CTA (16 KB and 64 KB were slower)
-constexpr int64_t WF_CHUNK_BYTES = (int64_t)1 << 40;  // rows per launch group (chunking for L2 reuse did not pay: see DESIGN.md)
+constexpr int WF_TILE_ELEMS = 8192;                 // 32 KB of fp32 per CTA
+constexpr int WF_CB = 32;                           // widest column block
+constexpr int WF_L1 = 16;                           // tiles per block, blocks per super-block
+constexpr int WF_MAX_ROWS = 2048;                   // bounds the per-row reciprocal tables
 
 struct WfGeom {
-    int O, R, G, RPG;                               // rows per tile, row groups per tile, rows per group
+    int O, CB, ncb;                                 // columns, columns per block (last block may be narrower), blocks
+    int R, G, RPG;                                  // rows per tile, row groups per tile, rows per group
     int64_t T;
-    int ntiles;
+    int ntr;                                        // row tiles; tiles in all = ntr * ncb
+    int nb1, nb2;                                   // blocks / super-blocks per column block
 };
 
-__host__ __device__ inline int wf_rows_per_tile(int O) {
-    int R = (WF_TILE_ELEMS / O) & ~3;               // multiple of 4 rows keeps tiles 16-byte aligned
-    if (R > 2048) R = 2048;                         // bounds the per-row reciprocal tables
+struct WfScratch {                                  // carved from the caller's scratch
+    int* ticket;
+    int *flagA, *flagB, *flagP;                     // [ncb][ntr], [ncb][nb1], [ncb][nb2+1]
+    double *payA, *payB, *payP;                     // same shapes x [2*CB]
+};
+
+__host__ __device__ inline int wf_rows_per_tile(int cb) {
+    int R = (WF_TILE_ELEMS / cb) & ~3;              // multiple of 4 rows keeps whole-row tiles 16-byte aligned
+    if (R > WF_MAX_ROWS) R = WF_MAX_ROWS;
     return R < 4 ? 4 : R;
 }
 
-// KEEP: the aggregate pass leaves the rows in L2 for the apply pass (which streams them out)
-template <bool KEEP>
-__device__ __forceinline__ void wf_load_tile(float* s, const float* __restrict__ g, int64_t off, int n, bool vec) {
-    if (vec && (n & 3) == 0) {
-        const float4* g4 = reinterpret_cast<const float4*>(g + off);
-        float4* s4 = reinterpret_cast<float4*>(s);
-        for (int i = threadIdx.x; i < n / 4; i += WF_THREADS) s4[i] = KEEP ? __ldg(&g4[i]) : __ldcs(&g4[i]);
-    } else {
-        for (int i = threadIdx.x; i < n; i += WF_THREADS) s[i] = g[off + i];
-    }
+__device__ __forceinline__ void wf_wait_flag(const int* f) {
+    while (ld_acquire_gpu(f) == 0) { }
 }
 
-// group-local sums: item (g,c) walks rows [g*RPG, min((g+1)*RPG, rows)) of column c
-__device__ __forceinline__ void wf_group_sums(const float* s, const float* s_p, const WfGeom& q, int rows,
-                                              double* s_g1, double* s_g2) {
-    for (int it = threadIdx.x; it < q.G * q.O; it += WF_THREADS) {
-        const int g = it / q.O, c = it - g * q.O;
+// dynamic smem: float tile[R*CB] | float p[CB], M0[CB] | double g1[G*CB], g2[G*CB] | double base[2*CB], agg[2*CB] |
+//               union { double look[31][2*CB];  double inv[R] + float nf[R] }
+__global__ void __launch_bounds__(WF_THREADS)
+wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const WfGeom q, float* __restrict__ n,
+                float* __restrict__ mean, float* __restrict__ mean_diff, float* __restrict__ var, const WfScratch w,
+                const bool vec, const double* __restrict__ totals, const int rank, const int world) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ int s_ticket;
+    float* s = reinterpret_cast<float*>(smem_raw);
+    float* s_p = s + q.R * q.CB;
+    float* s_m0 = s_p + WF_CB;
+    double* s_g1 = reinterpret_cast<double*>(s_m0 + WF_CB);
+    double* s_g2 = s_g1 + q.G * q.CB;
+    double* s_base = s_g2 + q.G * q.CB;
+    double* s_agg = s_base + 2 * WF_CB;
+    double* s_look = s_agg + 2 * WF_CB;
+    double* s_inv = s_look;                           // the look-back staging is dead when the tables are built
+    float* s_nf = reinterpret_cast<float*>(s_inv + q.R);
+
+    if (threadIdx.x == 0) s_ticket = atomicAdd(w.ticket, 1);
+    __syncthreads();
+    const int rt = s_ticket / q.ncb, cb = s_ticket - rt * q.ncb;     // row tile, column block
+    const int col0 = cb * q.CB, cw = min(q.CB, q.O - col0);           // this block's columns
+    const int V = 2 * q.CB;                                           // payload doubles per tile
+    const int64_t row0 = (int64_t)rt * q.R;
+    const int rows = (int)min((int64_t)q.R, q.T - row0);
+    const float n0f = n[col0];                                        // read before this tile publishes anything:
+    for (int c = threadIdx.x; c < cw; c += WF_THREADS) {              // the state is rewritten only by the LAST row
+        s_p[c] = mean[col0 + c];                                      // tile, which waits (transitively) for every
+        s_m0[c] = mean_diff[col0 + c];                                // other tile's sums
+    }
+    // ---- tile -> shared memory (the only read of obs) ----
+    if (cw == q.O) {
+        const int nel = rows * q.O;
+        const int64_t off = row0 * q.O;
+        if (vec && (nel & 3) == 0) {
+            const float4* g4 = reinterpret_cast<const float4*>(obs + off);
+            float4* s4 = reinterpret_cast<float4*>(s);
+            for (int i = threadIdx.x; i < nel / 4; i += WF_THREADS) s4[i] = __ldcs(&g4[i]);
+        } else {
+            for (int i = threadIdx.x; i < nel; i += WF_THREADS) s[i] = __ldcs(obs + off + i);
+        }
+    } else {
+        for (int i = threadIdx.x; i < rows * cw; i += WF_THREADS) {
+            const int r = i / cw, c = i - r * cw;
+            s[r * q.CB + c] = __ldcs(obs + (row0 + r) * q.O + col0 + c);
+        }
+    }
+    const int ld = (cw == q.O) ? q.O : q.CB;                          // row stride of the tile in shared memory
+    __syncthreads();
+    // ---- group-local sums: item (g,c) walks rows [g*RPG, min((g+1)*RPG, rows)) of column c ----
+    for (int it = threadIdx.x; it < q.G * cw; it += WF_THREADS) {
+        const int g = it / cw, c = it - g * cw;
         const float p = s_p[c];
         double a1 = 0.0, a2 = 0.0;
         const int r0 = g * q.RPG, r1 = min(r0 + q.RPG, rows);
+#pragma unroll 4
         for (int r = r0; r < r1; ++r) {
-            const double d = (double)__fsub_rn(s[r * q.O + c], p);
+            const double d = (double)__fsub_rn(s[r * ld + c], p);
             a1 += d;
             a2 = fma(d, d, a2);
         }
-        s_g1[it] = a1;
-        s_g2[it] = a2;
-    }
-}
-
-// dynamic smem: float tile[R*O] | float p[O] | double g1[G*O] | double g2[G*O]
-__global__ void __launch_bounds__(WF_THREADS)
-wf_aggregate_kernel(const float* __restrict__ obs, WfGeom q, const float* __restrict__ n, const float* __restrict__ mean,
-                    const float* __restrict__ mean_diff, float* __restrict__ state0, double* __restrict__ agg, bool vec) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    float* s = reinterpret_cast<float*>(smem_raw);
-    float* s_p = s + q.R * q.O;
-    double* s_g1 = reinterpret_cast<double*>(s_p + ((q.O + 3) & ~3));
-    double* s_g2 = s_g1 + q.G * q.O;
-    const int tile = blockIdx.x;
-    const int64_t row0 = (int64_t)tile * q.R;
-    const int rows = (int)min((int64_t)q.R, q.T - row0);
-    for (int c = threadIdx.x; c < q.O; c += WF_THREADS) {
-        s_p[c] = mean[c];
-        if (tile == 0) {                              // keep the pre-rollout state for pass (c)
-            state0[c] = mean[c];
-            state0[q.O + c] = mean_diff[c];
-            if (c == 0) state0[2 * q.O] = n[0];
-        }
-    }
-    wf_load_tile<true>(s, obs, row0 * q.O, rows * q.O, vec);
-    __syncthreads();
-    wf_group_sums(s, s_p, q, rows, s_g1, s_g2);
-    __syncthreads();
-    for (int c = threadIdx.x; c < q.O; c += WF_THREADS) {
-        double a1 = 0.0, a2 = 0.0;
-        for (int g = 0; g < q.G; ++g) { a1 += s_g1[g * q.O + c]; a2 += s_g2[g * q.O + c]; }
-        agg[(size_t)c * q.ntiles + tile] = a1;                                   // [2][O][ntiles]
-        agg[(size_t)(q.O + c) * q.ntiles + tile] = a2;
-    }
-}
-
-// one CTA per column: exclusive scan of the tile sums (in place) and the new state
-__global__ void __launch_bounds__(WF_THREADS)
-wf_scan_kernel(WfGeom q, double* __restrict__ agg, const float* __restrict__ state0, float* __restrict__ n,
-               float* __restrict__ mean, float* __restrict__ mean_diff, float* __restrict__ var) {
-    __shared__ double part[2][WF_THREADS];
-    const int c = blockIdx.x;
-    double* a1 = agg + (size_t)c * q.ntiles;
-    double* a2 = agg + (size_t)(q.O + c) * q.ntiles;
-    const int L = (q.ntiles + WF_THREADS - 1) / WF_THREADS;
-    const int t0 = min(threadIdx.x * L, q.ntiles), t1 = min(t0 + L, q.ntiles);
-    double s1 = 0.0, s2 = 0.0;
-    for (int t = t0; t < t1; ++t) { s1 += a1[t]; s2 += a2[t]; }
-    part[0][threadIdx.x] = s1;
-    part[1][threadIdx.x] = s2;
-    __syncthreads();
-    if (threadIdx.x < 2) {                             // serial exclusive scan of 256 partials, fixed order
-        double run = 0.0;
-        for (int i = 0; i < WF_THREADS; ++i) { const double x = part[threadIdx.x][i]; part[threadIdx.x][i] = run; run += x; }
-        if (threadIdx.x == 0) part[0][0] = 0.0;
+        s_g1[g * q.CB + c] = a1;
+        s_g2[g * q.CB + c] = a2;
     }
     __syncthreads();
-    double r1 = part[0][threadIdx.x], r2 = part[1][threadIdx.x];
-    for (int t = t0; t < t1; ++t) {
-        const double x1 = a1[t], x2 = a2[t];
-        a1[t] = r1; a2[t] = r2;
-        r1 += x1; r2 += x2;
-    }
-    __syncthreads();
-    if (threadIdx.x == WF_THREADS - 1) {               // r1, r2 of the last thread = column totals
-        // (threads whose chunk is empty carry the prefix through unchanged)
-        const float p = state0[c];
-        const double M0 = (double)state0[q.O + c];
-        const double n1 = (double)state0[2 * q.O] + (double)q.T;
-        const double inv = 1.0 / n1;
-        const float nn = (float)n1;
-        const float mm = (float)((double)p + r1 * inv);
-        const float md = (float)(M0 + r2 - r1 * r1 * inv);
-        n[c] = nn;
-        mean[c] = mm;
-        mean_diff[c] = md;
-        var[c] = fmaxf(__fdiv_rn(md, nn), 1e-2f);       // model.py:75
-    }
-}
-
-__global__ void __launch_bounds__(WF_THREADS)
-wf_apply_kernel(const float* __restrict__ obs, float* __restrict__ out, WfGeom q, const float* __restrict__ state0,
-                const double* __restrict__ agg, bool vec) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    float* s = reinterpret_cast<float*>(smem_raw);
-    float* s_p = s + q.R * q.O;
-    double* s_g1 = reinterpret_cast<double*>(s_p + ((q.O + 3) & ~3));
-    double* s_g2 = s_g1 + q.G * q.O;
-    const int tile = blockIdx.x;
-    const int64_t row0 = (int64_t)tile * q.R;
-    const int rows = (int)min((int64_t)q.R, q.T - row0);
-    for (int c = threadIdx.x; c < q.O; c += WF_THREADS) s_p[c] = state0[c];
-    wf_load_tile<false>(s, obs, row0 * q.O, rows * q.O, vec);
-    __syncthreads();
-    wf_group_sums(s, s_p, q, rows, s_g1, s_g2);
-    __syncthreads();
-    // exclusive prefix over the row groups of each column, seeded with the tile prefix
-    for (int c = threadIdx.x; c < q.O; c += WF_THREADS) {
-        double r1 = agg[(size_t)c * q.ntiles + tile], r2 = agg[(size_t)(q.O + c) * q.ntiles + tile];
+    // ---- tile sums (fixed order over the groups), exclusive prefix of the groups in place, publish ----
+    const int tix = cb * q.ntr + rt;                                  // this tile in the [ncb][ntr] arrays
+    if (threadIdx.x < cw) {
+        const int c = threadIdx.x;
+        double r1 = 0.0, r2 = 0.0;
         for (int g = 0; g < q.G; ++g) {
-            const double x1 = s_g1[g * q.O + c], x2 = s_g2[g * q.O + c];
-            s_g1[g * q.O + c] = r1; s_g2[g * q.O + c] = r2;
+            const double x1 = s_g1[g * q.CB + c], x2 = s_g2[g * q.CB + c];
+            s_g1[g * q.CB + c] = r1; s_g2[g * q.CB + c] = r2;
             r1 += x1; r2 += x2;
         }
+        s_agg[c] = r1; s_agg[q.CB + c] = r2;
+        __stcg(&w.payA[(size_t)tix * V + c], r1);
+        __stcg(&w.payA[(size_t)tix * V + q.CB + c], r2);
     }
     __syncthreads();
-    const double n0 = (double)state0[2 * q.O];
-    // per-row 1/n_t (fp64 and fp32), once per row instead of once per element: the int->fp64 and
-    // fp64->fp32 conversions run at 1/8 of the FP32 rate and were the bottleneck of this kernel
-    double* s_inv = s_g2 + q.G * q.O;
-    float* s_nf = reinterpret_cast<float*>(s_inv + q.R);
+    if (threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flagA[tix], 1); }
+    // ---- sums of all rows above this tile: P[a] + B[a][0..b) + A[..][0..c), fixed order ----
+    const int a = rt / (WF_L1 * WF_L1), b = (rt / WF_L1) % WF_L1, c1 = rt % WF_L1;
+    const int nP = a > 0 ? 1 : 0, nlook = nP + b + c1;                // payloads to fetch (<= 31)
+    if (threadIdx.x < nlook) {                                        // one thread per flag: the waits overlap
+        const int j = threadIdx.x;
+        const int* f = j < nP ? &w.flagP[cb * (q.nb2 + 1) + a]
+                     : j < nP + b ? &w.flagB[cb * q.nb1 + (rt / WF_L1 - b) + (j - nP)]
+                                  : &w.flagA[cb * q.ntr + (rt - c1) + (j - nP - b)];
+        wf_wait_flag(f);
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < nlook * V; e += WF_THREADS) {
+        const int j = e / V, v = e - j * V;
+        const double* src = j < nP ? &w.payP[(size_t)(cb * (q.nb2 + 1) + a) * V]
+                          : j < nP + b ? &w.payB[(size_t)(cb * q.nb1 + (rt / WF_L1 - b) + (j - nP)) * V]
+                                       : &w.payA[(size_t)(cb * q.ntr + (rt - c1) + (j - nP - b)) * V];
+        s_look[j * V + v] = __ldcg(src + v);
+    }
+    __syncthreads();
+    const bool pubB = c1 == WF_L1 - 1;                                // last tile of its block
+    const bool pubP = pubB && b == WF_L1 - 1;                         // ... and of its super-block
+    if (threadIdx.x < V) {
+        const int v = threadIdx.x;
+        double sP = nP ? s_look[v] : 0.0, sB = 0.0, sA = 0.0;
+        for (int j = 0; j < b; ++j) sB += s_look[(nP + j) * V + v];
+        for (int j = 0; j < c1; ++j) sA += s_look[(nP + b + j) * V + v];
+        const double own = s_agg[v];
+        // statistics shared by several workers: the rollouts of the workers before this one (rank order) come first
+        double prior = 0.0;
+        if (totals != nullptr) {
+            const int c = v < q.CB ? v : v - q.CB;
+            if (c < cw)
+                for (int r = 0; r < rank; ++r)
+                    prior += totals[(size_t)r * (1 + 2 * q.O) + 1 + (v < q.CB ? 0 : q.O) + col0 + c];
+        }
+        s_base[v] = prior + ((sP + sB) + sA);
+        if (pubB) {
+            const double blk = sA + own;                              // sums of this block's 16 tiles
+            __stcg(&w.payB[(size_t)(cb * q.nb1 + rt / WF_L1) * V + v], blk);
+            if (pubP) __stcg(&w.payP[(size_t)(cb * (q.nb2 + 1) + a + 1) * V + v], (sP + sB) + blk);
+        }
+    }
+    __syncthreads();
+    if (pubB && threadIdx.x == 0) {
+        __threadfence();
+        st_release_gpu(&w.flagB[cb * q.nb1 + rt / WF_L1], 1);
+        if (pubP) st_release_gpu(&w.flagP[cb * (q.nb2 + 1) + a + 1], 1);
+    }
+    // ---- per-row 1/n_t (fp64 and fp32), once per row instead of once per element ----
+    double n0 = (double)n0f, rows_all = (double)q.T;               // rows before this rollout / rows of all workers
+    if (totals != nullptr) {
+        rows_all = 0.0;
+        for (int r = 0; r < world; ++r) {
+            const double tr = totals[(size_t)r * (1 + 2 * q.O)];
+            if (r < rank) n0 += tr;
+            rows_all += tr;
+        }
+    }
     for (int r = threadIdx.x; r < rows; r += WF_THREADS) {
         const double nt = n0 + (double)(row0 + r + 1);
-        const double r0 = (double)__frcp_rn((float)nt);       // fp32 reciprocal + one Newton step in fp64
+        const double r0 = (double)__frcp_rn((float)nt);              // fp32 reciprocal + one Newton step in fp64
         s_inv[r] = r0 * (2.0 - nt * r0);
-        s_nf[r] = (float)s_inv[r];                             // 1/n_t in fp32
+        s_nf[r] = (float)s_inv[r];
     }
     __syncthreads();
-    for (int it = threadIdx.x; it < q.G * q.O; it += WF_THREADS) {
-        const int g = it / q.O, c = it - g * q.O;
+    // ---- the new state, by the tile that holds the last row of this column block ----
+    if (rt == q.ntr - 1 && threadIdx.x < cw) {
+        const int c = threadIdx.x;
+        double t1 = s_base[c] + s_agg[c], t2 = s_base[q.CB + c] + s_agg[q.CB + c];
+        if (totals != nullptr) {                                     // every worker's rows, in rank order: the same
+            t1 = 0.0; t2 = 0.0;                                      // state on every replica
+            for (int r = 0; r < world; ++r) {
+                t1 += totals[(size_t)r * (1 + 2 * q.O) + 1 + col0 + c];
+                t2 += totals[(size_t)r * (1 + 2 * q.O) + 1 + q.O + col0 + c];
+            }
+        }
+        const double n1 = (double)n0f + rows_all, inv = 1.0 / n1;
+        const float nn = (float)n1;
+        const float md = (float)((double)s_m0[c] + t2 - t1 * t1 * inv);
+        n[col0 + c] = nn;
+        mean[col0 + c] = (float)((double)s_p[c] + t1 * inv);
+        mean_diff[col0 + c] = md;
+        var[col0 + c] = fmaxf(__fdiv_rn(md, nn), 1e-2f);             // model.py:75
+    }
+    // ---- per-row prefix + normalise, in place in shared memory ----
+    for (int it = threadIdx.x; it < q.G * cw; it += WF_THREADS) {
+        const int g = it / cw, c = it - g * cw;
         const float p = s_p[c];
-        const double M0 = (double)state0[q.O + c];
-        double a1 = s_g1[it], a2 = s_g2[it];
+        const double M0 = (double)s_m0[c];
+        double a1 = s_base[c] + s_g1[g * q.CB + c], a2 = s_base[q.CB + c] + s_g2[g * q.CB + c];
         const int r0 = g * q.RPG, r1 = min(r0 + q.RPG, rows);
+#pragma unroll 4
         for (int r = r0; r < r1; ++r) {
-            const float x = s[r * q.O + c];
+            const float x = s[r * ld + c];
             const double d = (double)__fsub_rn(x, p);
             a1 += d;
             a2 = fma(d, d, a2);
@@ -198,81 +249,178 @@ wf_apply_kernel(const float* __restrict__ obs, float* __restrict__ out, WfGeom q
             // rsqrt: within 2 ulp of the divide/sqrt form, an order of magnitude fewer instructions
             const float var_t = fmaxf(md_t * s_nf[r], 1e-2f);
             const float xh = __fsub_rn(x, mean_t) * rsqrtf(var_t);
-            s[r * q.O + c] = fminf(fmaxf(xh, -5.f), 5.f);
+            s[r * ld + c] = fminf(fmaxf(xh, -5.f), 5.f);
         }
     }
     __syncthreads();
-    const int nel = rows * q.O;
-    const int64_t off = row0 * q.O;
-    if (vec && (nel & 3) == 0) {
-        float4* o4 = reinterpret_cast<float4*>(out + off);
-        const float4* s4 = reinterpret_cast<const float4*>(s);
-        for (int i = threadIdx.x; i < nel / 4; i += WF_THREADS) __stcs(&o4[i], s4[i]);
+    // ---- stream the tile out (the only write) ----
+    if (cw == q.O) {
+        const int nel = rows * q.O;
+        const int64_t off = row0 * q.O;
+        if (vec && (nel & 3) == 0) {
+            float4* o4 = reinterpret_cast<float4*>(out + off);
+            const float4* s4 = reinterpret_cast<const float4*>(s);
+            for (int i = threadIdx.x; i < nel / 4; i += WF_THREADS) __stcs(&o4[i], s4[i]);
+        } else {
+            for (int i = threadIdx.x; i < nel; i += WF_THREADS) __stcs(out + off + i, s[i]);
+        }
     } else {
-        for (int i = threadIdx.x; i < nel; i += WF_THREADS) out[off + i] = s[i];
+        for (int i = threadIdx.x; i < rows * cw; i += WF_THREADS) {
+            const int r = i / cw, c = i - r * cw;
+            __stcs(out + (row0 + r) * q.O + col0 + c, s[r * q.CB + c]);
+        }
+    }
+}
+
+// ---- column sums of a whole rollout relative to the current mean (the worker's contribution to statistics that
+// several workers share): per-tile sums, then one CTA per column adds them in a fixed order ----
+__global__ void __launch_bounds__(WF_THREADS)
+wf_tile_sums_kernel(const float* __restrict__ obs, int64_t T, int O, int R, const float* __restrict__ mean,
+                    double* __restrict__ part, int ntiles) {
+    __shared__ double sh1[WF_THREADS], sh2[WF_THREADS];
+    const int tile = blockIdx.x, c = blockIdx.y * 32 + (threadIdx.x & 31), g = threadIdx.x >> 5;   // 8 row groups x 32 columns
+    const int64_t row0 = (int64_t)tile * R;
+    const int rows = (int)min((int64_t)R, T - row0);
+    double a1 = 0.0, a2 = 0.0;
+    if (c < O) {
+        const float p = mean[c];
+        for (int r = g; r < rows; r += WF_THREADS / 32) {
+            const double d = (double)__fsub_rn(obs[(row0 + r) * O + c], p);
+            a1 += d;
+            a2 = fma(d, d, a2);
+        }
+    }
+    sh1[threadIdx.x] = a1; sh2[threadIdx.x] = a2;
+    __syncthreads();
+    if (g == 0 && c < O) {
+        for (int k = 1; k < WF_THREADS / 32; ++k) { a1 += sh1[k * 32 + (threadIdx.x & 31)]; a2 += sh2[k * 32 + (threadIdx.x & 31)]; }
+        part[(size_t)c * ntiles + tile] = a1;
+        part[(size_t)(O + c) * ntiles + tile] = a2;
+    }
+}
+__global__ void __launch_bounds__(WF_THREADS)
+wf_totals_kernel(const double* __restrict__ part, int64_t T, int O, int ntiles, double* __restrict__ totals) {
+    __shared__ double sh[WF_THREADS];
+    const int v = blockIdx.x;                                         // 0..2*O-1
+    const double* a = part + (size_t)v * ntiles;
+    const int L = (ntiles + WF_THREADS - 1) / WF_THREADS;
+    const int t0 = min(threadIdx.x * L, ntiles), t1 = min(t0 + L, ntiles);
+    double sum = 0.0;
+    for (int t = t0; t < t1; ++t) sum += a[t];
+    sh[threadIdx.x] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double run = 0.0;
+        for (int i = 0; i < WF_THREADS; ++i) run += sh[i];
+        totals[1 + v] = run;
+        if (v == 0) totals[0] = (double)T;
     }
 }
 
 WfGeom wf_geom(int64_t T, int O) {
     WfGeom q;
     q.O = O; q.T = T;
-    q.R = wf_rows_per_tile(O);
-    q.G = WF_THREADS / O;
+    q.CB = O <= WF_CB ? O : WF_CB;
+    q.ncb = (O + q.CB - 1) / q.CB;
+    q.R = wf_rows_per_tile(q.CB);
+    q.G = WF_THREADS / q.CB;
     if (q.G < 1) q.G = 1;
     if (q.G > q.R) q.G = q.R;
     q.RPG = (q.R + q.G - 1) / q.G;
-    q.ntiles = (int)ceil_div64(T, q.R);
+    q.ntr = (int)ceil_div64(T, q.R);
+    q.nb1 = (q.ntr + WF_L1 - 1) / WF_L1;
+    q.nb2 = (q.nb1 + WF_L1 - 1) / WF_L1;
     return q;
 }
 
 size_t wf_smem_bytes(const WfGeom& q) {
-    return sizeof(float) * ((size_t)q.R * q.O + ((q.O + 3) & ~3)) + 2 * sizeof(double) * (size_t)q.G * q.O +
-           (sizeof(double) + sizeof(float)) * (size_t)q.R + 16;            // + per-row 1/n (fp64) and n (fp32)
+    const size_t look = sizeof(double) * 31 * 2 * q.CB;
+    const size_t tables = (sizeof(double) + sizeof(float)) * (size_t)q.R;
+    return sizeof(float) * ((size_t)q.R * q.CB + 2 * WF_CB) + sizeof(double) * (2 * (size_t)q.G * q.CB + 4 * WF_CB) +
+           (look > tables ? look : tables) + 16;
 }
+
+size_t wf_flag_ints(const WfGeom& q) { return 4 + (size_t)q.ncb * ((size_t)q.ntr + q.nb1 + q.nb2 + 1); }
+size_t wf_flag_bytes(const WfGeom& q) { return align_up(sizeof(int) * wf_flag_ints(q), 16); }
 
 }  // namespace
 
-// scratch: float state0[2*O+1 (padded)] | double agg[2][O][ntiles]
+// scratch: int ticket, flags | double payloads (see WfScratch); only the flags are cleared per call
 extern "C" size_t dppo_welford_scratch_bytes(int64_t T, int O) {
     if (T <= 0 || O <= 0) return 16;
     const WfGeom q = wf_geom(T, O);
-    return align_up(sizeof(float) * (size_t)(2 * O + 1), 16) + 2 * sizeof(double) * (size_t)O * q.ntiles;
+    return wf_flag_bytes(q) + sizeof(double) * 2 * q.CB * (size_t)q.ncb * ((size_t)q.ntr + q.nb1 + q.nb2 + 1);
 }
+
+extern "C" size_t dppo_welford_totals_scratch_bytes(int64_t T, int O) {
+    if (T <= 0 || O <= 0) return 16;
+    return sizeof(double) * 2 * (size_t)O * (size_t)ceil_div64(T, 512);
+}
+
+extern "C" int dppo_welford_totals(const float* obs, int64_t T, int O, const float* mean, double* totals,
+                                   void* scratch, size_t scratch_bytes, void* stream_) {
+    if (T <= 0 || O <= 0 || !obs || !mean || !totals || !scratch) return DPPO_E_BADARG;
+    if (O > 4096 || ceil_div64(T, 512) > 0x7fffffff) return DPPO_E_TOOLARGE;
+    if (scratch_bytes < dppo_welford_totals_scratch_bytes(T, O)) return DPPO_E_SCRATCH;
+    if (!aligned16(scratch)) return DPPO_E_ALIGN;
+    const int ntiles = (int)ceil_div64(T, 512);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    wf_tile_sums_kernel<<<dim3(ntiles, ceil_div(O, 32)), WF_THREADS, 0, stream>>>(obs, T, O, 512, mean, (double*)scratch, ntiles);
+    DPPO_LAUNCH_CHECK();
+    wf_totals_kernel<<<2 * O, WF_THREADS, 0, stream>>>((const double*)scratch, T, O, ntiles, totals);
+    DPPO_LAUNCH_CHECK();
+    return 0;
+}
+
+static int welford_launch(const float* obs, float* out, int64_t T, int O, float* n, float* mean, float* mean_diff,
+                          float* var, const double* totals, int rank, int world, void* scratch, size_t scratch_bytes,
+                          void* stream_);
 
 extern "C" int dppo_welford(const float* obs, float* out, int64_t T, int O, float* n, float* mean, float* mean_diff,
                             float* var, void* scratch, size_t scratch_bytes, void* stream_) {
+    return welford_launch(obs, out, T, O, n, mean, mean_diff, var, nullptr, 0, 1, scratch, scratch_bytes, stream_);
+}
+
+extern "C" int dppo_welford_shared(const float* obs, float* out, int64_t T, int O, float* n, float* mean,
+                                   float* mean_diff, float* var, const double* totals_all, int rank, int world,
+                                   void* scratch, size_t scratch_bytes, void* stream_) {
+    if (!totals_all || world < 1 || rank < 0 || rank >= world) return DPPO_E_BADARG;
+    return welford_launch(obs, out, T, O, n, mean, mean_diff, var, totals_all, rank, world, scratch, scratch_bytes, stream_);
+}
+
+static int welford_launch(const float* obs, float* out, int64_t T, int O, float* n, float* mean, float* mean_diff,
+                          float* var, const double* totals, int rank, int world, void* scratch, size_t scratch_bytes,
+                          void* stream_) {
     if (T < 0 || O <= 0) return DPPO_E_BADARG;
     if (T == 0) return 0;
     if (!obs || !out || !n || !mean || !mean_diff || !var || !scratch) return DPPO_E_BADARG;
     if (O > 4096) return DPPO_E_TOOLARGE;
-    if (ceil_div64(T, wf_rows_per_tile(O)) > 0x7fffffff) return DPPO_E_TOOLARGE;
+    const WfGeom q = wf_geom(T, O);
+    if ((int64_t)q.ntr * q.ncb > 0x3fffffff) return DPPO_E_TOOLARGE;
     if (scratch_bytes < dppo_welford_scratch_bytes(T, O)) return DPPO_E_SCRATCH;
     if (!aligned16(scratch)) return DPPO_E_ALIGN;
     cudaStream_t stream = (cudaStream_t)stream_;
-    float* state0 = (float*)scratch;
-    double* agg = (double*)((char*)scratch + align_up(sizeof(float) * (size_t)(2 * O + 1), 16));
+    WfScratch w;
+    w.ticket = (int*)scratch;
+    w.flagA = w.ticket + 4;
+    w.flagB = w.flagA + (size_t)q.ncb * q.ntr;
+    w.flagP = w.flagB + (size_t)q.ncb * q.nb1;
+    w.payA = (double*)((char*)scratch + wf_flag_bytes(q));
+    w.payB = w.payA + (size_t)2 * q.CB * q.ncb * q.ntr;
+    w.payP = w.payB + (size_t)2 * q.CB * q.ncb * q.nb1;
     const bool vec = aligned16(obs) && aligned16(out);
-    // Row chunks (WF_CHUNK_BYTES each; one chunk in practice).  The running state is carried from chunk
-    // to chunk exactly as between two calls.
-    const int R = wf_rows_per_tile(O);
-    int64_t chunk_rows = ((int64_t)WF_CHUNK_BYTES / ((int64_t)O * 4) / R) * R;
-    if (chunk_rows < R) chunk_rows = R;
-    for (int64_t t0 = 0; t0 < T; t0 += chunk_rows) {
-        const int64_t tc = (T - t0 < chunk_rows) ? T - t0 : chunk_rows;
-        const WfGeom q = wf_geom(tc, O);
-        const size_t smem = wf_smem_bytes(q);
-        if (smem > 48 * 1024 && t0 == 0) {
-            DPPO_CUDA_TRY(cudaFuncSetAttribute(wf_aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            DPPO_CUDA_TRY(cudaFuncSetAttribute(wf_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        }
-        const float* in = obs + t0 * O;
-        float* o = out + t0 * O;
-        wf_aggregate_kernel<<<q.ntiles, WF_THREADS, smem, stream>>>(in, q, n, mean, mean_diff, state0, agg, vec);
-        DPPO_LAUNCH_CHECK();
-        wf_scan_kernel<<<O, WF_THREADS, 0, stream>>>(q, agg, state0, n, mean, mean_diff, var);
-        DPPO_LAUNCH_CHECK();
-        wf_apply_kernel<<<q.ntiles, WF_THREADS, smem, stream>>>(in, o, q, state0, agg, vec);
-        DPPO_LAUNCH_CHECK();
+    const size_t smem = wf_smem_bytes(q);
+    static size_t smem_set[64] = {0};                             // per device
+    int dev = 0;
+    DPPO_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return DPPO_E_BADARG;
+    if (smem > smem_set[dev]) {
+        DPPO_CUDA_TRY(cudaFuncSetAttribute(wf_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        smem_set[dev] = smem;
     }
+    DPPO_CUDA_TRY(cudaMemsetAsync(scratch, 0, wf_flag_bytes(q), stream));
+    wf_fused_kernel<<<q.ntr * q.ncb, WF_THREADS, smem, stream>>>(obs, out, q, n, mean, mean_diff, var, w, vec, totals,
+                                                                  rank, world);
+    DPPO_LAUNCH_CHECK();
     return 0;
 }

@@ -151,10 +151,32 @@ class Shared_obs_stats():
             self._scratch = torch.empty(need, dtype=torch.uint8, device=self.n.device)
         return self._scratch
 
-    def observes_batch(self, obs, out=None):
+    def _shared_for(self, T, world):
+        """Buffers of the rank-ordered sharing across workers: this worker's totals, all workers' totals, scratch."""
+        O = self.n.numel()
+        need = nv.welford_totals_scratch_bytes(T, O)
+        sh = getattr(self, "_shared", None)
+        if sh is None or sh[1].shape[0] != world or sh[2].numel() < need:
+            dev = self.n.device
+            sh = self._shared = (torch.zeros(1 + 2 * O, dtype=torch.float64, device=dev),
+                                 torch.zeros(world, 1 + 2 * O, dtype=torch.float64, device=dev),
+                                 torch.empty(max(need, 16), dtype=torch.uint8, device=dev))
+        return sh
+
+    def observes_batch(self, obs, out=None, comm=None):
+        """A whole rollout through K4.  With ``comm`` (W > 1 workers, one per GPU) the statistics are the ONE set
+        the reference's workers share (main.py:54): the W rollouts of this outer iteration enter in rank order -
+        worker r continues from the rollouts of workers 0..r-1 - and every replica ends with the same state."""
         obs = obs.reshape(-1, self.n.numel()).contiguous()
         out = torch.empty_like(obs) if out is None else out
-        nv.welford(obs, out, self.n, self.mean, self.mean_diff, self.var, self._scratch_for(obs.shape[0]))
+        if comm is not None and comm.world > 1:
+            mine, every, scratch = self._shared_for(obs.shape[0], comm.world)
+            nv.welford_totals(obs, self.mean, mine, scratch)
+            comm.allgather(mine, every)
+            nv.welford_shared(obs, out, self.n, self.mean, self.mean_diff, self.var, every, comm.rank,
+                              self._scratch_for(obs.shape[0]))
+        else:
+            nv.welford(obs, out, self.n, self.mean, self.mean_diff, self.var, self._scratch_for(obs.shape[0]))
         return out
 
     def observes(self, obs):

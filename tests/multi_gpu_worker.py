@@ -79,7 +79,29 @@ def main():
         err = float((ref.flat - flat).abs().max()) / float(flat.abs().max())
         assert err < 1e-5, err
         print("MULTI_GPU_OK world=%d mode=%s rel_err_vs_single_gpu=%.2e" % (world, comm.mode, err), flush=True)
+    # ---- observation statistics shared by the workers in rank order (main.py:54, model.py:61-80) ----
+    stats = Shared_obs_stats(O, device=dev)
+    norm = stats.observes_batch(buf.raw_obs, comm=comm)
+    torch.cuda.synchronize()
+    finals = [torch.empty(4, O, device=dev) for _ in range(world)]
+    dist.all_gather(finals, torch.stack([stats.n, stats.mean, stats.mean_diff, stats.var]))
+    assert all(torch.equal(finals[0], f) for f in finals), "statistics replicas diverged"
+    last = [torch.empty_like(norm) for _ in range(world)]
+    dist.all_gather(last, norm)
+    if rank == 0:
+        seq = Shared_obs_stats(O, device=dev)                      # one statistics object fed rank after rank
+        for r in range(world):
+            _, b = build(r)
+            want = seq.observes_batch(b.raw_obs)
+            err = float((want - last[r]).abs().max()) / 5.0
+            assert err < 1e-5, (r, err)
+        for got, want in zip(finals[0], (seq.n, seq.mean, seq.mean_diff, seq.var)):
+            assert float((got - want).abs().max()) <= 1e-5 * float(want.abs().max()), "final statistics"
+        print("SHARED_STATS_OK world=%d" % world, flush=True)
     dist.barrier()
+    if comm.mode == "p2p":
+        import b200_native as nv2
+        nv2.comm_check(comm.handle)                                # no poll timed out
     comm.close()
     dist.destroy_process_group()
 

@@ -91,7 +91,7 @@ def test_two_gpus_match_single_process(mode):
                           os.path.join(ROOT, "tests", "multi_gpu_worker.py")], env=env, capture_output=True, text=True,
                          timeout=300)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
-    assert "MULTI_GPU_OK" in out.stdout
+    assert "MULTI_GPU_OK" in out.stdout and "SHARED_STATS_OK" in out.stdout
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
@@ -102,3 +102,91 @@ def test_two_gpus_main_launcher():
                           os.path.join(ROOT, "tests", "multi_gpu_main_worker.py")], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "MAIN_LAUNCHER_OK" in out.stdout
+
+
+# ---------------------------------------------------------------- statistics shared by the workers (model.py:61-80, main.py:54)
+def _shared_stats_loopback(nv, raws, state0=None):
+    """W workers' rollouts through dppo_welford_totals -> all-gather (loopback: W virtual ranks on this GPU) ->
+    dppo_welford_shared, every rank on its own replica of the statistics.  Returns (normalised rollouts, states)."""
+    W, O = len(raws), raws[0].shape[1]
+    comms = nv.comm_create_loopback(W, 8)
+    try:
+        X = [torch.as_tensor(r, dtype=torch.float32).to(DEV).contiguous() for r in raws]
+        st = [[(torch.zeros(O, device=DEV) if state0 is None else state0[i].to(DEV).clone()) for i in range(4)] for _ in range(W)]
+        mine = [torch.zeros(1 + 2 * O, dtype=torch.float64, device=DEV) for _ in range(W)]
+        every = [torch.zeros(W, 1 + 2 * O, dtype=torch.float64, device=DEV) for _ in range(W)]
+        for r in range(W):
+            T = X[r].shape[0]
+            nv.welford_totals(X[r], st[r][1], mine[r], torch.empty(max(nv.welford_totals_scratch_bytes(T, O), 16),
+                                                                    dtype=torch.uint8, device=DEV))
+        nv.comm_allgather_loopback(comms, mine, every)
+        torch.cuda.synchronize()
+        for r in range(1, W):
+            assert torch.equal(every[r], every[0])
+        outs = []
+        for r in range(W):
+            T = X[r].shape[0]
+            out = torch.empty_like(X[r])
+            nv.welford_shared(X[r], out, st[r][0], st[r][1], st[r][2], st[r][3], every[r], r,
+                              torch.empty(max(nv.welford_scratch_bytes(T, O), 16), dtype=torch.uint8, device=DEV))
+            outs.append(out)
+        torch.cuda.synchronize()
+        return [o.cpu() for o in outs], st
+    finally:
+        for c in comms:
+            nv.comm_destroy(c)
+
+
+def test_shared_stats_two_workers_match_the_reference_run(golden_dir):
+    """dppo_w2_o17a6 was recorded from the reference with ONE Shared_obs_stats updated by worker 0's rollout and
+    then worker 1's: worker 1's states continue worker 0's statistics.  Rank order here gives the same."""
+    import numpy as np
+    import b200_native as nv
+    g = np.load(os.path.join(golden_dir, "dppo_w2_o17a6.npz"))
+    outs, st = _shared_stats_loopback(nv, [g["w0_raw_obs"], g["w1_raw_obs"]])
+    for w in range(2):
+        Tn = g["w%d_states" % w].shape[0]
+        assert_close_scaled(outs[w][-Tn:], g["w%d_states" % w], 1e-5, "states of worker %d" % w)
+    for i, k in enumerate(("n", "mean", "mean_diff", "var")):
+        assert torch.equal(st[0][i], st[1][i]), k                                  # replicas end identical
+        assert_close_scaled(st[1][i].cpu(), g["w1_stats_" + k], 1e-5, "final " + k)
+    assert torch.equal(st[0][0].cpu(), torch.from_numpy(g["w1_stats_n"]))
+
+
+@pytest.mark.parametrize("W,T,O", [(4, 1500, 17), (3, 700, 40), (8, 300, 376)])
+def test_shared_stats_rank_order_vs_oracle(W, T, O):
+    """The sequential oracle (model.py:68-80 row by row) over the W rollouts concatenated in rank order, after an
+    earlier rollout has left a non-trivial state."""
+    import b200_native as nv
+    g = torch.Generator().manual_seed(W * 1000 + O)
+    loc = torch.rand(O, generator=g) * 4 - 2
+    scale = torch.rand(O, generator=g) * 3 + 0.05
+    first = loc + scale * torch.randn(500, O, generator=g)
+    raws = [loc + scale * torch.randn(T + 17 * r, O, generator=g) for r in range(W)]     # ragged rollout lengths
+    ref = orc.welford_new(O)
+    orc.welford_observe_normalize(ref, first)
+    state0 = [ref[k].clone() for k in ("n", "mean", "mean_diff", "var")]
+    want = [orc.welford_observe_normalize(ref, r) for r in raws]
+    outs, st = _shared_stats_loopback(nv, raws, state0)
+    for r in range(W):
+        assert_close_scaled(outs[r], want[r], 1e-5, "rank %d" % r)
+    for i, k in enumerate(("n", "mean", "mean_diff", "var")):
+        for r in range(1, W):
+            assert torch.equal(st[r][i], st[0][i])
+        assert_close_scaled(st[0][i].cpu(), ref[k], 1e-5, k)
+
+
+def test_shared_stats_world_one_equals_plain_welford():
+    import b200_native as nv
+    g = torch.Generator().manual_seed(2)
+    raw = 0.3 + 1.7 * torch.randn(5000, 17, generator=g)
+    outs, st = _shared_stats_loopback(nv, [raw])
+    X = raw.to(DEV)
+    out = torch.empty_like(X)
+    s2 = [torch.zeros(17, device=DEV) for _ in range(4)]
+    nv.welford(X, out, s2[0], s2[1], s2[2], s2[3], torch.empty(nv.welford_scratch_bytes(5000, 17), dtype=torch.uint8, device=DEV))
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0], out.cpu())
+    assert torch.equal(st[0][0], s2[0])
+    for i in range(1, 4):
+        assert_close_scaled(st[0][i].cpu(), s2[i].cpu(), 1e-6, "state %d" % i)
