@@ -42,6 +42,9 @@ __device__ long long g_k2_clock[64];
 #define K2_ACC(i) do { } while (0)
 #define K2_ACC_FLUSH do { } while (0)
 #endif
+#ifndef DPPO_K2_EARLY_RELEASE
+#define DPPO_K2_EARLY_RELEASE 0
+#endif
 #ifdef DPPO_K2_TRACE
 __device__ long long g_k2_trace[4 * 64 * 8];
 #define K2_TR(role, gp, ev) do { if (trace_on && lane == 0) g_k2_trace[(((role) * 64 + (gp)) << 3) + (ev)] = clock64() - trace_t0; } while (0)
@@ -540,6 +543,11 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32
                    "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
                    "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31]) : "memory");
 }
+// compiler barrier that needs 16 registers to hold their final values (used by the DPPO_K2_EARLY_RELEASE experiment)
+__device__ __forceinline__ void ts_pin16(const uint32_t* v) {
+    asm volatile("" ::"r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+                 "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+}
 // hi = rn_tf32(x); lo = x - hi exactly (<= 13 significant bits): the tensor core truncates it to tf32 (error <= 2^-22 |x|)
 __device__ __forceinline__ void ts_split(float x, uint32_t& hi, uint32_t& lo) {
     const float h = tc_rn_tf32(x);
@@ -657,6 +665,18 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                                 ts_split(x.z, hi[4 * c + 2], lo[4 * c + 2]); ts_split(x.w, hi[4 * c + 3], lo[4 * c + 3]);
                             }
                         }
+#if DPPO_K2_EARLY_RELEASE
+                        // EXPERIMENT (never the shipped build; see "raw tile release" below): release the slot as soon as
+                        // its last tile has been split.  =1: as ptxas schedules it (the arrive overtakes the split);
+                        // =2: with the split results pinned in registers first.
+                        if (i == nb2 - 1) {
+#if DPPO_K2_EARLY_RELEASE == 2
+                            ts_pin16(hi); ts_pin16(hi + 16); ts_pin16(lo); ts_pin16(lo + 16);
+#endif
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&raw_free[s]);
+                        }
+#endif
                         if (i == 0) {                       // the slot's previous MMAs have read these A columns
                             if (warp == 0) K2_TR(0, gp, 2);
                             if (gp >= 2) mbar_wait(&mma_done[s], par(TS_PH_MD + s, u - 1));
@@ -668,10 +688,21 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                     }
                 }
                 if (warp == 0) K2_TR(0, gp, 4);
+                // Raw tile release.  The producer warp refills the slot (TMA, async proxy) as soon as all four transform
+                // warps have arrived on raw_free, so an arrive may only be issued once the warp's LDS of the slot have
+                // DELIVERED their data.  Program order alone does not give that: the arrive does not depend on the loaded
+                // registers, and ptxas is free to sink the split arithmetic (the only consumer of the LDS results) below
+                // it - in the build that released right after the split, the SASS has the eight LDS.128, the warp sync and
+                // SYNCS.ARRIVE back to back and the first use of the loaded registers 30 instructions later, i.e. the
+                // slot was handed back with its loads still in flight, and the engine became non-repeatable
+                // (profiles/r02_k2_release_race.md).  Here the arrive follows both tiles' tcgen05.st in program order;
+                // the st instructions read the split results, the split results need every LDS destination register,
+                // so all loads of the slot have completed when the arrive issues: the ordering is a data dependence,
+                // not a time window.
+#if !DPPO_K2_EARLY_RELEASE
                 __syncwarp();
-                // the release stays HERE, after both tiles' tcgen05.st have been issued: arriving right after a tile's
-                // split (when its LDS results are already consumed) made the engine non-repeatable - see DESIGN.md, K2
                 if (lane == 0) mbar_arrive(&raw_free[s]);
+#endif
                 asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 __syncwarp();

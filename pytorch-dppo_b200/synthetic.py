@@ -11,6 +11,7 @@ import torch
 
 import b200_native as nv
 from b200_engine import RolloutBuffer
+from synthetic_data import host_arrays
 
 SHAPES = {                       # env name -> (obs dim, act dim)
     "InvertedPendulum": (4, 1), "HalfCheetah": (17, 6), "HopperBullet": (15, 3), "Humanoid": (376, 17),
@@ -22,15 +23,10 @@ def make_rollout(model, obs_stats, T, seed, flavour, seg_len=1000, pinned_host=T
     up to (and excluding) adv/ret, which K1 produces."""
     O, A = model.dims.O, model.dims.A
     dev = model.flat.device
-    g = torch.Generator().manual_seed(seed)
     host = RolloutBuffer(T, O, A, dev, pinned_host=pinned_host)
-    loc = torch.rand(O, generator=g) * 2 - 1
-    scale = torch.rand(O, generator=g) * 1.5 + 0.25
-    host.raw_obs.copy_(loc + scale * torch.randn(T, O, generator=g))
-    host.rew.copy_(torch.randn(T, generator=g).clamp_(-1, 1))
-    eps = torch.randn(T, A, generator=g)
-    boot_noise = torch.randn(T, generator=g)
-    coin = torch.rand(T, generator=g)
+    raw_obs, rew, eps, boot_noise, coin = host_arrays(O, A, T, seed)
+    host.raw_obs.copy_(raw_obs)
+    host.rew.copy_(rew)
     d = RolloutBuffer(T, O, A, dev)
     d.raw_obs.copy_(host.raw_obs)
     if obs_stats is not None:

@@ -297,3 +297,90 @@ def test_engine_is_bit_repeatable():
             torch.cuda.synchronize()
             res.append((m.flat.clone(), eng.m.clone()))
         assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1]), "repeat %d differs" % rep
+
+
+def _replay_run(widths, O, A, T, B, E, replays, seed=1):
+    """`replays` consecutive graph replays of the whole step (K4, K1, E x (K2, K3)) on one rollout with fresh
+    minibatch positions every time; returns the final parameters and Adam state."""
+    import b200_native as nv
+    from b200_engine import UpdateEngine
+    from model import Model, Shared_grad_buffers, Shared_obs_stats
+    from synthetic import make_rollout
+    torch.manual_seed(seed)
+    m = Model(O, A, *widths, device=DEV)
+    stats = Shared_obs_stats(O)
+    host, dev = make_rollout(m, stats, T, seed=7, flavour=nv.FLAVOUR_DPPO, seg_len=1000)
+    sgb = Shared_grad_buffers(m)
+    eng = UpdateEngine(m, nv.FLAVOUR_DPPO, B, E, 3e-4)
+    rng = random.Random(3)
+    stats0 = [t.clone() for t in (stats.n, stats.mean, stats.mean_diff, stats.var)]
+    for i in range(replays):
+        for t, s in zip((stats.n, stats.mean, stats.mean_diff, stats.var), stats0):
+            t.copy_(s)
+        eng.draw_indices(T, rng)
+        eng.run_epochs(dev, gshared=sgb.flat, use_graph=True, obs_stats=stats, with_gae=True)
+    torch.cuda.synchronize()
+    assert torch.isfinite(m.flat).all()
+    return m.flat.clone(), eng.m.clone(), eng.v.clone()
+
+
+def test_engine_is_bit_repeatable_at_the_bench_shape():
+    """C4 exactly as bench.py runs it (reference nets, 65536-step rollout, minibatch 4096 -> 28 samples per CTA on
+    147 CTAs, 10 epochs), 24 back-to-back graph replays, twice: bit-identical parameters and Adam moments.  This is
+    the guard on the ordering of the tensor-core pipeline's barriers (csrc/dppo_update.cu, ts_layer)."""
+    a = _replay_run((100, 100, 500, 100), 17, 6, 65536, 4096, 10, 24)
+    b = _replay_run((100, 100, 500, 100), 17, 6, 65536, 4096, 10, 24)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+
+
+@pytest.mark.parametrize("widths,O,A", [((100, 100, 500, 100), 17, 6), ((64, 64, 64, 64), 17, 6),
+                                        ((128, 128, 128, 128), 17, 6), ((96, 96, 160, 96), 11, 3)])
+def test_engine_replay_stress_is_bit_repeatable(widths, O, A):
+    """120 graph replays x 4 epochs per shape (every tcgen05 layer variant: 3..16 k-blocks, one and several tiles),
+    two runs, compared bit for bit."""
+    a = _replay_run(widths, O, A, 8192, 1024, 4, 120)
+    b = _replay_run(widths, O, A, 8192, 1024, 4, 120)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+
+
+def test_engine_vs_oracle_c4_shape_full_cycle():
+    """The benchmark's own configuration end to end (K4 -> K1 -> 10 x (K2 -> K3) on a 65536-step rollout, minibatch
+    4096) against the oracle on the same data and the same random.sample stream."""
+    import b200_native as nv
+    from b200_engine import UpdateEngine
+    from model import Model, Shared_grad_buffers, Shared_obs_stats
+    from synthetic import make_rollout
+    torch.manual_seed(1)
+    O, A, T, B, E = 17, 6, 65536, 4096, 10
+    m = Model(O, A, device=DEV)
+    stats = Shared_obs_stats(O)
+    host, dev = make_rollout(m, stats, T, seed=2, flavour=nv.FLAVOUR_DPPO)
+    p = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    sgb = Shared_grad_buffers(m)
+    eng = UpdateEngine(m, nv.FLAVOUR_DPPO, B, E, 3e-4)
+    eng.draw_indices(T, random.Random(11))
+    loss = eng.run_epochs(dev, gshared=sgb.flat, use_graph=True, obs_stats=stats, with_gae=True).cpu()
+    torch.cuda.synchronize()
+    rng = random.Random(11)
+    idx = [orc.sample_indices(T, B, rng) for _ in range(E)]
+    assert np.array_equal(np.asarray(idx, np.int32), eng.idx_host.numpy())
+    mo, vo = orc.zeros_like_params(p), orc.zeros_like_params(p)
+    gsh = orc.zeros_like_params(p, 1.0)                               # model.py:51
+    worker = dict(states=dev.obs.cpu(), actions=host.act.clone(), returns=dev.ret.cpu().reshape(-1, 1),
+                  advantages=dev.adv.cpu().reshape(-1, 1))
+    terms = []
+    orc.dppo_update_cycle(p, mo, vo, 0, [worker], [idx], gsh, lr=3e-4, num_epoch=E,
+                          record=lambda k, w, t, g: terms.append(t))
+    for k in range(E):
+        assert float(loss[k, 0]) == pytest.approx(terms[k]["loss_clip"], rel=1e-5, abs=1e-7)
+        assert float(loss[k, 1]) == pytest.approx(terms[k]["loss_value"], rel=1e-5)
+    got = unpadded(m.flat, m.offsets, m.sizes)
+    assert_close_scaled(got, orc.flatten(p), 1e-5, "theta after 10 epochs (C4)")
+    o = 0
+    for k in orc.PARAM_ORDER:                                         # and tensor by tensor
+        n = p[k].numel()
+        assert_close_scaled(got[o:o + n], p[k].reshape(-1), 1e-5, "theta[%s] (C4)" % k)
+        o += n
+    assert_close_scaled(unpadded(eng.m, m.offsets, m.sizes), orc.flatten(mo), 1e-5, "Adam m (C4)")
