@@ -11,11 +11,15 @@
 //
 // One pass over HBM (20 B/step + 1 B flag): every thread owns 8 consecutive
 // steps, composes them, a warp-shuffle suffix scan and a block scan give each
-// thread its carry-in, and tiles are chained right-to-left with a decoupled
-// look-back (tile order is handed out by an atomic ticket, so a tile's
-// right-hand neighbours always started earlier).  Because |a| < 1 the
-// composed coefficient of a whole tile underflows to 0, so the look-back
-// normally ends after one hop.  With its carry known, each thread REPLAYS its
+// thread its carry-in.  Tiles are independent when gamma*lam decays fast enough
+// (see HALO below); otherwise they are chained right-to-left: tile order is handed
+// out by an atomic ticket (a tile's right-hand neighbours always started earlier)
+// and the value entering a tile is obtained from a FIXED two-level hierarchy of
+// composed maps - blocks of 16 tiles, super-blocks of 16 blocks - applied in a fixed
+// order, so the result does not depend on timing (fp32 composition is not
+// associative; the usual decoupled look-back, which composes whatever mix of tile
+// maps and resolved values it finds, is not bit-repeatable when the decay is slow).
+// With its carry known, each thread REPLAYS its
 // 8 steps with the reference's exact fp32 operation order (no FMA), so the
 // only rounding difference to the sequential loop sits in the carries.
 #include <math.h>
@@ -28,6 +32,11 @@ constexpr int GAE_K = 8;                          // steps per thread
 constexpr int GAE_TILE = GAE_THREADS * GAE_K;     // 4096 steps per CTA
 
 struct Aff { float a, b; };                       // x -> b + a*x
+struct GaeChain {                                 // chained mode: carved from the caller's scratch
+    int *ticket, *flagA, *flagB, *flagG;
+    float2 *mapA, *mapB;
+    float* valG;
+};
 // (f o g)(x) = f.b + f.a*(g.b + g.a*x)
 __device__ __forceinline__ Aff compose(Aff f, Aff g) {
     Aff r;
@@ -36,9 +45,12 @@ __device__ __forceinline__ Aff compose(Aff f, Aff g) {
     return r;
 }
 
-// scratch layout: int ticket; int status[ntiles]; float2 ab[ntiles]
-// status: 0 = nothing, 1 = ab is the tile-local composition, 2 = ab.b is the
-// resolved A at the tile's first step (ab.a = 0)
+// Chained mode, scratch layout (GaeChain): tiles are numbered u = 0, 1, ... from the RIGHT end of the buffer.
+//   mapA[u]  the tile's own map f_u               flagA[u]   published by every tile, depends on nothing
+//   mapB[q]  f_{16q+15} o ... o f_{16q}           flagB[q]   published by the block's last tile, needs only mapA
+//   valG[a]  the advantage entering tile 256a     flagG[a]   published by the last tile of super-block a-1: the
+//                                                            only serial chain, one link per 256 tiles
+// The value entering tile u = 256a + 16b + c is  (f_{u-1} o ... o f_{u-c}) ( mapB[16a+b-1] ( ... mapB[16a] ( valG[a] ) ) ).
 // HALO > 0: the tile's window is GAE_TILE steps of which the last HALO are a read-only look-ahead:
 // |gamma*lam|^HALO is below 2^-40, so the advantage entering the window from the right cannot change
 // any fp32 result in the first GAE_TILE-HALO steps and the tiles become independent (no ticket, no
@@ -48,9 +60,9 @@ template <bool VEC, bool HALO>
 __global__ void __launch_bounds__(GAE_THREADS)
 gae_scan_kernel(const float* __restrict__ rew, const float* __restrict__ val, const float* __restrict__ boot,
                 const uint8_t* __restrict__ seg_end, float* __restrict__ adv, float* __restrict__ ret,
-                int64_t T, float g, float gl, int ntiles, int halo, int* __restrict__ ticket, int* __restrict__ status,
-                float2* __restrict__ ab) {
+                int64_t T, float g, float gl, int ntiles, int halo, const GaeChain ch) {
     __shared__ int s_tile;
+    __shared__ float2 s_look[32];
     __shared__ Aff s_warp[GAE_THREADS / 32];
     __shared__ float s_carry;
 
@@ -61,7 +73,7 @@ gae_scan_kernel(const float* __restrict__ rew, const float* __restrict__ val, co
         tile_base = (int64_t)tile * (GAE_TILE - halo);
         out_end = tile_base + (GAE_TILE - halo);          // steps >= out_end belong to the next tile
     } else {
-        if (threadIdx.x == 0) s_tile = ntiles - 1 - atomicAdd(ticket, 1);   // right-most tile first
+        if (threadIdx.x == 0) s_tile = ntiles - 1 - atomicAdd(ch.ticket, 1);   // right-most tile first
         __syncthreads();
         tile = s_tile;
         tile_base = (int64_t)tile * GAE_TILE;
@@ -134,38 +146,55 @@ gae_scan_kernel(const float* __restrict__ rew, const float* __restrict__ val, co
     for (int w = 0; w < GAE_THREADS / 32; ++w)
         if (w > warp) right = compose(right, s_warp[w]);
 
-    // tile aggregate and look-back (thread 0)
+    // tile map and the value entering the tile from the right (warp 0; see GaeChain)
     if (HALO) {
         if (threadIdx.x == 0) s_carry = 0.f;              // what enters from beyond the halo has decayed away
-    } else if (threadIdx.x == 0) {
-        Aff agg = compose(loc, right);
-        float carry = 0.f;
-        if (tile == ntiles - 1) {
-            __stcg(&ab[tile], make_float2(0.f, agg.b));
+    } else if (warp == 0) {
+        const int u = ntiles - 1 - tile;
+        const int sa = u >> 8, sb = (u >> 4) & 15, sc = u & 15;
+        const Aff agg = compose(loc, right);              // (lane 0 holds the whole tile's map)
+        if (lane == 0) {
+            __stcg(&ch.mapA[u], make_float2(agg.a, agg.b));
             __threadfence();
-            st_release_gpu(&status[tile], 2);
-        } else {
-            __stcg(&ab[tile], make_float2(agg.a, agg.b));
-            __threadfence();
-            st_release_gpu(&status[tile], 1);
-            Aff acc; acc.a = 1.f; acc.b = 0.f;
-            int t = tile + 1;
-            while (true) {
-                int st;
-                while ((st = ld_acquire_gpu(&status[t])) == 0) { }
-                const float2 d = __ldcg(&ab[t]);         // one 64-bit L2 read: (a,b) never tears
-                Aff o; o.a = (st == 2) ? 0.f : d.x; o.b = d.y;
-                acc = compose(acc, o);
-                if (acc.a == 0.f) break;
-                ++t;                                  // t <= ntiles-1 always ends with status 2
-            }
-            carry = acc.b;
-            const float first = (agg.a == 0.f) ? agg.b : fmaf(agg.a, carry, agg.b);
-            __stcg(&ab[tile], make_float2(0.f, first));
-            __threadfence();
-            st_release_gpu(&status[tile], 2);
+            st_release_gpu(&ch.flagA[u], 1);
         }
-        s_carry = carry;
+        // round 0: the maps of the tiles before this one in its block, fetched side by side, composed in order
+        if (lane < sc) {
+            while (ld_acquire_gpu(&ch.flagA[u - sc + lane]) == 0) { }
+            s_look[lane] = __ldcg(&ch.mapA[u - sc + lane]);
+        }
+        __syncwarp();
+        Aff M; M.a = 1.f; M.b = 0.f;                      // f_{u-1} o ... o f_{u-sc}
+        if (lane == 0) {
+            for (int j = 0; j < sc; ++j) { Aff f; f.a = s_look[j].x; f.b = s_look[j].y; M = compose(f, M); }
+            if (sc == 15) {                               // last tile of its block: publish the block's map
+                const Aff Bm = compose(agg, M);
+                __stcg(&ch.mapB[u >> 4], make_float2(Bm.a, Bm.b));
+                __threadfence();
+                st_release_gpu(&ch.flagB[u >> 4], 1);
+            }
+        }
+        __syncwarp();
+        // round 1: the maps of the blocks before this one in its super-block and the value entering the super-block
+        if (lane < sb) {
+            while (ld_acquire_gpu(&ch.flagB[(sa << 4) + lane]) == 0) { }
+            s_look[lane] = __ldcg(&ch.mapB[(sa << 4) + lane]);
+        } else if (lane == 16 && sa > 0) {
+            while (ld_acquire_gpu(&ch.flagG[sa]) == 0) { }
+            s_look[16] = make_float2(__ldcg(&ch.valG[sa]), 0.f);
+        }
+        __syncwarp();
+        if (lane == 0) {
+            float x = sa > 0 ? s_look[16].x : 0.f;
+            for (int j = 0; j < sb; ++j) x = (s_look[j].x == 0.f) ? s_look[j].y : fmaf(s_look[j].x, x, s_look[j].y);
+            s_carry = (M.a == 0.f) ? M.b : fmaf(M.a, x, M.b);
+            if (sc == 15 && sb == 15) {                   // last tile of its super-block: the value entering the next one
+                const Aff Bm = compose(agg, M);
+                __stcg(&ch.valG[sa + 1], (Bm.a == 0.f) ? Bm.b : fmaf(Bm.a, x, Bm.b));
+                __threadfence();
+                st_release_gpu(&ch.flagG[sa + 1], 1);
+            }
+        }
     }
     __syncthreads();
     // A at the first step right of this thread
@@ -205,10 +234,14 @@ static int gae_halo(float gl) {
     return ((int)h + 7) & ~7;
 }
 
+static size_t gae_flag_bytes(int64_t ntiles) {
+    const int64_t nb1 = ceil_div64(ntiles, 16), nb2 = ceil_div64(nb1, 16);
+    return align_up(sizeof(int) * (size_t)(1 + ntiles + nb1 + nb2 + 1), 16);
+}
 extern "C" size_t dppo_gae_scratch_bytes(int64_t T) {
     if (T <= 0) return 16;
-    const int64_t ntiles = ceil_div64(T, GAE_TILE);
-    return align_up(sizeof(int) * (size_t)(1 + ntiles), 16) + sizeof(float2) * (size_t)ntiles;
+    const int64_t ntiles = ceil_div64(T, GAE_TILE), nb1 = ceil_div64(ntiles, 16), nb2 = ceil_div64(nb1, 16);
+    return gae_flag_bytes(ntiles) + sizeof(float2) * (size_t)(ntiles + nb1) + align_up(sizeof(float) * (size_t)(nb2 + 1), 16);
 }
 
 extern "C" int dppo_gae_scan(const float* rewards, const float* values, const float* boot, const uint8_t* seg_end,
@@ -227,30 +260,37 @@ extern "C" int dppo_gae_scan(const float* rewards, const float* values, const fl
     const bool vec = aligned16(rewards) && aligned16(values) && aligned16(boot) && aligned16(adv) && aligned16(ret) &&
                      ((reinterpret_cast<uintptr_t>(seg_end) & 7u) == 0);
     const int halo = gae_halo(gl);
+    GaeChain ch = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     if (halo > 0) {
         const int step = GAE_TILE - halo;
         const int ntiles = (int)ceil_div64(T, step);
         if (vec)
             gae_scan_kernel<true, true><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T,
-                                                                             g, gl, ntiles, halo, nullptr, nullptr, nullptr);
+                                                                             g, gl, ntiles, halo, ch);
         else
             gae_scan_kernel<false, true><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T,
-                                                                              g, gl, ntiles, halo, nullptr, nullptr, nullptr);
+                                                                              g, gl, ntiles, halo, ch);
         DPPO_LAUNCH_CHECK();
         return 0;
     }
     const int ntiles = (int)ceil_div64(T, GAE_TILE);
-    const size_t flag_bytes = align_up(sizeof(int) * (size_t)(1 + ntiles), 16);
-    int* ticket = (int*)scratch;
-    int* status = ticket + 1;
-    float2* ab = (float2*)((char*)scratch + flag_bytes);
+    const int nb1 = ceil_div(ntiles, 16), nb2 = ceil_div(nb1, 16);
+    const size_t flag_bytes = gae_flag_bytes(ntiles);
+    ch.ticket = (int*)scratch;
+    ch.flagA = ch.ticket + 1;
+    ch.flagB = ch.flagA + ntiles;
+    ch.flagG = ch.flagB + nb1;
+    ch.mapA = (float2*)((char*)scratch + flag_bytes);
+    ch.mapB = ch.mapA + ntiles;
+    ch.valG = (float*)(ch.mapB + nb1);
+    (void)nb2;
     DPPO_CUDA_TRY(cudaMemsetAsync(scratch, 0, flag_bytes, stream));
     if (vec)
         gae_scan_kernel<true, false><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T, g,
-                                                                          gl, ntiles, 0, ticket, status, ab);
+                                                                          gl, ntiles, 0, ch);
     else
         gae_scan_kernel<false, false><<<ntiles, GAE_THREADS, 0, stream>>>(rewards, values, boot, seg_end, adv, ret, T, g,
-                                                                           gl, ntiles, 0, ticket, status, ab);
+                                                                           gl, ntiles, 0, ch);
     DPPO_LAUNCH_CHECK();
     return 0;
 }
@@ -265,7 +305,7 @@ extern "C" int dppo_gae_scan(const float* rewards, const float* values, const fl
 // because cudaMalloc synchronises the whole device and may fail late; code that
 // runs after the application has frozen its memory pool.  For them the chain
 // lives in the array below, which is part of the library image: every GPU that
-// loads libdppo_b200.so keeps these ~12 KB resident until the process exits.
+// loads libdppo_b200.so keeps these ~13 KB resident until the process exits.
 //
 // Limits and rules
 //   * T <= DPPO_GAE_NOALLOC_MAX_T (4 194 304 steps); longer buffers are refused
@@ -285,8 +325,13 @@ extern "C" int dppo_gae_scan(const float* rewards, const float* values, const fl
 //     them) race on it - serialise them.
 // ---------------------------------------------------------------------------
 #define DPPO_GAE_NOALLOC_MAX_TILES ((DPPO_GAE_NOALLOC_MAX_T + GAE_TILE - 1) / GAE_TILE)
-#define DPPO_GAE_NOALLOC_FLAG_BYTES ((sizeof(int) * (1 + DPPO_GAE_NOALLOC_MAX_TILES) + 15) / 16 * 16)
-#define DPPO_GAE_NOALLOC_BYTES (DPPO_GAE_NOALLOC_FLAG_BYTES + sizeof(float2) * DPPO_GAE_NOALLOC_MAX_TILES)
+#define DPPO_GAE_NOALLOC_NB1 ((DPPO_GAE_NOALLOC_MAX_TILES + 15) / 16)
+#define DPPO_GAE_NOALLOC_NB2 ((DPPO_GAE_NOALLOC_NB1 + 15) / 16)
+#define DPPO_GAE_NOALLOC_FLAG_BYTES \
+    ((sizeof(int) * (1 + DPPO_GAE_NOALLOC_MAX_TILES + DPPO_GAE_NOALLOC_NB1 + DPPO_GAE_NOALLOC_NB2 + 1) + 15) / 16 * 16)
+#define DPPO_GAE_NOALLOC_BYTES                                                                                  \
+    (DPPO_GAE_NOALLOC_FLAG_BYTES + sizeof(float2) * (DPPO_GAE_NOALLOC_MAX_TILES + DPPO_GAE_NOALLOC_NB1) + \
+     (sizeof(float) * (DPPO_GAE_NOALLOC_NB2 + 1) + 15) / 16 * 16)
 
 static __device__ __align__(256) unsigned char g_gae_noalloc_scratch[DPPO_GAE_NOALLOC_BYTES];
 

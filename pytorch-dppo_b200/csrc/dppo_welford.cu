@@ -28,7 +28,8 @@
 //   + B[a][0..b-1]    the sums of the blocks before its block       (each published by the block's last tile)
 //   + A[..][0..c-1]   the sums of the tiles before it in its block  (each published by its tile)
 // The only serial chain is P: one link per 256 tiles (~34 links for a 570 MB rollout), far faster than
-// the tiles stream.  Every wait is on a flag with acquire/release semantics; at most 31 payloads are read.
+// the tiles stream; B needs only the A of its own block.  Every wait is on a flag with acquire/release semantics; at
+// most 31 payloads are read.
 #include "common.cuh"
 
 namespace {
@@ -64,7 +65,7 @@ __device__ __forceinline__ void wf_wait_flag(const int* f) {
 }
 
 // dynamic smem: float tile[R*CB] | float p[CB], M0[CB] | double g1[G*CB], g2[G*CB] | double base[2*CB], agg[2*CB] |
-//               union { double look[31][2*CB];  double inv[R] + float nf[R] }
+//               union { double look[16][2*CB];  double inv[R] + float nf[R] }
 __global__ void __launch_bounds__(WF_THREADS)
 wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const WfGeom q, float* __restrict__ n,
                 float* __restrict__ mean, float* __restrict__ mean_diff, float* __restrict__ var, const WfScratch w,
@@ -146,32 +147,53 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
     __syncthreads();
     if (threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flagA[tix], 1); }
     // ---- sums of all rows above this tile: P[a] + B[a][0..b) + A[..][0..c), fixed order ----
+    // Two rounds, so that nothing a LATER tile waits for depends on this tile's own waits more than it must:
+    // round 0 fetches the sums of the tiles before this one in its block (they depend on nothing) - the last tile of
+    // a block then publishes the block sum B at once; round 1 fetches B[a][0..b) and P[a].  Only P is a serial chain
+    // (one link per 256 tiles).
     const int a = rt / (WF_L1 * WF_L1), b = (rt / WF_L1) % WF_L1, c1 = rt % WF_L1;
-    const int nP = a > 0 ? 1 : 0, nlook = nP + b + c1;                // payloads to fetch (<= 31)
-    if (threadIdx.x < nlook) {                                        // one thread per flag: the waits overlap
-        const int j = threadIdx.x;
-        const int* f = j < nP ? &w.flagP[cb * (q.nb2 + 1) + a]
-                     : j < nP + b ? &w.flagB[cb * q.nb1 + (rt / WF_L1 - b) + (j - nP)]
-                                  : &w.flagA[cb * q.ntr + (rt - c1) + (j - nP - b)];
-        wf_wait_flag(f);
-    }
-    __syncthreads();
-    for (int e = threadIdx.x; e < nlook * V; e += WF_THREADS) {
-        const int j = e / V, v = e - j * V;
-        const double* src = j < nP ? &w.payP[(size_t)(cb * (q.nb2 + 1) + a) * V]
-                          : j < nP + b ? &w.payB[(size_t)(cb * q.nb1 + (rt / WF_L1 - b) + (j - nP)) * V]
-                                       : &w.payA[(size_t)(cb * q.ntr + (rt - c1) + (j - nP - b)) * V];
-        s_look[j * V + v] = __ldcg(src + v);
-    }
-    __syncthreads();
+    const int nP = a > 0 ? 1 : 0;
     const bool pubB = c1 == WF_L1 - 1;                                // last tile of its block
     const bool pubP = pubB && b == WF_L1 - 1;                         // ... and of its super-block
+    double sA = 0.0, sPB = 0.0;                                       // (threads v < V) tiles before me in my block / P + blocks
+    for (int round = 0; round < 2; ++round) {
+        const int cnt = round == 0 ? c1 : nP + b;                     // payloads of this round (<= 16)
+        if (cnt > 0) {
+            if (threadIdx.x < cnt) {                                  // one thread per flag: the waits overlap
+                const int j = threadIdx.x;
+                const int* f = round == 0 ? &w.flagA[cb * q.ntr + (rt - c1) + j]
+                             : j < nP ? &w.flagP[cb * (q.nb2 + 1) + a]
+                                      : &w.flagB[cb * q.nb1 + (rt / WF_L1 - b) + (j - nP)];
+                wf_wait_flag(f);
+            }
+            __syncthreads();
+            for (int e = threadIdx.x; e < cnt * V; e += WF_THREADS) {
+                const int j = e / V, v = e - j * V;
+                const double* src = round == 0 ? &w.payA[(size_t)(cb * q.ntr + (rt - c1) + j) * V]
+                                  : j < nP ? &w.payP[(size_t)(cb * (q.nb2 + 1) + a) * V]
+                                           : &w.payB[(size_t)(cb * q.nb1 + (rt / WF_L1 - b) + (j - nP)) * V];
+                s_look[j * V + v] = __ldcg(src + v);
+            }
+            __syncthreads();
+            if (threadIdx.x < V) {
+                const int v = threadIdx.x;
+                if (round == 0) {
+                    for (int j = 0; j < c1; ++j) sA += s_look[j * V + v];
+                } else {
+                    sPB = nP ? s_look[v] : 0.0;
+                    for (int j = 0; j < b; ++j) sPB += s_look[(nP + j) * V + v];
+                }
+            }
+        }
+        if (round == 0 && pubB) {                                     // the block's sum: this tile's own + the 15 before it
+            if (threadIdx.x < V) __stcg(&w.payB[(size_t)(cb * q.nb1 + rt / WF_L1) * V + threadIdx.x], sA + s_agg[threadIdx.x]);
+            __syncthreads();
+            if (threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flagB[cb * q.nb1 + rt / WF_L1], 1); }
+        }
+        __syncthreads();                                              // s_look is reused by the next round / the tables
+    }
     if (threadIdx.x < V) {
         const int v = threadIdx.x;
-        double sP = nP ? s_look[v] : 0.0, sB = 0.0, sA = 0.0;
-        for (int j = 0; j < b; ++j) sB += s_look[(nP + j) * V + v];
-        for (int j = 0; j < c1; ++j) sA += s_look[(nP + b + j) * V + v];
-        const double own = s_agg[v];
         // statistics shared by several workers: the rollouts of the workers before this one (rank order) come first
         double prior = 0.0;
         if (totals != nullptr) {
@@ -180,19 +202,11 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
                 for (int r = 0; r < rank; ++r)
                     prior += totals[(size_t)r * (1 + 2 * q.O) + 1 + (v < q.CB ? 0 : q.O) + col0 + c];
         }
-        s_base[v] = prior + ((sP + sB) + sA);
-        if (pubB) {
-            const double blk = sA + own;                              // sums of this block's 16 tiles
-            __stcg(&w.payB[(size_t)(cb * q.nb1 + rt / WF_L1) * V + v], blk);
-            if (pubP) __stcg(&w.payP[(size_t)(cb * (q.nb2 + 1) + a + 1) * V + v], (sP + sB) + blk);
-        }
+        s_base[v] = prior + (sPB + sA);
+        if (pubP) __stcg(&w.payP[(size_t)(cb * (q.nb2 + 1) + a + 1) * V + v], sPB + (sA + s_agg[v]));
     }
     __syncthreads();
-    if (pubB && threadIdx.x == 0) {
-        __threadfence();
-        st_release_gpu(&w.flagB[cb * q.nb1 + rt / WF_L1], 1);
-        if (pubP) st_release_gpu(&w.flagP[cb * (q.nb2 + 1) + a + 1], 1);
-    }
+    if (pubP && threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flagP[cb * (q.nb2 + 1) + a + 1], 1); }
     // ---- per-row 1/n_t (fp64 and fp32), once per row instead of once per element ----
     double n0 = (double)n0f, rows_all = (double)q.T;               // rows before this rollout / rows of all workers
     if (totals != nullptr) {
@@ -334,7 +348,7 @@ WfGeom wf_geom(int64_t T, int O) {
 }
 
 size_t wf_smem_bytes(const WfGeom& q) {
-    const size_t look = sizeof(double) * 31 * 2 * q.CB;
+    const size_t look = sizeof(double) * 16 * 2 * q.CB;
     const size_t tables = (sizeof(double) + sizeof(float)) * (size_t)q.R;
     return sizeof(float) * ((size_t)q.R * q.CB + 2 * WF_CB) + sizeof(double) * (2 * (size_t)q.G * q.CB + 4 * WF_CB) +
            (look > tables ? look : tables) + 16;

@@ -47,8 +47,21 @@ def run(params, num_inputs, num_outputs):
     params.update_treshold = world - 1
     torch.manual_seed(params.seed)
     shared_model = Model(num_inputs, num_outputs)
+    shared_obs_stats = Shared_obs_stats(num_inputs)
+    test_n = torch.zeros(1)
+    evaluator = None
+    if rank == 0 and getattr(params, "with_evaluator", False):
+        # main.py:62-64: the test process.  A thread of rank 0 here; it normalises with its own copy of the statistics
+        # (in the reference its observations enter the shared statistics, unlocked: test.py:45)
+        import threading
+        from test import test
+        evaluator = threading.Thread(target=test, args=(world, params, shared_model, shared_obs_stats.clone(), test_n),
+                                     daemon=True)
+        evaluator.start()
     train(rank, params, TrafficLight(), Counter(), shared_model, Shared_grad_buffers(shared_model),
-          Shared_obs_stats(num_inputs), torch.zeros(1))
+          shared_obs_stats, test_n)
+    if evaluator is not None:
+        evaluator.join(getattr(params, "eval_join_s", 60))
 
 
 if __name__ == '__main__':

@@ -179,6 +179,14 @@ class Shared_obs_stats():
             nv.welford(obs, out, self.n, self.mean, self.mean_diff, self.var, self._scratch_for(obs.shape[0]))
         return out
 
+    def clone(self):
+        """An independent copy of the statistics (the evaluator normalises with its own copy so that the
+        replicas of the training statistics stay identical on every rank)."""
+        c = Shared_obs_stats(self.n.numel(), device=self.n.device)
+        for k in ("n", "mean", "mean_diff", "var"):
+            getattr(c, k).copy_(getattr(self, k))
+        return c
+
     def observes(self, obs):
         x = getattr(obs, "data", obs).reshape(1, -1).to(self.n.device, torch.float32)
         self.observes_batch(x)

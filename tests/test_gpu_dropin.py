@@ -246,3 +246,26 @@ def test_checkpoint_roundtrip(tmp_path):
     eng2.update_from_host(host2, dev2, obs_stats=stats2, rng=rng2)
     assert torch.equal(m2.flat, want[0]) and torch.equal(eng2.m, want[1]) and torch.equal(eng2.v, want[2])
     assert eng2.step == want[3] and torch.equal(stats2.mean, want[4])
+
+
+def test_evaluator_role_runs_on_the_shared_model(capsys):
+    """test.test(rank, params, shared_model, shared_obs_stats, test_n) - the reference's evaluator (test.py:24-65):
+    three episodes on the shared model, the reference's print format, statistics fed per step."""
+    import importlib.util
+    import os
+    from model import Model, Shared_obs_stats
+    spec = importlib.util.spec_from_file_location("dppo_test_role", os.path.join(os.path.dirname(os.path.dirname(
+        os.path.abspath(__file__))), "pytorch-dppo_b200", "test.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    O, A = 5, 2
+    torch.manual_seed(1)
+    model = Model(O, A, device=DEV)
+    stats = Shared_obs_stats(O)
+    p = _params(O, A)
+    p.max_eval_episodes, p.eval_sleep_s = 3, 0.0
+    res = mod.test(1, p, model, stats, torch.zeros(1))
+    out = capsys.readouterr().out
+    assert len(res) == 3 and all(r[1] == 37 for r in res)              # FakeEnv episodes last 37 steps
+    assert out.count("episode reward") == 3 and "episode length 37" in out
+    assert float(stats.n[0]) == 3 * 37                                 # test.py:45: every step observed
