@@ -329,7 +329,7 @@ def main():
     for _ in range(args.warmup):
         reset_stats()
         engine.draw_indices(wl["T"], rng)
-        engine.idx_dev.copy_(engine.idx_host, non_blocking=True)
+        engine._upload_indices()
         step_resident()
     launches_per_step = engine.launches_per_cycle - (1 if flavour == nv.FLAVOUR_DPPO else 0)   # minus the theta_old copy
     barrier()
@@ -341,7 +341,7 @@ def main():
     barrier()
     for _ in range(args.steps):
         engine.draw_indices(wl["T"], rng)
-        engine.idx_dev.copy_(engine.idx_host, non_blocking=True)
+        engine._upload_indices()                                   # (draw_indices waits for the previous upload of the block)
         flush.fill_(1)                                             # evict L2 (126 MB) between steps
         reset_stats()                                              # keep n below 2^24 (fp32 counter, model.py:71)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -132,8 +132,23 @@ class UpdateEngine:
         """E minibatches of B positions, exactly ReplayMemory.sample's index stream
         (``random.sample`` without replacement, independent per epoch; train.py:31-33),
         generated by the C restatement of CPython's algorithm on ``rng``'s own state."""
+        self._wait_idx_upload()
         nv.sample_indices(T, self.B, self.E, rng=rng, out=self.idx_host)
         return self.idx_host
+
+    def _wait_idx_upload(self):
+        """The pinned index block is uploaded asynchronously; it may only be rewritten once that upload has run
+        (a loop of draw_indices / run_epochs without a synchronise in between would otherwise train on a mixture
+        of two index streams, depending on timing)."""
+        ev = getattr(self, "_idx_read", None)
+        if ev is not None:
+            ev.synchronize()
+            self._idx_read = None
+
+    def _upload_indices(self):
+        self.idx_dev.copy_(self.idx_host, non_blocking=True)
+        self._idx_read = torch.cuda.Event()
+        self._idx_read.record(torch.cuda.current_stream())
 
     # ---- E x (K2 -> K3) -----------------------------------------------------------------------
     def _launch_epochs(self, buf, gshared, obs_stats=None, with_gae=False):
@@ -183,7 +198,7 @@ class UpdateEngine:
         ``idx_host`` (see draw_indices).  Returns the (E,4) device tensor of per-epoch
         loss terms (clip, value, entropy, -)."""
         if not indices_staged:
-            self.idx_dev.copy_(self.idx_host, non_blocking=True)
+            self._upload_indices()
         if not scalars_staged:
             self._stage_scalars()
         if not use_graph or (self.comm is not None and self.comm.mode == "nccl"):
@@ -244,7 +259,7 @@ class UpdateEngine:
         else:
             self.draw_indices(dev.T, rng)
         self._prefetched = None
-        self.idx_dev.copy_(self.idx_host, non_blocking=True)
+        self._upload_indices()
         h2d += self.idx_host.numel() * 4 + self.scalars_host.numel() * 4
         self.run_epochs(dev, gshared=gshared, use_graph=use_graph, indices_staged=True)
         self.loss_host.copy_(self.loss_out, non_blocking=True)

@@ -13,7 +13,7 @@
 // sums are carried in fp64, mean_t / M2_t are rounded to fp32 and the
 // normalisation is the reference's fp32 arithmetic.
 //
-// One launch.  A CTA owns a tile of R rows x CB columns (32 KB of fp32; CB = O for O <= 32, else column
+// One launch.  A CTA owns a tile of R rows x CB columns (~33 KB of fp32; CB = O for O <= 32, else column
 // blocks of 32), reads it from HBM once into shared memory, forms its column sums, obtains the sums of all
 // rows above it from the tiles before it, normalises the tile in shared memory and streams it out: 8*O
 // bytes per row of HBM traffic.  Tiles are handed out by an atomic ticket, so every tile above a running
@@ -35,10 +35,9 @@
 namespace {
 
 constexpr int WF_THREADS = 256;
-constexpr int WF_TILE_ELEMS = 8192;                 // 32 KB of fp32 per CTA
 constexpr int WF_CB = 32;                           // widest column block
 constexpr int WF_L1 = 16;                           // tiles per block, blocks per super-block
-constexpr int WF_MAX_ROWS = 2048;                   // bounds the per-row reciprocal tables
+constexpr int WF_MAX_ROWS = 8448;                   // bounds the per-row reciprocal table (256 groups x 33 rows, O = 1)
 
 struct WfGeom {
     int O, CB, ncb;                                 // columns, columns per block (last block may be narrower), blocks
@@ -54,18 +53,12 @@ struct WfScratch {                                  // carved from the caller's 
     double *payA, *payB, *payP;                     // same shapes x [2*CB]
 };
 
-__host__ __device__ inline int wf_rows_per_tile(int cb) {
-    int R = (WF_TILE_ELEMS / cb) & ~3;              // multiple of 4 rows keeps whole-row tiles 16-byte aligned
-    if (R > WF_MAX_ROWS) R = WF_MAX_ROWS;
-    return R < 4 ? 4 : R;
-}
-
 __device__ __forceinline__ void wf_wait_flag(const int* f) {
     while (ld_acquire_gpu(f) == 0) { }
 }
 
 // dynamic smem: float tile[R*CB] | float p[CB], M0[CB] | double g1[G*CB], g2[G*CB] | double base[2*CB], agg[2*CB] |
-//               union { double look[16][2*CB];  double inv[R] + float nf[R] }
+//               union { double look[16][2*CB];  float nf[R] }
 __global__ void __launch_bounds__(WF_THREADS)
 wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const WfGeom q, float* __restrict__ n,
                 float* __restrict__ mean, float* __restrict__ mean_diff, float* __restrict__ var, const WfScratch w,
@@ -80,8 +73,7 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
     double* s_base = s_g2 + q.G * q.CB;
     double* s_agg = s_base + 2 * WF_CB;
     double* s_look = s_agg + 2 * WF_CB;
-    double* s_inv = s_look;                           // the look-back staging is dead when the tables are built
-    float* s_nf = reinterpret_cast<float*>(s_inv + q.R);
+    float* s_nf = reinterpret_cast<float*>(s_look);   // the look-back staging is dead when the table is built
 
     if (threadIdx.x == 0) s_ticket = atomicAdd(w.ticket, 1);
     __syncthreads();
@@ -207,7 +199,7 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
     }
     __syncthreads();
     if (pubP && threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flagP[cb * (q.nb2 + 1) + a + 1], 1); }
-    // ---- per-row 1/n_t (fp64 and fp32), once per row instead of once per element ----
+    // ---- per-row 1/n_t in fp32, once per row instead of once per element ----
     double n0 = (double)n0f, rows_all = (double)q.T;               // rows before this rollout / rows of all workers
     if (totals != nullptr) {
         rows_all = 0.0;
@@ -217,12 +209,8 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
             rows_all += tr;
         }
     }
-    for (int r = threadIdx.x; r < rows; r += WF_THREADS) {
-        const double nt = n0 + (double)(row0 + r + 1);
-        const double r0 = (double)__frcp_rn((float)nt);              // fp32 reciprocal + one Newton step in fp64
-        s_inv[r] = r0 * (2.0 - nt * r0);
-        s_nf[r] = (float)s_inv[r];
-    }
+    for (int r = threadIdx.x; r < rows; r += WF_THREADS)
+        s_nf[r] = __frcp_rn((float)(n0 + (double)(row0 + r + 1)));   // n_t < 2^24 is exact in fp32
     __syncthreads();
     // ---- the new state, by the tile that holds the last row of this column block ----
     if (rt == q.ntr - 1 && threadIdx.x < cw) {
@@ -243,27 +231,35 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
         mean_diff[col0 + c] = md;
         var[col0 + c] = fmaxf(__fdiv_rn(md, nn), 1e-2f);             // model.py:75
     }
-    // ---- per-row prefix + normalise, in place in shared memory ----
+    // ---- per-row statistics + normalise, in place in shared memory ----
+    // The state at the first row of a group comes from the fp64 prefix sums; from there the group's <= 33 rows follow
+    // the reference's own fp32 recurrence (model.py:71-75: mean += (x-mean)/n; M2 += (x-mean_old)(x-mean)), so no
+    // fp64 arithmetic or conversion is spent per element and no error accumulates beyond a group.
     for (int it = threadIdx.x; it < q.G * cw; it += WF_THREADS) {
         const int g = it / cw, c = it - g * cw;
-        const float p = s_p[c];
-        const double M0 = (double)s_m0[c];
-        double a1 = s_base[c] + s_g1[g * q.CB + c], a2 = s_base[q.CB + c] + s_g2[g * q.CB + c];
         const int r0 = g * q.RPG, r1 = min(r0 + q.RPG, rows);
+        if (r0 >= r1) continue;
+        const double ng = n0 + (double)(row0 + r0);                  // rows before the group
+        float mean_f = s_p[c], m2_f = s_m0[c];
+        if (ng > 0.0) {
+            const double a1 = s_base[c] + s_g1[g * q.CB + c], a2 = s_base[q.CB + c] + s_g2[g * q.CB + c];
+            const double t = a1 / ng;
+            mean_f = (float)((double)s_p[c] + t);
+            m2_f = (float)((double)s_m0[c] + a2 - a1 * t);
+        }
 #pragma unroll 4
         for (int r = r0; r < r1; ++r) {
-            const float x = s[r * ld + c];
-            const double d = (double)__fsub_rn(x, p);
-            a1 += d;
-            a2 = fma(d, d, a2);
-            const double t = a1 * s_inv[r];
-            const float mean_t = (float)((double)p + t);
-            const float md_t = (float)(M0 + a2 - a1 * t);
+            const float x = s[r * ld + c], inv = s_nf[r];
+            const float d = __fsub_rn(x, mean_f);                    // x - mean_old
+            mean_f = fmaf(d, inv, mean_f);                           // model.py:73
+            const float e = __fsub_rn(x, mean_f);                    // x - mean
+            m2_f = fmaf(d, e, m2_f);                                 // model.py:74
             // var = max(M2/n, 1e-2), xhat = (x-mean)/sqrt(var) (model.py:75-80) as multiply-by-reciprocal and
-            // rsqrt: within 2 ulp of the divide/sqrt form, an order of magnitude fewer instructions
-            const float var_t = fmaxf(md_t * s_nf[r], 1e-2f);
-            const float xh = __fsub_rn(x, mean_t) * rsqrtf(var_t);
-            s[r * ld + c] = fminf(fmaxf(xh, -5.f), 5.f);
+            // rsqrt.approx (2 ulp): var >= 1e-2, so no denormal handling is needed
+            const float var_t = fmaxf(m2_f * inv, 1e-2f);
+            float rs;
+            asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(var_t));
+            s[r * ld + c] = fminf(fmaxf(e * rs, -5.f), 5.f);
         }
     }
     __syncthreads();
@@ -336,11 +332,19 @@ WfGeom wf_geom(int64_t T, int O) {
     q.O = O; q.T = T;
     q.CB = O <= WF_CB ? O : WF_CB;
     q.ncb = (O + q.CB - 1) / q.CB;
-    q.R = wf_rows_per_tile(q.CB);
+    // G row groups of RPG rows; RPG = 33 makes consecutive groups start 33*CB = CB (mod 32) banks apart, so a warp
+    // whose 32 (group, column) items span two or more groups reads 32 different banks (RPG = 32 put every group on
+    // the same banks: half of all shared-memory wavefronts were conflicts)
     q.G = WF_THREADS / q.CB;
     if (q.G < 1) q.G = 1;
-    if (q.G > q.R) q.G = q.R;
-    q.RPG = (q.R + q.G - 1) / q.G;
+    q.RPG = 33;
+    while (q.RPG > 1 && (int64_t)q.G * q.RPG > WF_MAX_ROWS) q.RPG -= 2;
+    q.R = (q.G * q.RPG) & ~3;                       // multiple of 4 rows keeps whole-row tiles 16-byte aligned
+    if (q.R < 4) q.R = 4;
+    if ((int64_t)q.R > ((T + 3) & ~(int64_t)3)) {   // short rollouts: one tile, fewer rows per group
+        q.R = (int)((T + 3) & ~(int64_t)3);
+        q.RPG = (q.R + q.G - 1) / q.G;
+    }
     q.ntr = (int)ceil_div64(T, q.R);
     q.nb1 = (q.ntr + WF_L1 - 1) / WF_L1;
     q.nb2 = (q.nb1 + WF_L1 - 1) / WF_L1;
@@ -349,7 +353,7 @@ WfGeom wf_geom(int64_t T, int O) {
 
 size_t wf_smem_bytes(const WfGeom& q) {
     const size_t look = sizeof(double) * 16 * 2 * q.CB;
-    const size_t tables = (sizeof(double) + sizeof(float)) * (size_t)q.R;
+    const size_t tables = sizeof(float) * (size_t)q.R;
     return sizeof(float) * ((size_t)q.R * q.CB + 2 * WF_CB) + sizeof(double) * (2 * (size_t)q.G * q.CB + 4 * WF_CB) +
            (look > tables ? look : tables) + 16;
 }
