@@ -115,7 +115,8 @@ struct UpdArgs {
     int use_ts;
     int first_ts;                                   // ... and on the tensor cores (small_first, room for the sample tiles)
     int small_first;                                // first layers (K = O <= 32) run from prefetched flat weight copies
-    alignas(64) CUtensorMap map_fwd[2][2];          // [theta, theta_old][W2, V2]: box 32 (k) x 128 (n), SWIZZLE_128B
+    int trunk_serial;                               // policy trunk start to end, then the value trunk, in the same activation buffers
+    alignas(64) CUtensorMap map_fwd[2][4];          // [theta, theta_old][W2, V2, W1, V1]: box 32 (k) x 128 (n), SWIZZLE_128B
     alignas(64) CUtensorMap map_dx[2];              // theta's W2, V2 for dX: box 128 (k) x 32 (n), no swizzle
 };
 
@@ -593,7 +594,7 @@ __device__ __forceinline__ void ts_stage_samples(unsigned char* bh, const float*
 //   warp 7     MMA issuer (whole warp, uniform operands, elected lane), one commit per pair
 // Barriers (index from TS_BAR0; parity bit in `ph`):  raw_full[2] +0 (bits 8,9)   raw_free[2] +2 (bits 10,11)
 //                                                      a_full[2]  +4 (bits 12,13)  mma_done[2] +8 (bits 16,17)
-// DX = false: out[m][n] = tanh(sum_k in[m][k] W[n][k] + b[n]); map box 32 (k) x 128 (n), SWIZZLE_128B; one tile.
+// DX = false: out[m][n] = tanh(sum_k in[m][k] W[n][k] + b[n]); map box 32 (k) x 128 (n), SWIZZLE_128B; tiles of 128 n.
 // DX = true : act[m][k] <- (sum_n dOut[m][n] W[n][k]) (1 - act[m][k]^2); map box 128 (k) x 32 (n), no swizzle;
 //             tiles of 128 k, the rings run across tiles, the accumulators are drained between tiles.
 // ---------------------------------------------------------------------------
@@ -606,7 +607,7 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
     const int R = DX ? N : K;                               // reduction length
     const int nrb = (R + TC_KB - 1) / TC_KB;                // k-blocks per tile
     const int npt = (nrb + 1) >> 1;                         // pairs per tile
-    const int ntiles = DX ? (K + 127) >> 7 : 1;
+    const int ntiles = DX ? (K + 127) >> 7 : (N + 127) >> 7;   // tiles of 128 TMEM lanes: k (dX) / output features (forward)
     const int NP = npt * ntiles;                            // pairs in all
     uint64_t* raw_full = bars + TS_BAR0;
     uint64_t* raw_free = raw_full + 2;
@@ -614,8 +615,6 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
     uint64_t* mma_done = raw_full + 8;
     unsigned char* raw = ts;
     unsigned char* bst = ts + 4 * TS_RAW_BYTES;
-    float bb = 0.f;                                         // forward: bias of my epilogue feature, fetched now
-    if (!DX) { const int n = 32 * (warp & 3) + lane; bb = n < N ? __ldg(bias + n) : 0.f; }
     // parity of the u-th use (u = 0, 1, ...) of a barrier whose tracked bit is `bit`
     auto par = [&](int bit, int u) -> unsigned { return ((ph >> bit) ^ (unsigned)u) & 1u; };
     auto tma_pair = [&](int gp) {                           // (whole warp 6) both raw tiles of pair gp into slot gp & 1
@@ -624,7 +623,7 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
         const uint32_t d0 = smem_u32(raw + (2 * s) * TS_RAW_BYTES), bar = smem_u32(&raw_full[s]);
         const int blk = 2 * p;
         if (DX) tma_pair_elect(d0, d0 + TS_RAW_BYTES, map, 128 * mt, TC_KB * blk, 128 * mt, TC_KB * (blk + 1), bar, (1u + two) * TS_RAW_BYTES, two);
-        else tma_pair_elect(d0, d0 + TS_RAW_BYTES, map, TC_KB * blk, 0, TC_KB * (blk + 1), 0, bar, (1u + two) * TS_RAW_BYTES, two);
+        else tma_pair_elect(d0, d0 + TS_RAW_BYTES, map, TC_KB * blk, 128 * mt, TC_KB * (blk + 1), 128 * mt, bar, (1u + two) * TS_RAW_BYTES, two);
     };
     __syncthreads();                                        // previous users of the staging region are done
 #ifdef DPPO_K2_TRACE
@@ -776,6 +775,7 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
         // ---------------- epilogue: lane = feature, this warp's 16 samples; the four small halves first ----------------
         {
             const int q = warp & 3, f = 128 * mt + 32 * q + lane, c0 = 16 * (warp >> 2);
+            const float bb = (!DX && f < N) ? __ldg(bias + f) : 0.f;   // forward: bias of my feature (in flight during the loads)
             float sum[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j) sum[j] = 0.f;
@@ -1010,7 +1010,7 @@ __device__ __forceinline__ unsigned fwd_layer(const float* __restrict__ W, const
                                           const float* in, int ldin, float* out, int ldout, float* stage, int SF,
                                           uint64_t* bars, unsigned ph, uint32_t tmem, const CUtensorMap* wmap) {
     // wide GEMM-shaped layers go to the tensor cores (tcgen05), the rest stays on the FP32 pipe
-    if (wmap != nullptr && N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0)
+    if (wmap != nullptr && N >= 32 && K >= 64 && (K & 3) == 0)          // = ts_eligible() on the host
         return ts_layer<false>(wmap, bias, N, K, in, ldin, out, ldout, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
     // 4*CN columns per warp: 28 fits N = 100 (reference widths) in four blocks, 32 otherwise
     const int blocks32 = (N + 31) / 32;
@@ -1048,10 +1048,11 @@ __device__ __forceinline__ HeadS heads_at(const float* base, const UpdArgs& P) {
 // both heads of one network in one pass: thread (m, n) does one dot product from shared memory
 //   n < A : mu[m][n] = h2[m] . Wmu[n] + bmu[n]         n == A : v[m] = g2[m] . Wv + bv
 __device__ __noinline__ void heads_fwd(HeadS hs, int A, int H2, int G2, const float* h2, int ldh2, const float* g2,
-                                       int ldg2, float* mu_out, int ldA, float* v_out) {
+                                       int ldg2, float* mu_out, int ldA, float* v_out, int mode = 0) {
     for (int o = threadIdx.x; o < UPD_ROWS * (A + 1); o += UPD_THREADS) {
         const int m = o / (A + 1), n = o - m * (A + 1);
         const bool isv = n == A;
+        if ((mode == 1 && isv) || (mode == 2 && !isv)) continue;   // one trunk at a time (trunk-serial tiles)
         const float* x = isv ? g2 + m * ldg2 : h2 + m * ldh2;
         const float* w = isv ? hs.Wv : hs.Wmu + n * hs.ldw;
         const int K4 = ((isv ? G2 : H2) + 3) >> 2;          // pad columns: activations finite, weights 0
@@ -1187,7 +1188,7 @@ __device__ __noinline__ unsigned dx_layer_t(const float* __restrict__ W, int N, 
 __device__ __forceinline__ unsigned dx_layer(const float* __restrict__ W, int N, int K, const float* dOut, int ldd,
                                          float* act, int lda, float* stage, int SF, uint64_t* bars, unsigned ph,
                                          const CUtensorMap* xmap, uint32_t tmem) {
-    if (xmap != nullptr && N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0)   // = ts_eligible() on the host
+    if (xmap != nullptr && N >= 32 && K >= 64 && (K & 3) == 0)               // = ts_eligible() on the host
         return ts_layer<true>(xmap, nullptr, N, K, dOut, ldd, act, lda, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
     const int KQ = (K + 3) >> 2;
     if (KQ > UPD_THREADS / 4) return dx_layer_t<4>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
@@ -1374,111 +1375,115 @@ __device__ __noinline__ void dw_layer_smallk(float* __restrict__ gW, float* __re
 
 
 // dW of a wide layer on the tensor cores, operands through tensor memory:
-//   dW[n][k] (+)= sum_s dOut[s][n] in[s][k]      D[k][n] = A[k][s] . B[n][s]^T  per tile of 128 k
+//   dW[n][k] (+)= sum_s dOut[s][n] in[s][k]      D[k][n] = A[k][s] . B[n][s]^T  per tile of 128 k and chunk of <= 128 n
 //   A = in^T: TMEM lane = k, columns = the 32 samples (read down a column of the activations, conflict-free)
-//   B = dOut^T as [hi rows 0..Np-1 | lo rows Np..2Np-1] K-major tiles (Np = N rounded up to 16), staged once
+//   B = dOut^T as [hi rows 0..Np-1 | lo rows Np..2Np-1] K-major tiles (Np = chunk width rounded up to 16), staged per chunk
 //   MMAs per k-step: D[:, 0..2Np) += A_hi x [B_hi | B_lo]  (N = 2 Np),  D[:, Np..2Np) += A_lo x B_hi  (N = Np)
 // Only 4 k-steps per tile, so one accumulator is accurate.  The epilogue has lane = k: for a fixed n a warp writes
 // 128 contiguous bytes of the partial.  Tiles are processed one after the other (transform, MMA, epilogue); the
-// epilogue - 2 Np columns of tensor memory and N x 128 floats to global memory - dominates.
+// epilogue - 2 Np columns of tensor memory and Np x 128 floats to global memory - dominates.  Layers with more than
+// 128 outputs (256-wide nets) run chunk by chunk; the activation tile is transformed again for every chunk.
 __device__ __noinline__ unsigned dw_layer_ts(float* __restrict__ gW, float* __restrict__ gb, int N, int K, const float* dOut,
                                              int ldd, const float* in, int ldin, bool accumulate, unsigned char* ts,
                                              uint64_t* bars, unsigned ph, uint32_t tmem) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int Np = (N + 15) & ~15;
     const int ntiles = (K + 127) >> 7;
     uint64_t* mma_done = bars + TS_BAR0 + 8;
-    __syncthreads();                                        // staging region free, dOut / in complete
     K2_ACC_DECL;
     K2_ACC_T0;
-    // ---- B: dOut^T, split, once ----
-    for (int e = tid; e < Np * 8; e += UPD_THREADS) {
-        const int n = e % Np, kc = e / Np;                  // consecutive threads -> consecutive n
-        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (n < N) {
-            const float* p = dOut + (4 * kc) * ldd + n;
-            x = make_float4(p[0], p[ldd], p[2 * ldd], p[3 * ldd]);
-        }
-        uint32_t hh[4], ll[4];
-        ts_split(x.x, hh[0], ll[0]); ts_split(x.y, hh[1], ll[1]); ts_split(x.z, hh[2], ll[2]); ts_split(x.w, hh[3], ll[3]);
-        *reinterpret_cast<uint4*>(ts + tc_off(n, kc)) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
-        *reinterpret_cast<uint4*>(ts + tc_off(Np + n, kc)) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
-    }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    K2_ACC(40);
-    const uint32_t idm = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)((2 * Np) >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-    const uint32_t idc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(Np >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-    const uint64_t bd = tc_desc(smem_u32(ts));
     constexpr uint64_t KSTEP = (2 * TC_LBO) >> 4;
-    for (int t = 0; t < ntiles; ++t) {
-        if (warp < 4) {                                     // ---- A: 32 samples of my activation column ----
-            const int k = 128 * t + 32 * warp + lane;
-            uint32_t hi[32], lo[32];
-            const float* cp = in + min(k, K - 1);
-#pragma unroll
-            for (int sidx = 0; sidx < 32; ++sidx) ts_split(k < K ? cp[sidx * ldin] : 0.f, hi[sidx], lo[sidx]);
-            const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A;
-            tmem_st32(ta, hi);
-            tmem_st32(ta + 32, lo);
-            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    for (int nbase = 0; nbase < N; nbase += 128) {
+        const int Nc = min(128, N - nbase);                 // this chunk's outputs
+        const int Np = (Nc + 15) & ~15;
+        __syncthreads();                                    // staging region free, dOut / in complete
+        // ---- B: dOut^T of the chunk, split ----
+        for (int e = tid; e < Np * 8; e += UPD_THREADS) {
+            const int n = e % Np, kc = e / Np;              // consecutive threads -> consecutive n
+            float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (n < Nc) {
+                const float* p = dOut + (4 * kc) * ldd + nbase + n;
+                x = make_float4(p[0], p[ldd], p[2 * ldd], p[3 * ldd]);
+            }
+            uint32_t hh[4], ll[4];
+            ts_split(x.x, hh[0], ll[0]); ts_split(x.y, hh[1], ll[1]); ts_split(x.z, hh[2], ll[2]); ts_split(x.w, hh[3], ll[3]);
+            *reinterpret_cast<uint4*>(ts + tc_off(n, kc)) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+            *reinterpret_cast<uint4*>(ts + tc_off(Np + n, kc)) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
         }
-        K2_ACC(41);
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();
-        K2_ACC(42);
-        if (warp == 7) {
-            const uint32_t el = elect_one();
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        K2_ACC(40);
+        const uint32_t idm = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)((2 * Np) >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t idc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(Np >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        const uint64_t bd = tc_desc(smem_u32(ts));
+        for (int t = 0; t < ntiles; ++t) {
+            if (warp < 4) {                                 // ---- A: 32 samples of my activation column ----
+                const int k = 128 * t + 32 * warp + lane;
+                uint32_t hi[32], lo[32];
+                const float* cp = in + min(k, K - 1);
+#pragma unroll
+                for (int sidx = 0; sidx < 32; ++sidx) ts_split(k < K ? cp[sidx * ldin] : 0.f, hi[sidx], lo[sidx]);
+                const uint32_t ta = tmem + ((uint32_t)(32 * warp) << 16) + TS_TM_A;
+                tmem_st32(ta, hi);
+                tmem_st32(ta + 32, lo);
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            }
+            K2_ACC(41);
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncthreads();
+            K2_ACC(42);
+            if (warp == 7) {
+                const uint32_t el = elect_one();
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) ts_mma_e(tmem, tmem + TS_TM_A + 8 * ks, bd + ks * KSTEP, idm, ks ? 1u : 0u, el);
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) ts_mma_e(tmem + Np, tmem + TS_TM_A + 32 + 8 * ks, bd + ks * KSTEP, idc, 1u, el);
+                ts_commit(&mma_done[0]);
+            }
+            mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);     // every thread sees every phase of this barrier
+            ph ^= 1u << TS_PH_MD;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            K2_ACC(43);
+            {
+                const int q = warp & 3, k = 128 * t + 32 * q + lane;
+                const int nh = Np >> 1, n0 = (warp >> 2) * nh;  // this warp's half of the chunk's columns
+                const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16);
+                for (int c = 0; c < nh; c += 32) {              // up to 32 columns of both halves in flight, one wait
+                    uint32_t v1[32], v2[32];
 #pragma unroll
-            for (int ks = 0; ks < 4; ++ks) ts_mma_e(tmem, tmem + TS_TM_A + 8 * ks, bd + ks * KSTEP, idm, ks ? 1u : 0u, el);
-#pragma unroll
-            for (int ks = 0; ks < 4; ++ks) ts_mma_e(tmem + Np, tmem + TS_TM_A + 32 + 8 * ks, bd + ks * KSTEP, idc, 1u, el);
-            ts_commit(&mma_done[0]);
-        }
-        mbar_wait(&mma_done[0], (ph >> TS_PH_MD) & 1u);     // every thread sees every phase of this barrier
-        ph ^= 1u << TS_PH_MD;
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        K2_ACC(43);
-        {
-            const int q = warp & 3, k = 128 * t + 32 * q + lane;
-            const int nh = Np >> 1, n0 = (warp >> 2) * nh;  // this warp's half of the columns
-            const uint32_t tb = tmem + ((uint32_t)(32 * q) << 16);
-            for (int c = 0; c < nh; c += 32) {              // up to 32 columns of both halves in flight, one wait
-                uint32_t v1[32], v2[32];
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (c + 8 * i < nh) {
-                        tmem_ld_issue<8>(tb + n0 + c + 8 * i, v1 + 8 * i);
-                        tmem_ld_issue<8>(tb + Np + n0 + c + 8 * i, v2 + 8 * i);
-                    }
-                tmem_ld_wait();
-                // straight-line stores: one running pointer, the column limit as a predicate (a branch per element
-                // costs more than the store here)
-                const int lim = min(nh - c, N - n0 - c);
-                if (k < K && lim > 0) {
-                    float* dst = gW + (size_t)(n0 + c) * K + k;
-                    if (!accumulate) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const float o = __uint_as_float(v2[j]) + __uint_as_float(v1[j]);
-                            if (j < lim) *dst = o;
-                            dst += K;
+                    for (int i = 0; i < 4; ++i)
+                        if (c + 8 * i < nh) {
+                            tmem_ld_issue<8>(tb + n0 + c + 8 * i, v1 + 8 * i);
+                            tmem_ld_issue<8>(tb + Np + n0 + c + 8 * i, v2 + 8 * i);
                         }
-                    } else {
+                    tmem_ld_wait();
+                    // straight-line stores: one running pointer, the column limit as a predicate (a branch per element
+                    // costs more than the store here)
+                    const int lim = min(nh - c, Nc - n0 - c);
+                    if (k < K && lim > 0) {
+                        float* dst = gW + (size_t)(nbase + n0 + c) * K + k;
+                        if (!accumulate) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const float o = __uint_as_float(v2[j]) + __uint_as_float(v1[j]);
-                            if (j < lim) *dst += o;
-                            dst += K;
+                            for (int j = 0; j < 32; ++j) {
+                                const float o = __uint_as_float(v2[j]) + __uint_as_float(v1[j]);
+                                if (j < lim) *dst = o;
+                                dst += K;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const float o = __uint_as_float(v2[j]) + __uint_as_float(v1[j]);
+                                if (j < lim) *dst += o;
+                                dst += K;
+                            }
                         }
                     }
                 }
             }
+            K2_ACC(44);
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncthreads();                                    // accumulator and A columns free for the next tile
+            K2_ACC(45);
         }
-        K2_ACC(44);
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncthreads();                                    // accumulator and A columns free for the next tile
-        K2_ACC(45);
     }
     for (int n = tid; n < N; n += UPD_THREADS) {
         float sb = 0.f;
@@ -1496,9 +1501,11 @@ __device__ __noinline__ unsigned dw_layer_ts(float* __restrict__ gW, float* __re
 __device__ __noinline__ void heads_dw(float* __restrict__ gWmu, float* __restrict__ gbmu, float* __restrict__ gWv,
                                       float* __restrict__ gbv, int A, int H2, int G2, const float* dmu, int ldA,
                                       const float* dv4, const float* h2, int ldh2, const float* g2, int ldg2,
-                                      bool accumulate) {
+                                      bool accumulate, int mode = 0) {
     const int nmu = A * H2;
     for (int o = threadIdx.x; o < nmu + G2 + A + 1; o += UPD_THREADS) {
+        const bool policy = o < nmu || (o >= nmu + G2 && o < nmu + G2 + A);
+        if ((mode == 1 && !policy) || (mode == 2 && policy)) continue;   // one trunk at a time (trunk-serial tiles)
         float s = 0.f;
         float* dst;
         if (o < nmu) {
@@ -1548,9 +1555,11 @@ __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, 
         else fwd_small_k<8>(stage + first_v1_offset(d), nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1);
         K2_TICK(tick + 1);
     } else {
-        ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, tmem, nullptr);
+        ph = fwd_layer<true>(nw.W1, nw.b1, d.H1, d.O, S + P.o_x, P.ldO, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, tmem,
+                             maps ? maps + 2 : nullptr);
         K2_TICK(tick + 0);
-        ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, tmem, nullptr);
+        ph = fwd_layer<true>(nw.V1, nw.c1, d.G1, d.O, S + P.o_x, P.ldO, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, tmem,
+                             maps ? maps + 3 : nullptr);
         K2_TICK(tick + 1);
     }
     ph = fwd_layer<true>(nw.W2, nw.b2, d.H2, d.H1, S + P.o_h1, P.ldH1, S + P.o_h2, P.ldH2, stage, P.SF, bars, ph, tmem,
@@ -1562,6 +1571,24 @@ __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, 
     if (P.small_first && next != nullptr) first_layers_prefetch(stage, next->W1, next->V1, d, &bars[0]);
     heads_fwd(hs, d.A, d.H2, d.G2, S + P.o_h2, P.ldH2, S + P.o_g2, P.ldG2, mu_out, P.ldA, v_out);
     K2_TICK(tick + 4);
+    return ph;
+}
+
+// One trunk of one network on the tile, in the shared activation buffers a1 / a2 (trunk-serial tiles: wide nets whose
+// two trunks do not fit shared memory side by side).  trunk 0: policy (p_fc1, p_fc2, mu), trunk 1: value (v_fc1, v_fc2, v).
+__device__ __forceinline__ unsigned trunk_forward(const Net& nw, const HeadS& hs, const UpdArgs& P, float* S, int trunk,
+                                              float* mu_out, float* v_out, unsigned ph, uint32_t tmem, const CUtensorMap* maps) {
+    const dppo_dims& d = P.d;
+    float* stage = S + P.o_stage;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
+    const int N1 = trunk ? d.G1 : d.H1, N2 = trunk ? d.G2 : d.H2, ld1 = trunk ? P.ldG1 : P.ldH1, ld2 = trunk ? P.ldG2 : P.ldH2;
+    float* a1 = S + P.o_h1;
+    float* a2 = S + P.o_h2;
+    ph = fwd_layer<true>(trunk ? nw.V1 : nw.W1, trunk ? nw.c1 : nw.b1, N1, d.O, S + P.o_x, P.ldO, a1, ld1, stage, P.SF, bars, ph,
+                         tmem, maps ? maps + 2 + trunk : nullptr);
+    ph = fwd_layer<true>(trunk ? nw.V2 : nw.W2, trunk ? nw.c2 : nw.b2, N2, N1, a1, ld1, a2, ld2, stage, P.SF, bars, ph, tmem,
+                         maps ? maps + trunk : nullptr);
+    heads_fwd(hs, d.A, d.H2, d.G2, a2, P.ldH2, a2, P.ldG2, mu_out, P.ldA, v_out, 1 + trunk);
     return ph;
 }
 
@@ -1664,156 +1691,221 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         __syncthreads();
 
         K2_TICK(2);
+        const float lo = 1.f - P.clip, hi = 1.f + P.clip;               // clamp bounds (train.py:151)
+        const Net no = net_of(P.flavour == DPPO_FLAVOUR_DPPO ? P.theta_old : P.theta, P.lay);
+        float* stage = S + P.o_stage;
+        uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
+        const bool acc = !first;
+
+        // ---- losses and their derivatives w.r.t. mu, log_std (policy part) and v (value part) --------------------
+        // The two parts share nothing: the policy loss needs mu, mu_old, the actions and the advantages, the value loss
+        // v, v_old and the returns.  They run back to back for ordinary tiles and one per trunk for trunk-serial tiles.
+        auto loss_policy = [&]() {
+            if (P.flavour == DPPO_FLAVOUR_DPPO) {
+                const float g0 = -1.f / ((float)P.B * (float)d.A);          // d loss_clip / d min(.,.)
+                const float ge = -P.ent_coeff / ((float)P.B * (float)d.A);
+                for (int e = threadIdx.x; e < UPD_ROWS * d.A; e += UPD_THREADS) {
+                    const int m = e / d.A, a = e - m * d.A;
+                    float dmu = 0.f, dls = 0.f;
+                    if (m < valid) {
+                        const float x = S[P.o_act + m * d.A + a];
+                        const float A_ = S[P.o_adv + m];
+                        // normal(x, mu, sigma_sq), train.py:41-44, new and old parameters
+                        const float s = expf(__ldg(nw.ls + a)), so = expf(__ldg(no.ls + a));
+                        const float u = x - S[P.o_mu + m * P.ldA + a];
+                        const float w = -(u * u);
+                        const float two_s = 2.f * s;
+                        const float qq = w / two_s;
+                        const float ea = expf(qq);
+                        const float z = two_s * 3.14159274101257324f;       // fp32(np.pi)
+                        const float rt = sqrtf(z);
+                        const float bb = 1.f / rt;
+                        const float p = ea * bb;
+                        const float uo = x - S[P.o_muo + m * P.ldA + a];
+                        const float po = expf(-(uo * uo) / (2.f * so)) * (1.f / sqrtf(2.f * so * 3.14159274101257324f));
+                        const float den = 1e-10f + po;                       // train.py:148
+                        const float ratio = p / den;
+                        const float surr1 = ratio * A_;
+                        const float rc = fminf(fmaxf(ratio, lo), hi);
+                        const float surr2 = rc * A_;
+                        lsum_clip += fminf(surr1, surr2);
+                        lsum_ent += p * logf(p + 1e-5f);                     // train.py:159
+                        // torch.min backward: ties split the gradient in halves
+                        float d1, d2;
+                        if (surr1 < surr2) { d1 = g0; d2 = 0.f; }
+                        else if (surr1 > surr2) { d1 = 0.f; d2 = g0; }
+                        else { d1 = 0.5f * g0; d2 = 0.5f * g0; }
+                        float dratio = d1 * A_;
+                        if (ratio >= lo && ratio <= hi) dratio += d2 * A_;   // clamp backward (inclusive)
+                        float dp = dratio / den;
+                        dp += ge * (logf(p + 1e-5f) + p / (p + 1e-5f));
+                        // back through normal()
+                        const float dea = dp * bb, dbb = dp * ea;
+                        const float dq = dea * ea;
+                        const float dw = dq / two_s;
+                        float dtwo_s = -dq * w / (two_s * two_s);
+                        dmu = 2.f * u * dw;                                  // u = x - mu, w = -u^2
+                        const float drt = -dbb / (rt * rt);
+                        const float dz = drt / (2.f * rt);
+                        dtwo_s += dz * 3.14159274101257324f;
+                        dls = 2.f * dtwo_s * s;                              // sigma_sq = exp(log_std)
+                    }
+                    S[P.o_dmu + m * P.ldA + a] = dmu;
+                    S[P.o_muo + m * P.ldA + a] = dls;                        // mu_old no longer needed: reuse for dls
+                }
+            } else {
+                const float g0 = -1.f / (float)P.B;                          // ppo.py:161
+                const float half_log_2pi = 0.918938533204672742f;            // 0.5*math.log(2*math.pi)
+                for (int m = threadIdx.x; m < UPD_ROWS; m += UPD_THREADS) {
+                    float dlogp = 0.f;
+                    if (m < valid) {
+                        float logp = 0.f;
+                        for (int a = 0; a < d.A; ++a) {                      // ppo.py:150-151
+                            const float ls = __ldg(nw.ls + a);
+                            const float zz = (S[P.o_act + m * d.A + a] - S[P.o_mu + m * P.ldA + a]) / expf(ls);
+                            const float t = (-0.5f * (zz * zz) - half_log_2pi) - ls;
+                            logp = (a == 0) ? t : logp + t;
+                        }
+                        const float ratio = expf(logp - S[P.o_lpo + m]);    // ppo.py:156
+                        const float A_ = S[P.o_adv + m];
+                        const float surr1 = ratio * A_;
+                        const float surr2 = fminf(fmaxf(ratio, lo), hi) * A_;
+                        lsum_clip += fminf(surr1, surr2);
+                        float d1, d2;
+                        if (surr1 < surr2) { d1 = g0; d2 = 0.f; }
+                        else if (surr1 > surr2) { d1 = 0.f; d2 = g0; }
+                        else { d1 = 0.5f * g0; d2 = 0.5f * g0; }
+                        float dratio = d1 * A_;
+                        if (ratio >= lo && ratio <= hi) dratio += d2 * A_;
+                        dlogp = dratio * ratio;
+                    }
+                    for (int a = 0; a < d.A; ++a) {
+                        float dmu = 0.f, dls = 0.f;
+                        if (m < valid) {
+                            const float sg = expf(__ldg(nw.ls + a));
+                            const float zz = (S[P.o_act + m * d.A + a] - S[P.o_mu + m * P.ldA + a]) / sg;
+                            dmu = dlogp * zz / sg;
+                            dls = dlogp * (zz * zz - 1.f);
+                        }
+                        S[P.o_dmu + m * P.ldA + a] = dmu;
+                        S[P.o_muo + m * P.ldA + a] = dls;
+                    }
+                }
+            }
+        };
+        auto loss_value = [&]() {
+            if (P.flavour == DPPO_FLAVOUR_DPPO) {
+                const float gv = 0.5f / (float)P.B;                          // train.py:157
+                for (int m = threadIdx.x; m < UPD_ROWS; m += UPD_THREADS) {
+                    float dv = 0.f;
+                    if (m < valid) {
+                        const float v = S[P.o_v + m], vo = S[P.o_vo + m], R = S[P.o_ret + m];
+                        const float e1 = v - R;
+                        const float f1 = e1 * e1;                            // train.py:154
+                        const float dl = v - vo;
+                        const float vc = vo + fminf(fmaxf(dl, -P.clip), P.clip);   // train.py:155
+                        const float e2 = vc - R;
+                        const float f2 = e2 * e2;                            // train.py:156
+                        lsum_val += fmaxf(f1, f2);
+                        const bool inr = (dl >= -P.clip) && (dl <= P.clip);
+                        float c1, c2;
+                        if (f1 > f2) { c1 = gv; c2 = 0.f; }
+                        else if (f1 < f2) { c1 = 0.f; c2 = gv; }
+                        else { c1 = 0.5f * gv; c2 = 0.5f * gv; }
+                        dv = c1 * 2.f * e1 + (inr ? c2 * 2.f * e2 : 0.f);
+                    }
+                    S[P.o_dv + 4 * m] = dv;
+                }
+            } else {
+                const float gv = 1.f / (float)P.B;                           // ppo.py:164
+                for (int m = threadIdx.x; m < UPD_ROWS; m += UPD_THREADS) {
+                    float dv = 0.f;
+                    if (m < valid) {
+                        const float e1 = S[P.o_v + m] - S[P.o_ret + m];
+                        lsum_val += e1 * e1;
+                        dv = gv * 2.f * e1;
+                    }
+                    S[P.o_dv + 4 * m] = dv;
+                }
+            }
+        };
+        // d log_std[a] = sum over the tile's samples (ascending m)
+        auto dls_reduce = [&]() {
+            for (int a = threadIdx.x; a < d.A; a += UPD_THREADS) {
+                float s = 0.f;
+                for (int m = 0; m < UPD_ROWS; ++m) s += S[P.o_muo + m * P.ldA + a];
+                if (P.flavour == DPPO_FLAVOUR_PPO && blockIdx.x == 0 && first) s -= P.ent_coeff;   // ppo.py:152-153,167
+                go.ls[a] = first ? s : go.ls[a] + s;
+            }
+        };
+        // dW / db of a layer: tensor cores when the shape allows (= ts_eligible() on the host), else the FP32 pipe
+        auto dw_any = [&](float* gW, float* gb, int N, int K, const float* dOut, int ldd, const float* in, int ldin) {
+            if (P.use_ts && N >= 32 && K >= 64 && (K & 3) == 0)
+                ph = dw_layer_ts(gW, gb, N, K, dOut, ldd, in, ldin, acc, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
+            else
+                dw_layer(gW, gb, N, K, dOut, ldd, in, ldin, acc);
+        };
+
+        if (P.trunk_serial) {
+            // ---- wide nets: one trunk from its forward passes to its last gradient, then the other, in the same
+            // activation buffers a1 (first hidden layer) and a2 (second hidden layer) --------------------------------
+            float* a1 = S + P.o_h1;
+            float* a2 = S + P.o_h2;
+            for (int trunk = 0; trunk < 2; ++trunk) {
+                const int N1 = trunk ? d.G1 : d.H1, N2 = trunk ? d.G2 : d.H2;
+                const int ld1 = trunk ? P.ldG1 : P.ldH1, ld2 = trunk ? P.ldG2 : P.ldH2;
+                if (trunk) {                                  // pad columns of the buffers must read as 0 again
+                    for (int i = P.o_h1 + threadIdx.x; i < P.o_act; i += UPD_THREADS) S[i] = 0.f;
+                    __syncthreads();
+                }
+                if (run_old)
+                    ph = trunk_forward(no, hs_old, P, S, trunk, S + P.o_muo, S + P.o_vo, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr);
+                ph = trunk_forward(nw, hs_new, P, S, trunk, S + P.o_mu, S + P.o_v, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr);
+                if (same_old) {
+                    if (trunk == 0) for (int e = threadIdx.x; e < UPD_ROWS * P.ldA; e += UPD_THREADS) S[P.o_muo + e] = S[P.o_mu + e];
+                    else for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
+                    __syncthreads();
+                }
+                if (trunk == 0) {
+                    loss_policy();
+                    __syncthreads();
+                    dls_reduce();
+                } else {
+                    loss_value();
+                }
+                __syncthreads();
+                heads_dw(go.Wmu, go.bmu, go.Wv, go.bv, d.A, d.H2, d.G2, S + P.o_dmu, P.ldA, S + P.o_dv, a2, P.ldH2, a2, P.ldG2,
+                         acc, 1 + trunk);
+                if (trunk == 0) head_dx(hs_new.Wmu, hs_new.ldw, d.A, d.H2, S + P.o_dmu, P.ldA, a2, ld2);      // a2 <- dz2
+                else head_dx(hs_new.Wv, 0, 1, d.G2, S + P.o_dv, 4, a2, ld2);
+                dw_any(trunk ? go.V2 : go.W2, trunk ? go.c2 : go.b2, N2, N1, a2, ld2, a1, ld1);
+                ph = dx_layer(trunk ? nw.V2 : nw.W2, N2, N1, a2, ld2, a1, ld1, stage, P.SF, bars, ph,
+                              P.use_ts ? &P.map_dx[trunk] : nullptr, tmem);                                   // a1 <- dz1
+                dw_any(trunk ? go.V1 : go.W1, trunk ? go.c1 : go.b1, N1, d.O, a1, ld1, S + P.o_x, P.ldO);
+            }
+            continue;
+        }
+
         // ---- forward(s) -----------------------------------------------------------------------
         // epoch 0 of a cycle: model_old is a copy of model (train.py:128-129), so the caller passes
         // theta_old == theta and the old network's outputs are the new network's, bit for bit
-        if (run_old) {
-            const Net no = net_of(P.theta_old, P.lay);
+        if (run_old)
             ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr, &nw);              // train.py:142
-        }
         ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr, nullptr);                    // train.py:145 / ppo.py:148
         if (same_old) {
             for (int e = threadIdx.x; e < UPD_ROWS * P.ldA; e += UPD_THREADS) S[P.o_muo + e] = S[P.o_mu + e];
             for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
             __syncthreads();
         }
-
-        // ---- losses and their derivatives w.r.t. mu, v, log_std ---------------------------------
-        const float lo = 1.f - P.clip, hi = 1.f + P.clip;               // clamp bounds (train.py:151)
-        if (P.flavour == DPPO_FLAVOUR_DPPO) {
-            const float g0 = -1.f / ((float)P.B * (float)d.A);          // d loss_clip / d min(.,.)
-            const float ge = -P.ent_coeff / ((float)P.B * (float)d.A);
-            const Net no = net_of(P.theta_old, P.lay);
-            for (int e = threadIdx.x; e < UPD_ROWS * d.A; e += UPD_THREADS) {
-                const int m = e / d.A, a = e - m * d.A;
-                float dmu = 0.f, dls = 0.f;
-                if (m < valid) {
-                    const float x = S[P.o_act + m * d.A + a];
-                    const float A_ = S[P.o_adv + m];
-                    // normal(x, mu, sigma_sq), train.py:41-44, new and old parameters
-                    const float s = expf(__ldg(nw.ls + a)), so = expf(__ldg(no.ls + a));
-                    const float u = x - S[P.o_mu + m * P.ldA + a];
-                    const float w = -(u * u);
-                    const float two_s = 2.f * s;
-                    const float qq = w / two_s;
-                    const float ea = expf(qq);
-                    const float z = two_s * 3.14159274101257324f;       // fp32(np.pi)
-                    const float rt = sqrtf(z);
-                    const float bb = 1.f / rt;
-                    const float p = ea * bb;
-                    const float uo = x - S[P.o_muo + m * P.ldA + a];
-                    const float po = expf(-(uo * uo) / (2.f * so)) * (1.f / sqrtf(2.f * so * 3.14159274101257324f));
-                    const float den = 1e-10f + po;                       // train.py:148
-                    const float ratio = p / den;
-                    const float surr1 = ratio * A_;
-                    const float rc = fminf(fmaxf(ratio, lo), hi);
-                    const float surr2 = rc * A_;
-                    lsum_clip += fminf(surr1, surr2);
-                    lsum_ent += p * logf(p + 1e-5f);                     // train.py:159
-                    // torch.min backward: ties split the gradient in halves
-                    float d1, d2;
-                    if (surr1 < surr2) { d1 = g0; d2 = 0.f; }
-                    else if (surr1 > surr2) { d1 = 0.f; d2 = g0; }
-                    else { d1 = 0.5f * g0; d2 = 0.5f * g0; }
-                    float dratio = d1 * A_;
-                    if (ratio >= lo && ratio <= hi) dratio += d2 * A_;   // clamp backward (inclusive)
-                    float dp = dratio / den;
-                    dp += ge * (logf(p + 1e-5f) + p / (p + 1e-5f));
-                    // back through normal()
-                    const float dea = dp * bb, dbb = dp * ea;
-                    const float dq = dea * ea;
-                    const float dw = dq / two_s;
-                    float dtwo_s = -dq * w / (two_s * two_s);
-                    dmu = 2.f * u * dw;                                  // u = x - mu, w = -u^2
-                    const float drt = -dbb / (rt * rt);
-                    const float dz = drt / (2.f * rt);
-                    dtwo_s += dz * 3.14159274101257324f;
-                    dls = 2.f * dtwo_s * s;                              // sigma_sq = exp(log_std)
-                }
-                S[P.o_dmu + m * P.ldA + a] = dmu;
-                S[P.o_muo + m * P.ldA + a] = dls;                        // mu_old no longer needed: reuse for dls
-            }
-            const float gv = 0.5f / (float)P.B;                          // train.py:157
-            for (int m = threadIdx.x; m < UPD_ROWS; m += UPD_THREADS) {
-                float dv = 0.f;
-                if (m < valid) {
-                    const float v = S[P.o_v + m], vo = S[P.o_vo + m], R = S[P.o_ret + m];
-                    const float e1 = v - R;
-                    const float f1 = e1 * e1;                            // train.py:154
-                    const float dl = v - vo;
-                    const float vc = vo + fminf(fmaxf(dl, -P.clip), P.clip);   // train.py:155
-                    const float e2 = vc - R;
-                    const float f2 = e2 * e2;                            // train.py:156
-                    lsum_val += fmaxf(f1, f2);
-                    const bool inr = (dl >= -P.clip) && (dl <= P.clip);
-                    float c1, c2;
-                    if (f1 > f2) { c1 = gv; c2 = 0.f; }
-                    else if (f1 < f2) { c1 = 0.f; c2 = gv; }
-                    else { c1 = 0.5f * gv; c2 = 0.5f * gv; }
-                    dv = c1 * 2.f * e1 + (inr ? c2 * 2.f * e2 : 0.f);
-                }
-                S[P.o_dv + 4 * m] = dv;
-            }
-        } else {
-            const float g0 = -1.f / (float)P.B;                          // ppo.py:161
-            const float gv = 1.f / (float)P.B;                           // ppo.py:164
-            const float half_log_2pi = 0.918938533204672742f;            // 0.5*math.log(2*math.pi)
-            for (int m = threadIdx.x; m < UPD_ROWS; m += UPD_THREADS) {
-                float dv = 0.f, dlogp = 0.f;
-                if (m < valid) {
-                    float logp = 0.f;
-                    for (int a = 0; a < d.A; ++a) {                      // ppo.py:150-151
-                        const float ls = __ldg(nw.ls + a);
-                        const float zz = (S[P.o_act + m * d.A + a] - S[P.o_mu + m * P.ldA + a]) / expf(ls);
-                        const float t = (-0.5f * (zz * zz) - half_log_2pi) - ls;
-                        logp = (a == 0) ? t : logp + t;
-                    }
-                    const float ratio = expf(logp - S[P.o_lpo + m]);    // ppo.py:156
-                    const float A_ = S[P.o_adv + m];
-                    const float surr1 = ratio * A_;
-                    const float surr2 = fminf(fmaxf(ratio, lo), hi) * A_;
-                    lsum_clip += fminf(surr1, surr2);
-                    float d1, d2;
-                    if (surr1 < surr2) { d1 = g0; d2 = 0.f; }
-                    else if (surr1 > surr2) { d1 = 0.f; d2 = g0; }
-                    else { d1 = 0.5f * g0; d2 = 0.5f * g0; }
-                    float dratio = d1 * A_;
-                    if (ratio >= lo && ratio <= hi) dratio += d2 * A_;
-                    dlogp = dratio * ratio;
-                    const float e1 = S[P.o_v + m] - S[P.o_ret + m];
-                    lsum_val += e1 * e1;
-                    dv = gv * 2.f * e1;
-                }
-                S[P.o_dv + 4 * m] = dv;
-                for (int a = 0; a < d.A; ++a) {
-                    float dmu = 0.f, dls = 0.f;
-                    if (m < valid) {
-                        const float sg = expf(__ldg(nw.ls + a));
-                        const float zz = (S[P.o_act + m * d.A + a] - S[P.o_mu + m * P.ldA + a]) / sg;
-                        dmu = dlogp * zz / sg;
-                        dls = dlogp * (zz * zz - 1.f);
-                    }
-                    S[P.o_dmu + m * P.ldA + a] = dmu;
-                    S[P.o_muo + m * P.ldA + a] = dls;
-                }
-            }
-        }
+        loss_policy();
+        loss_value();
         __syncthreads();
         K2_TICK(13);
-        // d log_std[a] = sum over the tile's samples (ascending m)
-        for (int a = threadIdx.x; a < d.A; a += UPD_THREADS) {
-            float s = 0.f;
-            for (int m = 0; m < UPD_ROWS; ++m) s += S[P.o_muo + m * P.ldA + a];
-            if (P.flavour == DPPO_FLAVOUR_PPO && blockIdx.x == 0 && first) s -= P.ent_coeff;   // ppo.py:152-153,167
-            go.ls[a] = first ? s : go.ls[a] + s;
-        }
+        dls_reduce();
         __syncthreads();
 
         K2_TICK(14);
         // ---- backward ---------------------------------------------------------------------------
-        const bool acc = !first;
-        float* stage = S + P.o_stage;
-        uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
         heads_dw(go.Wmu, go.bmu, go.Wv, go.bv, d.A, d.H2, d.G2, S + P.o_dmu, P.ldA, S + P.o_dv, S + P.o_h2, P.ldH2,
                  S + P.o_g2, P.ldG2, acc);
         K2_TICK(15);
@@ -1823,17 +1915,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         K2_TICK(16);
         head_dx(hs_new.Wv, 0, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);                          // g2 <- dz2 (value)
         K2_TICK(17);
-        if (P.use_ts && d.H2 <= 128 && d.H2 >= 32 && d.H1 >= 64 && (d.H1 & 3) == 0)
-            ph = dw_layer_ts(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc,
-                             reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
-        else
-            dw_layer(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, acc);
+        dw_any(go.W2, go.b2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1);
         K2_TICK(18);
-        if (P.use_ts && d.G2 <= 128 && d.G2 >= 32 && d.G1 >= 64 && (d.G1 & 3) == 0)
-            ph = dw_layer_ts(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc,
-                             reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
-        else
-            dw_layer(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, acc);
+        dw_any(go.V2, go.c2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1);
         K2_TICK(19);
         ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph,
                       P.use_ts ? &P.map_dx[0] : nullptr, tmem);                                     // h1 <- dz1
@@ -1844,12 +1928,12 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         if (P.first_ts && d.H1 <= 512)
             ph = dw_first_ts(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem);
         else if (d.O <= 24 && d.H1 >= 256 && d.H1 * d.O <= P.SF) dw_layer_smallk(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc, stage);
-        else dw_layer(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO, acc);
+        else dw_any(go.W1, go.b1, d.H1, d.O, S + P.o_h1, P.ldH1, S + P.o_x, P.ldO);
         K2_TICK(22);
         if (P.first_ts && d.G1 <= 512)
             ph = dw_first_ts(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage, first_b_tiles(stage, d), bars, ph, tmem);
         else if (d.O <= 24 && d.G1 >= 256 && d.G1 * d.O <= P.SF) dw_layer_smallk(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc, stage);
-        else dw_layer(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO, acc);
+        else dw_any(go.V1, go.c1, d.G1, d.O, S + P.o_g1, P.ldG1, S + P.o_x, P.ldO);
         K2_TICK(23);
         K2_TICK(24);
     }
@@ -1922,48 +2006,75 @@ void pick_tiling(int B, int* TM, int* nparts) {
     *nparts = ntiles < sms ? ntiles : sms;
 }
 
+// layers that can run on the tensor cores (mirrored by the conditions in fwd_layer / dx_layer / dw_any)
+bool ts_eligible(int N, int K) { return N >= 32 && K >= 64 && (K & 3) == 0; }
+
+// Shared-memory carve-up.  Preference order: everything resident with the 100 KB staging region that the tensor-core
+// layers need; if that does not fit (wide nets), first the head weights move to global memory, then the two trunks
+// share their activation buffers (trunk-serial tiles: P.o_g1 = P.o_h1, P.o_g2 = P.o_h2); if the staging region still
+// does not fit, the FP32-pipe layers run with whatever staging is left (>= UPD_STAGE_MIN).
 int plan(UpdArgs& P) {
     const dppo_dims& d = P.d;
     P.ldO = ld_of(d.O); P.ldH1 = ld_of(d.H1); P.ldH2 = ld_of(d.H2); P.ldG1 = ld_of(d.G1); P.ldG2 = ld_of(d.G2);
     P.ldA = ld_of(d.A);
     const int TM = UPD_ROWS;                    // tiles always hold 32 rows; P.TM of them are samples
-    int o = 0;
-    auto take = [&](int n) { int r = o; o += (n + 3) & ~3; return r; };
-    P.o_x = take(TM * P.ldO);
-    P.o_h1 = take(TM * P.ldH1);
-    P.o_h2 = take(TM * P.ldH2);
-    P.o_g1 = take(TM * P.ldG1);
-    P.o_g2 = take(TM * P.ldG2);
-    P.o_act = take(TM * d.A);
-    P.o_mu = take(TM * P.ldA);
-    P.o_muo = take(TM * P.ldA);
-    P.o_dmu = take(TM * P.ldA);
-    P.o_v = take(TM);
-    P.o_vo = take(TM);
-    P.o_dv = take(TM * 4);                      // [TM][4]: column 0 = dv, so rows are 16-byte vectors
-    P.o_adv = take(TM);
-    P.o_ret = take(TM);
-    P.o_lpo = take(TM);
-    P.o_zero_end = o;                           // everything before this is zeroed per tile
-    P.o_red = take(UPD_THREADS);
-    P.o_bars = take(2 * (TS_BAR0 + TS_NBARS) + 4);   // the mbarriers (8 bytes each) + the TMEM base address
     P.head_floats = (d.A * P.ldH2 + ((d.A + 3) & ~3) + P.ldG2 + 4 + 3) & ~3;
-    // head weights resident in shared memory unless that would squeeze the stage buffers below their
-    // minimum (then they are read from global memory, which needs 16-byte aligned rows)
-    P.heads_in_smem = 1;
-    if ((227 * 1024 / 4 - o - 2 * P.head_floats - 64) / 2 < UPD_STAGE_MIN && (d.H2 & 3) == 0 && (d.G2 & 3) == 0)
-        P.heads_in_smem = 0;
-    P.o_heads = take(P.heads_in_smem ? 2 * P.head_floats : 4);
-    o = (o + 255) & ~255;                       // 1024-byte aligned stage buffers (UMMA descriptors, TMA swizzle atoms)
-    P.o_stage = o;                              // everything before the stage is zeroed per tile
-    // two weight staging buffers from what is left of the 227 KB
-    int sf = ((227 * 1024 / 4 - o) / 2) & ~127;
-    if (sf > UPD_STAGE_MAX) sf = UPD_STAGE_MAX;
-    P.SF = sf;
-    o += 2 * (sf > 0 ? sf : 0);
-    P.smem_floats = o;
-    P.small_first = (d.O <= 32 && ((d.H1 * d.O + 3) & ~3) + d.G1 * d.O <= 2 * sf) ? 1 : 0;
-    P.first_ts = (P.small_first && ((((d.H1 * d.O + 3) & ~3) + d.G1 * d.O + 31) & ~31) + 2 * TS_BT_BYTES / 4 <= 2 * sf &&
+    const bool heads_global_ok = (d.H2 & 3) == 0 && (d.G2 & 3) == 0;     // global head rows must be 16-byte aligned
+    const bool want_ts = k2_path() == DPPO_K2_PATH_AUTO &&
+                         (ts_eligible(d.H2, d.H1) || ts_eligible(d.G2, d.G1) || ts_eligible(d.H1, d.O) || ts_eligible(d.G1, d.O));
+    auto layout = [&](bool heads_smem, bool serial) {
+        int o = 0;
+        auto take = [&](int n) { int r = o; o += (n + 3) & ~3; return r; };
+        P.o_x = take(TM * P.ldO);
+        if (serial) {
+            P.o_h1 = take(TM * (P.ldH1 > P.ldG1 ? P.ldH1 : P.ldG1));
+            P.o_h2 = take(TM * (P.ldH2 > P.ldG2 ? P.ldH2 : P.ldG2));
+            P.o_g1 = P.o_h1;
+            P.o_g2 = P.o_h2;
+        } else {
+            P.o_h1 = take(TM * P.ldH1);
+            P.o_h2 = take(TM * P.ldH2);
+            P.o_g1 = take(TM * P.ldG1);
+            P.o_g2 = take(TM * P.ldG2);
+        }
+        P.o_act = take(TM * d.A);
+        P.o_mu = take(TM * P.ldA);
+        P.o_muo = take(TM * P.ldA);
+        P.o_dmu = take(TM * P.ldA);
+        P.o_v = take(TM);
+        P.o_vo = take(TM);
+        P.o_dv = take(TM * 4);                      // [TM][4]: column 0 = dv, so rows are 16-byte vectors
+        P.o_adv = take(TM);
+        P.o_ret = take(TM);
+        P.o_lpo = take(TM);
+        P.o_zero_end = o;                           // everything before this is zeroed per tile
+        P.o_red = take(UPD_THREADS);
+        P.o_bars = take(2 * (TS_BAR0 + TS_NBARS) + 4);   // the mbarriers (8 bytes each) + the TMEM base address
+        P.heads_in_smem = heads_smem ? 1 : 0;
+        P.o_heads = take(heads_smem ? 2 * P.head_floats : 4);
+        o = (o + 255) & ~255;                       // 1024-byte aligned stage buffers (UMMA descriptors, TMA swizzle atoms)
+        P.o_stage = o;
+        int sf = ((227 * 1024 / 4 - o) / 2) & ~127;  // two weight staging buffers from what is left of the 227 KB
+        if (sf > UPD_STAGE_MAX) sf = UPD_STAGE_MAX;
+        P.SF = sf;
+        P.trunk_serial = serial ? 1 : 0;
+        P.smem_floats = o + 2 * (sf > 0 ? sf : 0);
+        return sf;
+    };
+    const int ts_floats = TS_BYTES / 8;             // per staging buffer
+    int sf = layout(true, false);
+    if (want_ts && sf < ts_floats) {
+        bool done = false;
+        if (heads_global_ok && layout(false, false) >= ts_floats) done = true;
+        if (!done && layout(true, true) >= ts_floats) done = true;
+        if (!done && heads_global_ok && layout(false, true) >= ts_floats) done = true;
+        if (!done) sf = layout(true, false);
+    }
+    if (P.SF < UPD_STAGE_MIN && !P.trunk_serial && heads_global_ok) layout(false, false);   // FP32 pipe, tight shared memory
+    const int o = P.smem_floats;
+    // first layers from flat weight copies prefetched a phase ahead (narrow observations); not for trunk-serial tiles
+    P.small_first = (!P.trunk_serial && d.O <= 32 && ((d.H1 * d.O + 3) & ~3) + d.G1 * d.O <= 2 * P.SF) ? 1 : 0;
+    P.first_ts = (P.small_first && ((((d.H1 * d.O + 3) & ~3) + d.G1 * d.O + 31) & ~31) + 2 * TS_BT_BYTES / 4 <= 2 * P.SF &&
                   k2_path() == DPPO_K2_PATH_AUTO) ? 1 : 0;
     return o;
 }
@@ -1997,7 +2108,6 @@ bool make_wmap(CUtensorMap* map, const float* W, int rows, int cols, int box_c, 
                CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
-bool ts_eligible(int N, int K) { return N <= 128 && N >= 32 && K >= 64 && (K & 3) == 0; }
 
 // The six tensor maps depend only on (device, theta, theta_old, dims): encoded once per combination and kept.
 // An engine alternates between at most two (theta_old = theta in epoch 0, the lagging copy afterwards).
@@ -2006,7 +2116,7 @@ struct MapEntry {
     const float *theta, *theta_old;
     dppo_dims d;
     bool ok;
-    CUtensorMap fwd[2][2], dx[2];
+    CUtensorMap fwd[2][4], dx[2];
 };
 constexpr int MAP_CACHE = 16;
 MapEntry g_maps[MAP_CACHE];
@@ -2028,6 +2138,10 @@ const MapEntry* wide_layer_maps(int dev, const float* theta, const float* theta_
             ok = ok && make_wmap(&e.fwd[net][0], t + lay.off[3], d.H2, d.H1, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
         if (ts_eligible(d.G2, d.G1))
             ok = ok && make_wmap(&e.fwd[net][1], t + lay.off[7], d.G2, d.G1, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (ts_eligible(d.H1, d.O))                              // wide observations: the first layers too
+            ok = ok && make_wmap(&e.fwd[net][2], t + lay.off[1], d.H1, d.O, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (ts_eligible(d.G1, d.O))
+            ok = ok && make_wmap(&e.fwd[net][3], t + lay.off[5], d.G1, d.O, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
     }
     if (ts_eligible(d.H2, d.H1))
         ok = ok && make_wmap(&e.dx[0], theta + lay.off[3], d.H2, d.H1, 128, TC_KB, CU_TENSOR_MAP_SWIZZLE_NONE);

@@ -286,6 +286,11 @@ CASES = [
     (376, 17, (256, 256, 256, 256), 32768, 4096),      # C5 at its full minibatch
     (4, 1, (64, 64, 64, 64), 2048, 64),                # C1 with BASELINE's 64x64 nets
     (17, 6, (64, 64, 64, 64), 2048, 2048),             # C2 with 64x64 nets
+    # tensor-core layers with several 128-row tiles, first layers on the tensor cores (observation width >= 64), trunk-serial tiles
+    (64, 3, (128, 128, 192, 128), 700, 300),           # first layers eligible (K = 64), 192 outputs = two tiles, trunks side by side
+    (40, 4, (300, 200, 260, 132), 900, 400),           # odd widths over several tiles: 300 (3 tiles), 200, 260, 132
+    (376, 17, (256, 256, 256, 256), 4096, 4096 - 17),  # Humanoid, more tiles than SMs is false here but the last tile is ragged
+    (128, 8, (512, 256, 512, 256), 800, 333),          # 512-wide first layers: four tiles, trunk-serial
 ]
 
 
