@@ -688,16 +688,15 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                 }
                 if (warp == 0) K2_TR(0, gp, 4);
                 // Raw tile release.  The producer warp refills the slot (TMA, async proxy) as soon as all four transform
-                // warps have arrived on raw_free, so an arrive may only be issued once the warp's LDS of the slot have
-                // DELIVERED their data.  Program order alone does not give that: the arrive does not depend on the loaded
-                // registers, and ptxas is free to sink the split arithmetic (the only consumer of the LDS results) below
-                // it - in the build that released right after the split, the SASS has the eight LDS.128, the warp sync and
-                // SYNCS.ARRIVE back to back and the first use of the loaded registers 30 instructions later, i.e. the
-                // slot was handed back with its loads still in flight, and the engine became non-repeatable
-                // (profiles/r02_k2_release_race.md).  Here the arrive follows both tiles' tcgen05.st in program order;
-                // the st instructions read the split results, the split results need every LDS destination register,
-                // so all loads of the slot have completed when the arrive issues: the ordering is a data dependence,
-                // not a time window.
+                // warps have arrived on raw_free, and nothing orders a shared-memory load that has been ISSUED but has not
+                // yet read the array against that refill: the arrive does not depend on the loaded registers, and ptxas
+                // sinks the split arithmetic (the only consumer of the loads) below it.  Round 1's per-tile release right
+                // after the split did exactly that and lost the race in the dX pass of the 500-wide layer (21-25 of 300
+                // launches; the same kernel with the split results pinned in registers before the arrive is bit-clean:
+                // profiles/r02_k2_release_race.md).  Rule: release a TMA destination only after an instruction that
+                // consumes every value loaded from it.  Here the arrive follows both tiles' tcgen05.st in program order;
+                // the st read the split results, the split results need every LDS destination register, so all loads of
+                // the slot have completed when the arrive issues - a data dependence, not a time window.
 #if !DPPO_K2_EARLY_RELEASE
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&raw_free[s]);
