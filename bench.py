@@ -265,6 +265,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--host-sampler", action="store_true",
+                    help="e2e: draw the minibatch positions with the host sampler (worker thread + upload) instead of on the GPU")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     wl = CONFIGS[args.config]
@@ -361,14 +363,15 @@ def main():
     devbuf2 = RolloutBuffer(wl["T"], wl["O"], wl["A"], dev)
     devs2 = [devbuf, devbuf2]
     reset_stats()
-    engine.update_stream([host], devs2, 3, obs_stats=stats, rng=rng, gshared=gsh, on_step=None)
+    sampler = None if args.host_sampler else nv.DeviceSampler(rng)       # random.sample on the GPU, same stream of positions
+    engine.update_stream([host], devs2, 3, obs_stats=stats, rng=rng, gshared=gsh, on_step=None, sampler=sampler)
     barrier()
     n_e2e = max(3, min(args.steps, 100))
     keep_n = max(1, (1 << 23) // wl["T"] // max(world, 1))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     reset_stats()
     e0.record()
-    _, h2d, d2h = engine.update_stream([host], devs2, n_e2e, obs_stats=stats, rng=rng, gshared=gsh,
+    _, h2d, d2h = engine.update_stream([host], devs2, n_e2e, obs_stats=stats, rng=rng, gshared=gsh, sampler=sampler,
                                        on_step=lambda i: reset_stats() if i % keep_n == keep_n - 1 else None)
     e1.record()
     barrier()
@@ -444,7 +447,9 @@ def main():
            "ms_per_step": t_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "f32", "data": "synthetic", "config": config_dict(wl, world), "clocks": sampler.summary(),
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                   "ms_per_step": e2e_ms / n_e2e, "steps": n_e2e},
+                   "ms_per_step": e2e_ms / n_e2e, "steps": n_e2e,
+                   "index_sampler": "host (C restatement of random.sample, worker thread, uploaded per step)" if args.host_sampler
+                   else "device (dppo_sample_indices: random.sample on the GPU, no index upload)"},
            "gpu_launches": launches_per_step * args.steps, "roofline": roofline, "parity": parity,
            "update_latency_us": step_us, "graph": use_graph, "comm": None if comm is None else comm.describe()}
     if world == 1 and not args.no_cpu_baseline:

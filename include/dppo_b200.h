@@ -232,6 +232,14 @@ int dppo_comm_allgather_loopback(dppo_comm** comms, int world, const double* con
 int dppo_sample_indices_host(uint32_t* mt_state624_host, int* mt_index_host, int64_t n, int k, int rounds,
                              int32_t* out_host);
 
+/* The same on the DEVICE: the Mersenne Twister state (624 words) and position live in device
+ * memory, the positions are written to device memory where K2 reads them - no index block crosses PCIe.  Bit-identical
+ * to random.sample for both of CPython's branches (pool / set), state and position advanced in place exactly as
+ * CPython would leave them.  scratch: dppo_sample_scratch_bytes(n, k) bytes.  One CTA; asynchronous on `stream`. */
+size_t dppo_sample_scratch_bytes(int64_t n, int k);
+int dppo_sample_indices(uint32_t* mt_state624, int* mt_index, int64_t n, int k, int rounds, int32_t* out,
+                        void* scratch, size_t scratch_bytes, void* stream);
+
 /* ---- bench utility: FP32 FMA throughput probe (no reference counterpart) ---
  * Launches 8 CTAs per SM of dependent-chain FMAs; *flops_host = FLOPs issued. */
 int dppo_fp32_probe(int iters, float* out, double* flops_host, void* stream);

@@ -136,6 +136,12 @@ class UpdateEngine:
         nv.sample_indices(T, self.B, self.E, rng=rng, out=self.idx_host)
         return self.idx_host
 
+    def draw_indices_device(self, T, sampler, out=None):
+        """The same E x B positions drawn ON THE DEVICE (b200_native.DeviceSampler: CPython's random.sample with the
+        Mersenne Twister state in device memory), written straight into the index block K2 reads: nothing crosses
+        PCIe."""
+        sampler.sample(T, self.B, self.E, out=self.idx_dev if out is None else out)
+
     def _wait_idx_upload(self):
         """The pinned index block is uploaded asynchronously; it may only be rewritten once that upload has run
         (a loop of draw_indices / run_epochs without a synchronise in between would otherwise train on a mixture
@@ -270,7 +276,7 @@ class UpdateEngine:
         return self.loss_host, h2d, self.loss_host.numel() * 4
 
 
-    def update_stream(self, hosts, devs, n_steps, obs_stats=None, rng=random, gshared=None, on_step=None):
+    def update_stream(self, hosts, devs, n_steps, obs_stats=None, rng=random, gshared=None, on_step=None, sampler=None):
         """``n_steps`` consecutive outer iterations from HOST rollouts, software-pipelined the way a training
         loop would run them: a copy stream uploads rollout i+1 (pinned ``hosts[(i+1) % len(hosts)]`` ->
         ``devs[(i+1) % 2]``) while the compute stream runs K4, K1 and the E epochs of rollout i, and the host
@@ -346,6 +352,73 @@ class UpdateEngine:
         self.idx_host, self._idx_next = blocks[cur], blocks[1 - cur]
         main.synchronize()
         return losses, h2d + self.idx_host.numel() * 4 + self.scalars_host.numel() * 4, self.E * 16
+
+
+    def _stream_fields(self, obs_stats):
+        fields = ["act", "rew", "val", "boot", "seg_end"] + (["raw_obs"] if obs_stats is not None else ["obs"])
+        if self.flavour == nv.FLAVOUR_PPO:
+            fields.append("logp")
+        return fields
+
+
+def _update_stream_device_sampler(self, hosts, devs, n_steps, obs_stats, gshared, on_step, sampler):
+    fields = self._stream_fields(obs_stats)
+    main = torch.cuda.current_stream()
+    if not hasattr(self, "_copy_stream"):
+        self._copy_stream = torch.cuda.Stream()
+        self._loss_ring = [torch.zeros(self.E, 4, pin_memory=True) for _ in range(4)]
+    if not hasattr(self, "_sample_stream"):
+        self._sample_stream = torch.cuda.Stream()
+        self._idx_next_dev = torch.zeros_like(self.idx_dev)
+    cs, ss = self._copy_stream, self._sample_stream
+    copied = [torch.cuda.Event(), torch.cuda.Event()]
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+    cs.wait_stream(main)
+    ss.wait_stream(main)
+    with torch.cuda.stream(cs):
+        h2d = devs[0].copy_from(hosts[0], fields)
+        copied[0].record(cs)
+    T = devs[0].T
+    drawn, taken = torch.cuda.Event(), torch.cuda.Event()
+    with torch.cuda.stream(ss):
+        self.draw_indices_device(T, sampler, out=self._idx_next_dev)
+        drawn.record(ss)
+    losses = []
+    for i in range(n_steps):
+        b = i & 1
+        main.wait_event(copied[b])
+        main.wait_event(drawn)
+        self.idx_dev.copy_(self._idx_next_dev)                    # device to device, 4*E*B bytes
+        taken.record(main)
+        if i + 1 < n_steps:
+            with torch.cuda.stream(ss):                           # next step's positions while this step computes
+                ss.wait_event(taken)
+                self.draw_indices_device(T, sampler, out=self._idx_next_dev)
+                drawn = torch.cuda.Event()
+                drawn.record(ss)
+        self._stage_scalars()
+        small_done = torch.cuda.Event()
+        small_done.record(main)
+        self.run_epochs(devs[b], gshared=gshared, use_graph=True, indices_staged=True, obs_stats=obs_stats,
+                        with_gae=True, scalars_staged=True)
+        consumed[b].record(main)
+        if i + 1 < n_steps:
+            with torch.cuda.stream(cs):
+                cs.wait_event(small_done)
+                if i >= 1:
+                    cs.wait_event(consumed[1 - b])
+                devs[1 - b].copy_from(hosts[(i + 1) % len(hosts)], fields)
+                copied[1 - b].record(cs)
+        out = self._loss_ring[i % len(self._loss_ring)]
+        out.copy_(self.loss_out, non_blocking=True)
+        losses.append(out)
+        if on_step is not None:
+            on_step(i)
+    main.synchronize()
+    return losses, h2d + self.scalars_host.numel() * 4, self.E * 16
+
+
+UpdateEngine._update_stream_device_sampler = _update_stream_device_sampler
 
 
 # ---- checkpoint / resume (the reference has none: SURVEY section 5; "next" row N4) --------------------

@@ -84,6 +84,8 @@ def _load():
                                                dbl, dbl, dbl, dbl, c.POINTER(vp), vp]),
         "dppo_reduce_partials": (i32, [vp, i32, vp, i32, vp]),
         "dppo_sample_indices_host": (i32, [c.POINTER(c.c_uint32), c.POINTER(i32), i64, i32, i32, c.POINTER(c.c_int32)]),
+        "dppo_sample_scratch_bytes": (sz, [i64, i32]),
+        "dppo_sample_indices": (i32, [vp, vp, i64, i32, i32, vp, vp, sz, vp]),
         "dppo_fp32_probe": (i32, [i32, vp, c.POINTER(dbl), vp]),
         "dppo_adam_scalars_host": (i32, [i32, dbl, dbl, dbl, dbl, c.POINTER(flt)]),
         "dppo_reduce_adam": (i32, [vp, i32, vp, vp, vp, vp, vp, i32, i32, dbl, dbl, dbl, dbl, vp, dbl, vp, vp, vp, vp, sz, vp]),
@@ -264,6 +266,45 @@ def sample_indices(n, k, rounds=1, rng=None, out=None):
                                        ctypes.cast(out.data_ptr(), ctypes.POINTER(ctypes.c_int32))))
     rng.setstate((ver, tuple(state) + (index.value,), gauss))
     return out
+
+
+class DeviceSampler:
+    """``random.sample`` on the GPU: the generator state of a Python ``random.Random`` (or of the ``random`` module)
+    is uploaded once; every ``sample`` call writes ``rounds`` x k positions into a device tensor and advances the
+    state on the device exactly as Python would have.  ``sync_to(rng)`` stores the state back into a Python generator."""
+
+    def __init__(self, rng=None, device=None):
+        import random as _random
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.state = torch.zeros(624, dtype=torch.int32, device=self.device)     # uint32 words
+        self.index = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._scratch = None
+        self.seed_from(_random if rng is None else rng)
+
+    def seed_from(self, rng):
+        ver, internal, gauss = rng.getstate()
+        words = torch.tensor([w - (1 << 32) if w >= (1 << 31) else w for w in internal[:624]], dtype=torch.int32)
+        self.state.copy_(words)
+        self.index.fill_(internal[624])
+
+    def sync_to(self, rng):
+        ver, internal, gauss = rng.getstate()
+        words = [int(w) & 0xffffffff for w in self.state.cpu().tolist()]
+        rng.setstate((ver, tuple(words) + (int(self.index.item()),), gauss))
+
+    def sample(self, n, k, rounds=1, out=None):
+        if out is None:
+            out = torch.empty(rounds, k, dtype=torch.int32, device=self.device)
+        if out.dtype != torch.int32 or not out.is_contiguous() or out.numel() < rounds * k or not out.is_cuda:
+            raise DppoError("DeviceSampler.sample: out must be a contiguous int32 CUDA tensor of rounds*k elements")
+        if k > n or n < 1:
+            raise DppoError("DeviceSampler.sample: need 1 <= n and k <= n")
+        need = lib.dppo_sample_scratch_bytes(n, k)
+        if self._scratch is None or self._scratch.numel() < need:
+            self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+        check(lib.dppo_sample_indices(self.state.data_ptr(), self.index.data_ptr(), n, k, rounds, out.data_ptr(),
+                                      self._scratch.data_ptr(), self._scratch.numel(), _stream()))
+        return out
 
 
 def fp32_probe(iters=4096):

@@ -384,3 +384,31 @@ def test_engine_vs_oracle_c4_shape_full_cycle():
         assert_close_scaled(got[o:o + n], p[k].reshape(-1), 1e-5, "theta[%s] (C4)" % k)
         o += n
     assert_close_scaled(unpadded(eng.m, m.offsets, m.sizes), orc.flatten(mo), 1e-5, "Adam m (C4)")
+
+
+def test_update_stream_with_device_sampler_equals_host_sampler():
+    """Minibatch positions drawn on the GPU (DeviceSampler, one step ahead on a side stream) give bit-identical
+    training to positions drawn by the host sampler from the same random.Random stream."""
+    import b200_native as nv
+    from b200_engine import RolloutBuffer, UpdateEngine
+    from model import Model, Shared_obs_stats
+    from synthetic import make_rollout
+    T, B, E, n = 4096, 512, 3, 6
+    res = []
+    for mode in ("host", "device"):
+        torch.manual_seed(1)
+        m = Model(17, 6, device=DEV)
+        stats = Shared_obs_stats(17)
+        hosts = [make_rollout(m, stats, T, seed=40 + i, flavour=nv.FLAVOUR_DPPO, seg_len=500)[0] for i in range(3)]
+        devs = [RolloutBuffer(T, 17, 6, DEV), RolloutBuffer(T, 17, 6, DEV)]
+        eng = UpdateEngine(m, nv.FLAVOUR_DPPO, B, E, 3e-4)
+        rng = random.Random(4)
+        if mode == "host":
+            losses, h2d_host, _ = eng.update_stream(hosts, devs, n, obs_stats=stats, rng=rng)
+        else:
+            losses, h2d_dev, _ = eng.update_stream(hosts, devs, n, obs_stats=stats, sampler=nv.DeviceSampler(rng))
+        torch.cuda.synchronize()
+        res.append((m.flat.clone(), eng.m.clone(), losses[-1].clone()))
+    assert h2d_dev == h2d_host - E * B * 4                      # the index block no longer crosses PCIe
+    for a, b in zip(res[0], res[1]):
+        assert torch.equal(a, b)
