@@ -363,15 +363,20 @@ def main():
     devbuf2 = RolloutBuffer(wl["T"], wl["O"], wl["A"], dev)
     devs2 = [devbuf, devbuf2]
     reset_stats()
-    sampler = None if args.host_sampler else nv.DeviceSampler(rng)       # random.sample on the GPU, same stream of positions
-    engine.update_stream([host], devs2, 3, obs_stats=stats, rng=rng, gshared=gsh, on_step=None, sampler=sampler)
+    # random.sample on the GPU (same stream of positions) where CPython's algorithm parallelises: its set branch
+    # (population larger than ~4x the sample, C4/C5).  Its pool branch (C1-C3: a permutation of the whole buffer) is a
+    # sequential swap chain - one GPU thread is slower at that than a host core - so those configs keep the host
+    # sampler (a worker thread one step ahead, 4*E*B bytes uploaded per step).
+    use_dev_sampler = not args.host_sampler and not nv.sample_uses_pool(wl["T"], wl["B"])
+    idx_sampler = nv.DeviceSampler(rng) if use_dev_sampler else None
+    engine.update_stream([host], devs2, 3, obs_stats=stats, rng=rng, gshared=gsh, on_step=None, sampler=idx_sampler)
     barrier()
     n_e2e = max(3, min(args.steps, 100))
     keep_n = max(1, (1 << 23) // wl["T"] // max(world, 1))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     reset_stats()
     e0.record()
-    _, h2d, d2h = engine.update_stream([host], devs2, n_e2e, obs_stats=stats, rng=rng, gshared=gsh, sampler=sampler,
+    _, h2d, d2h = engine.update_stream([host], devs2, n_e2e, obs_stats=stats, rng=rng, gshared=gsh, sampler=idx_sampler,
                                        on_step=lambda i: reset_stats() if i % keep_n == keep_n - 1 else None)
     e1.record()
     barrier()
@@ -448,7 +453,7 @@ def main():
            "dtype": "f32", "data": "synthetic", "config": config_dict(wl, world), "clocks": sampler.summary(),
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                    "ms_per_step": e2e_ms / n_e2e, "steps": n_e2e,
-                   "index_sampler": "host (C restatement of random.sample, worker thread, uploaded per step)" if args.host_sampler
+                   "index_sampler": "host (C restatement of random.sample, worker thread, uploaded per step)" if idx_sampler is None
                    else "device (dppo_sample_indices: random.sample on the GPU, no index upload)"},
            "gpu_launches": launches_per_step * args.steps, "roofline": roofline, "parity": parity,
            "update_latency_us": step_us, "graph": use_graph, "comm": None if comm is None else comm.describe()}

@@ -281,8 +281,12 @@ class UpdateEngine:
         loop would run them: a copy stream uploads rollout i+1 (pinned ``hosts[(i+1) % len(hosts)]`` ->
         ``devs[(i+1) % 2]``) while the compute stream runs K4, K1 and the E epochs of rollout i, and the host
         draws the next minibatch positions meanwhile.  Every step still copies its own inputs H2D and its
-        per-epoch losses D2H.  Returns (list of per-step loss tensors on the host, h2d bytes/step, d2h bytes/step)."""
+        per-epoch losses D2H.  With ``sampler`` (a b200_native.DeviceSampler) the minibatch positions are drawn on the
+        GPU instead - on a side stream, one step ahead - and no index block is uploaded.
+        Returns (list of per-step loss tensors on the host, h2d bytes/step, d2h bytes/step)."""
         assert len(devs) == 2
+        if sampler is not None:
+            return self._update_stream_device_sampler(hosts, devs, n_steps, obs_stats, gshared, on_step, sampler)
         fields = ["act", "rew", "val", "boot", "seg_end"] + (["raw_obs"] if obs_stats is not None else ["obs"])
         if self.flavour == nv.FLAVOUR_PPO:
             fields.append("logp")

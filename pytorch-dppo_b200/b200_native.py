@@ -268,6 +268,15 @@ def sample_indices(n, k, rounds=1, rng=None, out=None):
     return out
 
 
+def sample_uses_pool(n, k):
+    """True when CPython's random.sample(population of n, k) takes its pool branch (n <= setsize, Lib/random.py)."""
+    import math
+    setsize = 21
+    if k > 5:
+        setsize += 4 ** math.ceil(math.log(k * 3, 4))
+    return n <= setsize
+
+
 class DeviceSampler:
     """``random.sample`` on the GPU: the generator state of a Python ``random.Random`` (or of the ``random`` module)
     is uploaded once; every ``sample`` call writes ``rounds`` x k positions into a device tensor and advances the
