@@ -143,6 +143,19 @@ int dppo_update_fused(int flavour, const dppo_dims* d,
                       const float* theta, const float* theta_old,
                       float clip, float ent_coeff,
                       float* partials, float* loss_partials, void* stream);
+/* ---- the rollout's forward: batched Model.forward + action sampling ------------------------------------------
+ * Replaces, for N environments stepped together, the per-step block of the rollout loop train.py:84-90 /
+ * ppo.py:90-98 after the observation has been normalised (K4): ``mu, sigma_sq, v = model(state)``,
+ * ``action = mu + sigma_sq.sqrt()*eps`` (train.py:89; std_is_variance != 0) or ``mu + sigma_sq*eps`` (ppo.py:93), and
+ * the log-probability ppo.py:95-98.  Same kernel and layer routines as dppo_update_fused, forward only.
+ *   states[N*O] normalised observations, eps[N*A] standard-normal draws (NULL: action = mu)
+ *   outputs (each nullable, at least one given): mu_out[.*A], v_out[.], act_out[.*A], logp_out[.], states_out[.*O];
+ *   batch row r is written to row  out_row0 + r*out_row_stride  of every output - with the columns of a rollout
+ *   buffer, stride = steps per environment and row0 = the step, the rows land where K1/K2 read them. */
+int dppo_policy_forward(const dppo_dims* d, const float* states, int N, const float* theta, const float* eps,
+                        int std_is_variance, float* mu_out, float* v_out, float* act_out, float* logp_out,
+                        float* states_out, int64_t out_row0, int64_t out_row_stride, void* stream);
+
 /* Which layer routines dppo_update_fused uses: DPPO_K2_PATH_AUTO (default) puts every eligible layer on the
  * tensor cores (tcgen05, 3xTF32) and the rest on the FP32 pipe; DPPO_K2_PATH_FP32 forces the FP32-pipe
  * routines for all layers (A/B runs, tests).  Process-wide; the environment variable DPPO_K2_NO_TS=1, read

@@ -69,6 +69,7 @@ def _load():
         "dppo_update_nparts": (i32, [dp, i32]),
         "dppo_update_partials_bytes": (sz, [dp, i32]),
         "dppo_update_fused": (i32, [i32, dp, vp, vp, vp, vp, vp, vp, i32, vp, vp, flt, flt, vp, vp, vp]),
+        "dppo_policy_forward": (i32, [dp, vp, i32, vp, vp, i32, vp, vp, vp, vp, vp, i64, i64, vp]),
         "dppo_reduce_adam_scratch_bytes": (sz, [i32]),
         "dppo_comm_create": (i32, [i32, i32, i32, c.POINTER(vp)]),
         "dppo_comm_handle_bytes": (i32, []),
@@ -210,6 +211,17 @@ def update_fused(flavour, dims, obs, act, adv, ret, logp_old, idx, theta, theta_
                                 _ptr(logp_old, allow_none=True), _ptr(idx, torch.int32), idx.numel(), _ptr(theta),
                                 _ptr(theta_old, allow_none=True), clip, ent_coeff, _ptr(partials), _ptr(loss_partials),
                                 _stream()))
+
+
+def policy_forward(dims, theta, states, eps=None, std_is_variance=True, mu=None, v=None, act=None, logp=None,
+                   states_out=None, row0=0, row_stride=1):
+    """Batched Model.forward + action sampling of N states (train.py:84-90 / ppo.py:90-98); batch row r goes to row
+    ``row0 + r*row_stride`` of every output given."""
+    N = states.shape[0]
+    check(lib.dppo_policy_forward(ctypes.byref(dims), _ptr(states), N, _ptr(theta), _ptr(eps, allow_none=True),
+                                  1 if std_is_variance else 0, _ptr(mu, allow_none=True), _ptr(v, allow_none=True),
+                                  _ptr(act, allow_none=True), _ptr(logp, allow_none=True),
+                                  _ptr(states_out, allow_none=True), row0, row_stride, _stream()))
 
 
 K2_PATH_AUTO, K2_PATH_FP32 = 0, 1

@@ -116,6 +116,11 @@ struct UpdArgs {
     int first_ts;                                   // ... and on the tensor cores (small_first, room for the sample tiles)
     int small_first;                                // first layers (K = O <= 32) run from prefetched flat weight copies
     int trunk_serial;                               // policy trunk start to end, then the value trunk, in the same activation buffers
+    // forward-only mode (dppo_policy_forward: the rollout's batched Model.forward + action sampling, train.py:84-90)
+    int fwd_only, std_is_variance;
+    const float* eps;                               // [B][A] standard-normal draws (nullable: action = mu)
+    float *f_mu, *f_v, *f_act, *f_logp, *f_obs;     // output columns (nullable), row r of the batch lands in row
+    long long f_row0, f_stride;                     //   f_row0 + r * f_stride  (straight into the SoA rollout buffer)
     alignas(64) CUtensorMap map_fwd[2][4];          // [theta, theta_old][W2, V2, W1, V1]: box 32 (k) x 128 (n), SWIZZLE_128B
     alignas(64) CUtensorMap map_dx[2];              // theta's W2, V2 for dX: box 128 (k) x 32 (n), no swizzle
 };
@@ -1654,7 +1659,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
             hs_old.Wmu = no.Wmu; hs_old.bmu = no.bmu; hs_old.Wv = no.Wv; hs_old.bv = no.bv; hs_old.ldw = d.H2;
         }
     }
-    if (threadIdx.x < DPPO_N_PARAMS)                                   // padding floats of the bucket stay 0
+    if (threadIdx.x < DPPO_N_PARAMS && !P.fwd_only)                    // padding floats of the bucket stay 0
         for (int j = P.lay.size[threadIdx.x]; j < ((P.lay.size[threadIdx.x] + 3) & ~3); ++j)
             part[P.lay.off[threadIdx.x] + j] = 0.f;
     float lsum_clip = 0.f, lsum_val = 0.f, lsum_ent = 0.f;           // this thread's share of the loss sums
@@ -1675,13 +1680,14 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         __syncthreads();
         for (int e = threadIdx.x; e < valid * d.O; e += UPD_THREADS) {
             const int m = e / d.O, k = e - m * d.O;
-            S[P.o_x + m * P.ldO + k] = __ldg(P.obs + (size_t)__ldg(P.idx + b0 + m) * d.O + k);
+            const size_t r = P.idx ? (size_t)__ldg(P.idx + b0 + m) : (size_t)(b0 + m);
+            S[P.o_x + m * P.ldO + k] = __ldg(P.obs + r * d.O + k);
         }
-        for (int e = threadIdx.x; e < valid * d.A; e += UPD_THREADS) {
+        for (int e = threadIdx.x; e < valid * d.A && !P.fwd_only; e += UPD_THREADS) {
             const int m = e / d.A, a = e - m * d.A;
             S[P.o_act + m * d.A + a] = __ldg(P.act + (size_t)__ldg(P.idx + b0 + m) * d.A + a);
         }
-        for (int m = threadIdx.x; m < valid; m += UPD_THREADS) {
+        for (int m = threadIdx.x; m < valid && !P.fwd_only; m += UPD_THREADS) {
             const size_t r = (size_t)__ldg(P.idx + b0 + m);
             S[P.o_adv + m] = __ldg(P.adv + r);
             S[P.o_ret + m] = __ldg(P.ret + r);
@@ -1845,6 +1851,42 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
                 dw_layer(gW, gb, N, K, dOut, ldd, in, ldin, acc);
         };
 
+        // forward-only mode: mu, v, the sampled action and its log-probability of this tile's rows, then the next tile
+        auto write_policy_outputs = [&]() {
+            const float half_log_2pi = 0.918938533204672742f;
+            for (int e = threadIdx.x; e < valid * d.A; e += UPD_THREADS) {
+                const int m = e / d.A, a = e - m * d.A;
+                const size_t r = (size_t)(P.f_row0 + (long long)(b0 + m) * P.f_stride);
+                const float mu = S[P.o_mu + m * P.ldA + a];
+                const float s = expf(__ldg(nw.ls + a));                              // sigma_sq = exp(log_std), model.py:40
+                const float sd = P.std_is_variance ? sqrtf(s) : s;                   // train.py:89 / ppo.py:93
+                const float act = P.eps ? mu + sd * __ldg(P.eps + (size_t)(b0 + m) * d.A + a) : mu;
+                S[P.o_dmu + m * P.ldA + a] = act;
+                if (P.f_mu) P.f_mu[r * d.A + a] = mu;
+                if (P.f_act) P.f_act[r * d.A + a] = act;
+            }
+            for (int e = threadIdx.x; e < valid * d.O && P.f_obs != nullptr; e += UPD_THREADS) {
+                const int m = e / d.O, k = e - m * d.O;
+                P.f_obs[(size_t)(P.f_row0 + (long long)(b0 + m) * P.f_stride) * d.O + k] = S[P.o_x + m * P.ldO + k];
+            }
+            __syncthreads();
+            for (int m = threadIdx.x; m < valid; m += UPD_THREADS) {
+                const size_t r = (size_t)(P.f_row0 + (long long)(b0 + m) * P.f_stride);
+                if (P.f_v) P.f_v[r] = S[P.o_v + m];
+                if (P.f_logp) {                                                       // ppo.py:95-98 (sigma_sq used as the std)
+                    float lp = 0.f;
+                    for (int a = 0; a < d.A; ++a) {
+                        const float ls = __ldg(nw.ls + a);
+                        const float zz = (S[P.o_dmu + m * P.ldA + a] - S[P.o_mu + m * P.ldA + a]) / expf(ls);
+                        const float t = (-0.5f * (zz * zz) - half_log_2pi) - ls;
+                        lp = (a == 0) ? t : lp + t;
+                    }
+                    P.f_logp[r] = lp;
+                }
+            }
+            __syncthreads();
+        };
+
         if (P.trunk_serial) {
             // ---- wide nets: one trunk from its forward passes to its last gradient, then the other, in the same
             // activation buffers a1 (first hidden layer) and a2 (second hidden layer) --------------------------------
@@ -1860,6 +1902,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
                 if (run_old)
                     ph = trunk_forward(no, hs_old, P, S, trunk, S + P.o_muo, S + P.o_vo, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr);
                 ph = trunk_forward(nw, hs_new, P, S, trunk, S + P.o_mu, S + P.o_v, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr);
+                if (P.fwd_only) continue;
                 if (same_old) {
                     if (trunk == 0) for (int e = threadIdx.x; e < UPD_ROWS * P.ldA; e += UPD_THREADS) S[P.o_muo + e] = S[P.o_mu + e];
                     else for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
@@ -1882,6 +1925,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
                               P.use_ts ? &P.map_dx[trunk] : nullptr, tmem);                                   // a1 <- dz1
                 dw_any(trunk ? go.V1 : go.W1, trunk ? go.c1 : go.b1, N1, d.O, a1, ld1, S + P.o_x, P.ldO);
             }
+            if (P.fwd_only) write_policy_outputs();
             continue;
         }
 
@@ -1891,6 +1935,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         if (run_old)
             ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr, &nw);              // train.py:142
         ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr, nullptr);                    // train.py:145 / ppo.py:148
+        if (P.fwd_only) { write_policy_outputs(); continue; }
         if (same_old) {
             for (int e = threadIdx.x; e < UPD_ROWS * P.ldA; e += UPD_THREADS) S[P.o_muo + e] = S[P.o_mu + e];
             for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
@@ -1942,7 +1987,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
     const float sc = block_sum(lsum_clip, red);
     const float sv = block_sum(lsum_val, red);
     const float se = block_sum(lsum_ent, red);
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0 && !P.fwd_only) {
         float* lp = P.loss_partials + 4 * blockIdx.x;
         if (P.flavour == DPPO_FLAVOUR_DPPO) {
             const float BA = (float)P.B * (float)d.A;
@@ -2204,36 +2249,22 @@ extern "C" size_t dppo_update_partials_bytes(const dppo_dims* d, int B) {
     return sizeof(float) * (size_t)np * L.P_pad;
 }
 
-extern "C" int dppo_update_fused(int flavour, const dppo_dims* d, const float* obs, const float* act, const float* adv,
-                                 const float* ret, const float* logp_old, const int32_t* idx, int B, const float* theta,
-                                 const float* theta_old, float clip, float ent_coeff, float* partials,
-                                 float* loss_partials, void* stream_) {
-    int rc = check_dims(d);
-    if (rc) return rc;
-    if (flavour != DPPO_FLAVOUR_DPPO && flavour != DPPO_FLAVOUR_PPO) return DPPO_E_BADARG;
-    if (B < 1 || !obs || !act || !adv || !ret || !idx || !theta || !partials || !loss_partials) return DPPO_E_BADARG;
-    if (flavour == DPPO_FLAVOUR_DPPO && !theta_old) return DPPO_E_BADARG;
-    if (flavour == DPPO_FLAVOUR_PPO && !logp_old) return DPPO_E_BADARG;
-    if (!aligned16(theta) || !aligned16(theta_old) || !aligned16(partials)) return DPPO_E_ALIGN;
-    UpdArgs P;
-    P.flavour = flavour;
-    P.d = *d;
+// shared tail of the two entry points: tiling, shared-memory plan, tensor maps, launch
+static int plan_and_launch(UpdArgs& P, const dppo_dims* d, int B, const float* theta, const float* theta_old, void* stream_) {
     fill_layout(*d, P.lay);
-    P.obs = obs; P.act = act; P.adv = adv; P.ret = ret; P.logp_old = logp_old; P.idx = idx;
+    P.d = *d;
     P.B = B;
     int nparts;
     pick_tiling(B, &P.TM, &nparts);
     P.ntiles = (B + P.TM - 1) / P.TM;
     P.theta = theta; P.theta_old = theta_old;
-    P.clip = clip; P.ent_coeff = ent_coeff;
-    P.partials = partials; P.loss_partials = loss_partials;
     plan(P);
     const size_t smem = sizeof(float) * (size_t)P.smem_floats;
     if (smem > 227 * 1024 || P.SF < UPD_STAGE_MIN) return DPPO_E_TOOLARGE;
-    // tensor-core path of the wide layers: needs the 100 KB staging region and tensor maps of the weights
     int dev = 0;
     DPPO_CUDA_TRY(cudaGetDevice(&dev));
     if (dev < 0 || dev >= MAX_DEVICES) return DPPO_E_BADARG;
+    // tensor-core path of the wide layers: needs the 100 KB staging region and tensor maps of the weights
     P.use_ts = 0;
     if ((size_t)2 * P.SF * sizeof(float) >= (size_t)TS_BYTES && k2_path() == DPPO_K2_PATH_AUTO) {
         const MapEntry* e = wide_layer_maps(dev, theta, theta_old, *d, P.lay);
@@ -2251,6 +2282,48 @@ extern "C" int dppo_update_fused(int flavour, const dppo_dims* d, const float* o
     update_fused_kernel<<<nparts, UPD_THREADS, smem, (cudaStream_t)stream_>>>(P);
     DPPO_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int dppo_update_fused(int flavour, const dppo_dims* d, const float* obs, const float* act, const float* adv,
+                                 const float* ret, const float* logp_old, const int32_t* idx, int B, const float* theta,
+                                 const float* theta_old, float clip, float ent_coeff, float* partials,
+                                 float* loss_partials, void* stream_) {
+    int rc = check_dims(d);
+    if (rc) return rc;
+    if (flavour != DPPO_FLAVOUR_DPPO && flavour != DPPO_FLAVOUR_PPO) return DPPO_E_BADARG;
+    if (B < 1 || !obs || !act || !adv || !ret || !idx || !theta || !partials || !loss_partials) return DPPO_E_BADARG;
+    if (flavour == DPPO_FLAVOUR_DPPO && !theta_old) return DPPO_E_BADARG;
+    if (flavour == DPPO_FLAVOUR_PPO && !logp_old) return DPPO_E_BADARG;
+    if (!aligned16(theta) || !aligned16(theta_old) || !aligned16(partials)) return DPPO_E_ALIGN;
+    UpdArgs P;
+    memset(&P, 0, sizeof(P));
+    P.flavour = flavour;
+    P.obs = obs; P.act = act; P.adv = adv; P.ret = ret; P.logp_old = logp_old; P.idx = idx;
+    P.clip = clip; P.ent_coeff = ent_coeff;
+    P.partials = partials; P.loss_partials = loss_partials;
+    return plan_and_launch(P, d, B, theta, theta_old, stream_);
+}
+
+// Forward-only use of the same kernel: the tile's gather and net_forward, then mu / v / action / log-prob instead of
+// the loss and the backward pass.
+extern "C" int dppo_policy_forward(const dppo_dims* d, const float* states, int N, const float* theta, const float* eps,
+                                   int std_is_variance, float* mu_out, float* v_out, float* act_out, float* logp_out,
+                                   float* states_out, int64_t out_row0, int64_t out_row_stride, void* stream_) {
+    int rc = check_dims(d);
+    if (rc) return rc;
+    if (N < 1 || !states || !theta || out_row0 < 0 || out_row_stride < 1) return DPPO_E_BADARG;
+    if (!mu_out && !v_out && !act_out && !logp_out) return DPPO_E_BADARG;
+    if (!aligned16(theta)) return DPPO_E_ALIGN;
+    UpdArgs P;
+    memset(&P, 0, sizeof(P));
+    P.flavour = DPPO_FLAVOUR_PPO;                               // one network, no lagging copy
+    P.obs = states;
+    P.fwd_only = 1;
+    P.std_is_variance = std_is_variance ? 1 : 0;
+    P.eps = eps;
+    P.f_mu = mu_out; P.f_v = v_out; P.f_act = act_out; P.f_logp = logp_out; P.f_obs = states_out;
+    P.f_row0 = out_row0; P.f_stride = out_row_stride;
+    return plan_and_launch(P, d, N, theta, nullptr, stream_);
 }
 
 #ifdef DPPO_K2_TRACE

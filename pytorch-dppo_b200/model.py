@@ -85,6 +85,23 @@ class Model(nn.Module):
         x = torch.tanh(self.v_fc2(x))
         return mu, sigma_sq, self.v(x)
 
+    def act(self, states, eps=None, std_is_variance=True, mu=None, v=None, act=None, logp=None, states_out=None,
+            row0=0, row_stride=1):
+        """The rollout's forward for a BATCH of normalised states on the update path's own kernel (no autograd, no
+        cuBLAS): mu, v, ``action = mu + std*eps`` and its log-probability (train.py:87-90 / ppo.py:91-98).  Outputs
+        that are given are filled in place (row r of the batch -> row ``row0 + r*row_stride``); returns (mu, v, act,
+        logp) tensors of the batch when none is given."""
+        states = states.reshape(-1, self.dims.O).contiguous()
+        N = states.shape[0]
+        own = mu is None and v is None and act is None and logp is None
+        if own:
+            mu = torch.empty(N, self.dims.A, device=self.flat.device)
+            act = torch.empty(N, self.dims.A, device=self.flat.device)
+            v = torch.empty(N, device=self.flat.device)
+            logp = torch.empty(N, device=self.flat.device)
+        nv.policy_forward(self.dims, self.flat, states, eps, std_is_variance, mu, v, act, logp, states_out, row0, row_stride)
+        return (mu, v, act, logp) if own else None
+
     @property
     def device(self):
         return self.flat.device

@@ -135,6 +135,70 @@ def collect_rollout(env, model, shared_obs_stats, params, state, episode_length,
     return buf, state, episode_length
 
 
+def collect_rollout_vec(envs, model, shared_obs_stats, params, states, episode_lengths, std_is_variance=True, out=None,
+                        eps_fn=None):
+    """The rollout phase of train.py:69-124 for N environments stepped together.  Per step ONE
+    K4 launch feeds the N raw observations to the shared statistics in environment order and normalises them
+    (model.py:68-80), and ONE launch of the update path's forward kernel (Model.act) computes mu, v, the action
+    ``mu + std*eps`` and its log-probability for all N and writes them straight into the SoA rollout buffer - nothing of
+    the per-step arithmetic runs through torch eager.  Only the N actions go back to the host for ``env.step``.
+
+    Environment e owns rows [e*L, (e+1)*L) of the buffer (L = exploration_size / N steps each): its trajectory is
+    contiguous, a segment ends where the episode ends (bootstrap 0) or at row (e+1)*L - 1 (bootstrap V of the raw next
+    state, train.py:109-112).  ``states``: list of the N current raw observations; returns (buffer, states, lengths)."""
+    dev = model.device
+    N, O, A = len(envs), model.dims.O, model.dims.A
+    T = params.exploration_size
+    if T % N:
+        raise nv.DppoError("collect_rollout_vec: exploration_size (%d) must be a multiple of the number of environments (%d)" % (T, N))
+    L = T // N
+    buf = out if out is not None else RolloutBuffer(T, O, A, dev)
+    if buf.T != T:
+        raise nv.DppoError("collect_rollout_vec: out holds %d steps, the rollout has %d" % (buf.T, T))
+    raw_host = torch.empty(N, O, pin_memory=True)
+    raw_dev, norm_dev = torch.empty(N, O, device=dev), torch.empty(N, O, device=dev)
+    act_dev = torch.empty(N, A, device=dev)
+    act_host = torch.empty(N, A, pin_memory=True)
+    rew = torch.zeros(T)
+    seg_end = torch.zeros(T, dtype=torch.uint8)
+    boot = torch.zeros(T)
+    for t in range(L):
+        for e in range(N):
+            raw_host[e] = torch.as_tensor(np.asarray(states[e]), dtype=torch.float32).reshape(-1)
+        raw_dev.copy_(raw_host, non_blocking=True)
+        shared_obs_stats.observes_batch(raw_dev, out=norm_dev)                      # train.py:84-85 for N rows
+        eps = eps_fn(t) if eps_fn is not None else torch.randn(N, A, device=dev)
+        model.act(norm_dev, eps, std_is_variance, v=buf.val, act=buf.act, logp=buf.logp, states_out=buf.obs,
+                  row0=t, row_stride=L)                                             # train.py:87-90, rows e*L + t
+        act_dev.copy_(buf.act.view(N, L, A)[:, t])
+        act_host.copy_(act_dev)                                                     # synchronises: the host needs the actions
+        for e in range(N):
+            nxt, reward, done, _ = envs[e].step(act_host[e].numpy())
+            episode_lengths[e] += 1
+            done = bool(done or episode_lengths[e] >= params.max_episode_length)
+            row = e * L + t
+            rew[row] = max(min(float(reward), 1.0), -1.0)                           # train.py:96
+            if done:
+                seg_end[row] = 1
+                episode_lengths[e] = 0
+                nxt = envs[e].reset()
+            states[e] = nxt
+    # bootstrap of the open segments: V of the RAW next state (train.py:110-112), one more batched forward
+    for e in range(N):
+        raw_host[e] = torch.as_tensor(np.asarray(states[e]), dtype=torch.float32).reshape(-1)
+    raw_dev.copy_(raw_host)
+    v_next = torch.empty(N, device=dev)
+    model.act(raw_dev, None, std_is_variance, v=v_next)
+    v_next = v_next.cpu()
+    for e in range(N):
+        row = (e + 1) * L - 1
+        if not seg_end[row]:
+            seg_end[row] = 1
+            boot[row] = v_next[e]
+    buf.rew.copy_(rew); buf.seg_end.copy_(seg_end); buf.boot.copy_(boot)
+    return buf, states, episode_lengths
+
+
 def make_engine(params, model, comm=None):
     return UpdateEngine(model, nv.FLAVOUR_DPPO, params.batch_size, params.num_epoch, params.lr, clip=params.clip,
                         ent_coeff=params.ent_coeff, gamma=params.gamma, gae_param=params.gae_param, comm=comm)
@@ -145,14 +209,23 @@ def train(rank, params, traffic_light, counter, shared_model, shared_grad_buffer
     env = _make_env(params)
     model = shared_model                       # one replica per GPU process; K3 keeps replicas identical
     engine = getattr(params, "engine", None) or make_engine(params, model, getattr(params, "comm", None))
-    state = torch.as_tensor(np.asarray(env.reset()), dtype=torch.float32).unsqueeze(0)
+    num_envs = int(getattr(params, "num_envs", 1))
+    if num_envs > 1:                           # N environments stepped together, forward + statistics batched on the GPU
+        envs = [env] + [_make_env(params) for _ in range(num_envs - 1)]
+        states, lengths = [e.reset() for e in envs], [0] * num_envs
+    else:
+        state = torch.as_tensor(np.asarray(env.reset()), dtype=torch.float32).unsqueeze(0)
     episode_length = 0
     fused = getattr(params, "fused_chief", True)
     outer = 0
     while getattr(params, "max_outer_iters", None) is None or outer < params.max_outer_iters:
         outer += 1
-        buf, state, episode_length = collect_rollout(env, model, shared_obs_stats, params, state, episode_length,
-                                                     out=engine.rollout_buffer(params.exploration_size))
+        if num_envs > 1:
+            buf, states, lengths = collect_rollout_vec(envs, model, shared_obs_stats, params, states, lengths,
+                                                       out=engine.rollout_buffer(params.exploration_size))
+        else:
+            buf, state, episode_length = collect_rollout(env, model, shared_obs_stats, params, state, episode_length,
+                                                         out=engine.rollout_buffer(params.exploration_size))
         engine.gae(buf)                                                      # train.py:108-122
         engine.draw_indices(buf.T)                                           # train.py:140, all epochs
         if fused:
