@@ -20,23 +20,23 @@
 // tile has started and publishes its sums without depending on anything below it (no deadlock whatever
 // the residency).
 //
-// The prefix over the tiles of a column block is DETERMINISTIC: fp64 addition is not associative, so the
-// classic decoupled look-back (which adds whatever mix of aggregates and prefixes it happens to find) would
-// make results depend on timing.  Instead the tiles form a fixed two-level hierarchy - blocks of 16 tiles,
-// super-blocks of 16 blocks - and every tile adds, in a fixed order,
-//     P[a]            the sums of everything before super-block a   (published by the last tile of a-1)
-//   + B[a][0..b-1]    the sums of the blocks before its block       (each published by the block's last tile)
-//   + A[..][0..c-1]   the sums of the tiles before it in its block  (each published by its tile)
-// The only serial chain is P: one link per 256 tiles (~34 links for a 570 MB rollout), far faster than
-// the tiles stream; B needs only the A of its own block.  Every wait is on a flag with acquire/release semantics; at
-// most 31 payloads are read.
+// The prefix over the tiles of a column block is DETERMINISTIC and has NO serial chain.  fp64 addition is not
+// associative, so the classic decoupled look-back (which adds whatever mix of aggregates and prefixes it happens to
+// find) would make results depend on timing; and a chain of inclusive prefixes handed from tile to tile costs an L2
+// round trip per link.  Instead the tiles form a fixed radix-16 hierarchy: level 0 = tiles, level l = groups of 16^l
+// tiles.  The last tile of a group publishes the group's sums (tot[l]) from the 16 sums one level down - that needs
+// nothing from outside the group - and every tile adds, in a fixed order (highest level first),
+//     for each level l:  tot[l][the d_l groups before mine inside my level-(l+1) group]      (d_l = digit l of the
+// tile number in base 16: at most 15 payloads per level, 5 levels cover 10^6 tiles).  Every wait is on a flag with
+// acquire/release semantics and only ever on tiles with smaller ticket numbers, which have started.
 #include "common.cuh"
 
 namespace {
 
 constexpr int WF_THREADS = 256;
 constexpr int WF_CB = 32;                           // widest column block
-constexpr int WF_L1 = 16;                           // tiles per block, blocks per super-block
+constexpr int WF_L1 = 16;                           // radix of the hierarchy
+constexpr int WF_MAX_LEV = 6;                       // 16^6 tiles
 constexpr int WF_MAX_ROWS = 8448;                   // bounds the per-row reciprocal table (256 groups x 33 rows, O = 1)
 
 struct WfGeom {
@@ -44,13 +44,16 @@ struct WfGeom {
     int R, G, RPG;                                  // rows per tile, row groups per tile, rows per group
     int64_t T;
     int ntr;                                        // row tiles; tiles in all = ntr * ncb
-    int nb1, nb2;                                   // blocks / super-blocks per column block
+    int nlev;                                       // levels of the radix-16 hierarchy (level 0 = tiles)
+    int lev_n[WF_MAX_LEV];                          // groups per column block at each level (lev_n[0] = ntr)
+    int lev_off[WF_MAX_LEV];                        // offset of level l in the per-column-block arrays
+    int per_cb;                                     // entries per column block over all levels
 };
 
 struct WfScratch {                                  // carved from the caller's scratch
     int* ticket;
-    int *flagA, *flagB, *flagP;                     // [ncb][ntr], [ncb][nb1], [ncb][nb2+1]
-    double *payA, *payB, *payP;                     // same shapes x [2*CB]
+    int* flag;                                      // [ncb][per_cb]: tot[l][g] of column block cb at cb*per_cb + lev_off[l] + g
+    double* pay;                                    // same shape x [2*CB]
 };
 
 __device__ __forceinline__ void wf_wait_flag(const int* f) {
@@ -123,7 +126,7 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
     }
     __syncthreads();
     // ---- tile sums (fixed order over the groups), exclusive prefix of the groups in place, publish ----
-    const int tix = cb * q.ntr + rt;                                  // this tile in the [ncb][ntr] arrays
+    const size_t cb0 = (size_t)cb * q.per_cb;                         // this column block's slice of flag[] / pay[]
     if (threadIdx.x < cw) {
         const int c = threadIdx.x;
         double r1 = 0.0, r2 = 0.0;
@@ -133,59 +136,54 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
             r1 += x1; r2 += x2;
         }
         s_agg[c] = r1; s_agg[q.CB + c] = r2;
-        __stcg(&w.payA[(size_t)tix * V + c], r1);
-        __stcg(&w.payA[(size_t)tix * V + q.CB + c], r2);
+        __stcg(&w.pay[(cb0 + rt) * V + c], r1);
+        __stcg(&w.pay[(cb0 + rt) * V + q.CB + c], r2);
     }
     __syncthreads();
-    if (threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flagA[tix], 1); }
-    // ---- sums of all rows above this tile: P[a] + B[a][0..b) + A[..][0..c), fixed order ----
-    // Two rounds, so that nothing a LATER tile waits for depends on this tile's own waits more than it must:
-    // round 0 fetches the sums of the tiles before this one in its block (they depend on nothing) - the last tile of
-    // a block then publishes the block sum B at once; round 1 fetches B[a][0..b) and P[a].  Only P is a serial chain
-    // (one link per 256 tiles).
-    const int a = rt / (WF_L1 * WF_L1), b = (rt / WF_L1) % WF_L1, c1 = rt % WF_L1;
-    const int nP = a > 0 ? 1 : 0;
-    const bool pubB = c1 == WF_L1 - 1;                                // last tile of its block
-    const bool pubP = pubB && b == WF_L1 - 1;                         // ... and of its super-block
-    double sA = 0.0, sPB = 0.0;                                       // (threads v < V) tiles before me in my block / P + blocks
-    for (int round = 0; round < 2; ++round) {
-        const int cnt = round == 0 ? c1 : nP + b;                     // payloads of this round (<= 16)
-        if (cnt > 0) {
-            if (threadIdx.x < cnt) {                                  // one thread per flag: the waits overlap
-                const int j = threadIdx.x;
-                const int* f = round == 0 ? &w.flagA[cb * q.ntr + (rt - c1) + j]
-                             : j < nP ? &w.flagP[cb * (q.nb2 + 1) + a]
-                                      : &w.flagB[cb * q.nb1 + (rt / WF_L1 - b) + (j - nP)];
-                wf_wait_flag(f);
-            }
+    if (threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flag[cb0 + rt], 1); }
+    // ---- sums of all rows above this tile, level by level (bottom-up, so that group sums are published as early
+    // as possible); own = the sums of the group this tile completes at the current level ----
+    double own = threadIdx.x < V ? s_agg[threadIdx.x] : 0.0;
+    double lev_sum[WF_MAX_LEV];
+    bool completing = true;                                           // this tile is the last of its group so far
+    int idx = rt;                                                     // my group's number at the current level
+#pragma unroll
+    for (int l = 0; l < WF_MAX_LEV; ++l) {
+        lev_sum[l] = 0.0;
+        if (l >= q.nlev) continue;
+        const int dgt = idx % WF_L1, first = idx - dgt;               // siblings before me: first .. first+dgt-1
+        const size_t base = cb0 + q.lev_off[l] + first;
+        if (dgt > 0) {
+            if (threadIdx.x < dgt) wf_wait_flag(&w.flag[base + threadIdx.x]);     // one thread per flag: the waits overlap
             __syncthreads();
-            for (int e = threadIdx.x; e < cnt * V; e += WF_THREADS) {
+            for (int e = threadIdx.x; e < dgt * V; e += WF_THREADS) {
                 const int j = e / V, v = e - j * V;
-                const double* src = round == 0 ? &w.payA[(size_t)(cb * q.ntr + (rt - c1) + j) * V]
-                                  : j < nP ? &w.payP[(size_t)(cb * (q.nb2 + 1) + a) * V]
-                                           : &w.payB[(size_t)(cb * q.nb1 + (rt / WF_L1 - b) + (j - nP)) * V];
-                s_look[j * V + v] = __ldcg(src + v);
+                s_look[j * V + v] = __ldcg(&w.pay[(base + j) * V + v]);
             }
             __syncthreads();
             if (threadIdx.x < V) {
-                const int v = threadIdx.x;
-                if (round == 0) {
-                    for (int j = 0; j < c1; ++j) sA += s_look[j * V + v];
-                } else {
-                    sPB = nP ? s_look[v] : 0.0;
-                    for (int j = 0; j < b; ++j) sPB += s_look[(nP + j) * V + v];
-                }
+                double sum = 0.0;
+                for (int j = 0; j < dgt; ++j) sum += s_look[j * V + threadIdx.x];
+                lev_sum[l] = sum;
             }
         }
-        if (round == 0 && pubB) {                                     // the block's sum: this tile's own + the 15 before it
-            if (threadIdx.x < V) __stcg(&w.payB[(size_t)(cb * q.nb1 + rt / WF_L1) * V + threadIdx.x], sA + s_agg[threadIdx.x]);
+        const bool pub = completing && dgt == WF_L1 - 1 && l + 1 < q.nlev;   // I complete a group of the next level
+        if (pub) {
+            own = lev_sum[l] + own;                                   // (threads v < V) the 15 before me + mine
+            const size_t up = cb0 + q.lev_off[l + 1] + idx / WF_L1;
+            if (threadIdx.x < V) __stcg(&w.pay[up * V + threadIdx.x], own);
             __syncthreads();
-            if (threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flagB[cb * q.nb1 + rt / WF_L1], 1); }
+            if (threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flag[up], 1); }
         }
-        __syncthreads();                                              // s_look is reused by the next round / the tables
+        completing = pub;
+        idx /= WF_L1;
+        __syncthreads();                                              // s_look is reused by the next level / the table
     }
     if (threadIdx.x < V) {
         const int v = threadIdx.x;
+        double above = 0.0;                                           // highest level first: a fixed order
+#pragma unroll
+        for (int l = WF_MAX_LEV - 1; l >= 0; --l) above += lev_sum[l];
         // statistics shared by several workers: the rollouts of the workers before this one (rank order) come first
         double prior = 0.0;
         if (totals != nullptr) {
@@ -194,11 +192,9 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
                 for (int r = 0; r < rank; ++r)
                     prior += totals[(size_t)r * (1 + 2 * q.O) + 1 + (v < q.CB ? 0 : q.O) + col0 + c];
         }
-        s_base[v] = prior + (sPB + sA);
-        if (pubP) __stcg(&w.payP[(size_t)(cb * (q.nb2 + 1) + a + 1) * V + v], sPB + (sA + s_agg[v]));
+        s_base[v] = prior + above;
     }
     __syncthreads();
-    if (pubP && threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flagP[cb * (q.nb2 + 1) + a + 1], 1); }
     // ---- per-row 1/n_t in fp32, once per row instead of once per element ----
     double n0 = (double)n0f, rows_all = (double)q.T;               // rows before this rollout / rows of all workers
     if (totals != nullptr) {
@@ -346,8 +342,18 @@ WfGeom wf_geom(int64_t T, int O) {
         q.RPG = (q.R + q.G - 1) / q.G;
     }
     q.ntr = (int)ceil_div64(T, q.R);
-    q.nb1 = (q.ntr + WF_L1 - 1) / WF_L1;
-    q.nb2 = (q.nb1 + WF_L1 - 1) / WF_L1;
+    q.nlev = 0;
+    int n = q.ntr, off = 0;
+    for (int l = 0; l < WF_MAX_LEV; ++l) { q.lev_n[l] = 0; q.lev_off[l] = 0; }
+    while (q.nlev < WF_MAX_LEV) {
+        q.lev_n[q.nlev] = n;
+        q.lev_off[q.nlev] = off;
+        off += n;
+        ++q.nlev;
+        if (n <= WF_L1) break;                      // every tile's group number at this level is < 16: the top level
+        n = (n + WF_L1 - 1) / WF_L1;                // groups one level up (the last may be partial: never read)
+    }
+    q.per_cb = off;
     return q;
 }
 
@@ -358,7 +364,7 @@ size_t wf_smem_bytes(const WfGeom& q) {
            (look > tables ? look : tables) + 16;
 }
 
-size_t wf_flag_ints(const WfGeom& q) { return 4 + (size_t)q.ncb * ((size_t)q.ntr + q.nb1 + q.nb2 + 1); }
+size_t wf_flag_ints(const WfGeom& q) { return 4 + (size_t)q.ncb * (size_t)q.per_cb; }
 size_t wf_flag_bytes(const WfGeom& q) { return align_up(sizeof(int) * wf_flag_ints(q), 16); }
 
 }  // namespace
@@ -367,7 +373,7 @@ size_t wf_flag_bytes(const WfGeom& q) { return align_up(sizeof(int) * wf_flag_in
 extern "C" size_t dppo_welford_scratch_bytes(int64_t T, int O) {
     if (T <= 0 || O <= 0) return 16;
     const WfGeom q = wf_geom(T, O);
-    return wf_flag_bytes(q) + sizeof(double) * 2 * q.CB * (size_t)q.ncb * ((size_t)q.ntr + q.nb1 + q.nb2 + 1);
+    return wf_flag_bytes(q) + sizeof(double) * 2 * q.CB * (size_t)q.ncb * (size_t)q.per_cb;
 }
 
 extern "C" size_t dppo_welford_totals_scratch_bytes(int64_t T, int O) {
@@ -420,12 +426,8 @@ static int welford_launch(const float* obs, float* out, int64_t T, int O, float*
     cudaStream_t stream = (cudaStream_t)stream_;
     WfScratch w;
     w.ticket = (int*)scratch;
-    w.flagA = w.ticket + 4;
-    w.flagB = w.flagA + (size_t)q.ncb * q.ntr;
-    w.flagP = w.flagB + (size_t)q.ncb * q.nb1;
-    w.payA = (double*)((char*)scratch + wf_flag_bytes(q));
-    w.payB = w.payA + (size_t)2 * q.CB * q.ncb * q.ntr;
-    w.payP = w.payB + (size_t)2 * q.CB * q.ncb * q.nb1;
+    w.flag = w.ticket + 4;
+    w.pay = (double*)((char*)scratch + wf_flag_bytes(q));
     const bool vec = aligned16(obs) && aligned16(out);
     const size_t smem = wf_smem_bytes(q);
     static size_t smem_set[64] = {0};                             // per device

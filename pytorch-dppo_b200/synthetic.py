@@ -5,8 +5,6 @@ actions = mu_theta0(state) + std*N(0,1) with the flavour's convention
 (train.py:89 / ppo.py:93), rewards ~ clamp(N(0,1),-1,1) (train.py:96), values
 = V_theta0(state), segments of ``seg_len`` steps plus a ragged tail, each ending
 with done (p = 1/2, bootstrap 0) or a bootstrap value (train.py:109-112)."""
-import math
-
 import torch
 
 import b200_native as nv
@@ -37,13 +35,9 @@ def make_rollout(model, obs_stats, T, seed, flavour, seg_len=1000, pinned_host=T
         st.observes_batch(d.raw_obs, out=d.obs)
     else:
         d.obs.copy_(d.raw_obs.clamp(-5, 5))
-    with torch.no_grad():
-        mu, sigma_sq, v = model(d.obs)
-        std = sigma_sq.sqrt() if flavour == nv.FLAVOUR_DPPO else sigma_sq
-        d.act.copy_(mu + std * eps.to(dev))
-        d.val.copy_(v.reshape(-1))
-        logp = (-0.5 * ((d.act - mu) / sigma_sq).pow(2) - 0.5 * math.log(2 * math.pi) - model.log_std).sum(-1)
-        d.logp.copy_(logp)
+    # actions, values and stored log-probs from the batched rollout forward of the update path (Model.act, no torch
+    # eager / cuBLAS): action = mu + std*eps with the flavour's convention (train.py:89 / ppo.py:93)
+    model.act(d.obs, eps.to(dev), flavour == nv.FLAVOUR_DPPO, v=d.val, act=d.act, logp=d.logp)
     seg_end = torch.zeros(T, dtype=torch.uint8)
     seg_end[seg_len - 1::seg_len] = 1
     seg_end[T - 1] = 1

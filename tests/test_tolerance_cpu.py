@@ -2,9 +2,8 @@
 meaningful: the REFERENCE'S OWN fp32 gradients do not meet it against themselves when only the number of
 MKL threads changes (a different summation order), nor against their fp64 evaluation.  Small entries of a
 gradient tensor carry the absolute rounding error of a 4096-term reduction.  The GPU tests therefore assert
-the per-tensor bound (1e-5 * max|ref|) everywhere, the survey's element-wise bound where no long reduction is
-involved, and ELEM_ATOL_REDUCTION (util.py) for reduction results; the floor measured here is what that
-constant is set against."""
+the per-tensor bound (1e-5 * max|ref|) and an element-wise bound with atol = 5e-6 * max|ref| (util.py); the floor
+measured here is what that constant is set against."""
 import torch
 
 from oracle import ppo_oracle as orc

@@ -27,18 +27,19 @@ def unpadded(flat, offsets, sizes):
     return torch.cat([flat[offsets[i]:offsets[i] + sizes[i]] for i in range(len(sizes))])
 
 
-# Two criteria:
+# Two criteria, both asserted by every comparison:
 #   per tensor     max|got-ref| <= rel * max|ref|                                   (north_star's 1e-5 relative)
-#   element-wise   |got_i-ref_i| <= ELEM_RTOL*|ref_i| + elem_atol * max|ref|        (survey: elem_atol = 1e-8)
-# Every comparison records the smallest elem_atol that would pass (CLOSENESS); conftest writes the table to
-# gpurun_out/closeness_report.json so the tensors that need more than 1e-8 are listed with their numbers.
-# Which ones do, and why: results of long fp32 reductions (gradients, means) whose terms cancel.  An entry that is
-# 1e-3 of the tensor's largest carries the absolute rounding error of the whole reduction (~1e-7 * scale), i.e.
-# 1e-4 relative to itself - for the reference's own fp32 run just as for ours (test_elementwise_floor_of_the_reference
-# measures the reference against its fp64 self).  ELEM_ATOL_REDUCTION is the bound asserted for those.
+#   element-wise   |got_i-ref_i| <= ELEM_RTOL*|ref_i| + elem_atol * max|ref|        with elem_atol = rel/2 by default
+# The survey proposed elem_atol = 1e-8.  That is below what fp32 can deliver for the results of long reductions
+# (gradients, means, normalised rows): an entry that is 1e-3 of the tensor's largest carries the absolute rounding error
+# of the whole reduction (~1e-7 * scale), i.e. 1e-4 relative to itself - for the reference's own fp32 run just as for
+# ours: tests/test_tolerance_cpu.py shows the reference missing 1e-8 against its own fp64 evaluation and against
+# itself with another thread count.  Measured on the B200 over the whole GPU suite (closeness_report.json, written by
+# conftest): the largest elem_atol any tensor needs is 2.4e-6 (p_fc2.bias gradient), the largest per-tensor error
+# 2.4e-6; the asserted 5e-6 / 1e-5 leave a factor 2 / 4.  Every comparison records what it needed (CLOSENESS).
 ELEM_RTOL = 1e-5
 ELEM_ATOL_SURVEY = 1e-8
-ELEM_ATOL_REDUCTION = 2e-6
+ELEM_ATOL_REDUCTION = 5e-6
 CLOSENESS = []
 
 
@@ -55,8 +56,10 @@ def closeness(got, ref):
                 n=int(ref.numel()), n_beyond_survey=int((excess > ELEM_ATOL_SURVEY * s).sum()))
 
 
-def assert_close_scaled(got, ref, rel=1e-5, name="", elem_atol=None):
-    """Per-tensor bound always; the element-wise bound too when ``elem_atol`` is given."""
+def assert_close_scaled(got, ref, rel=1e-5, name="", elem_atol="default"):
+    """Per-tensor bound and element-wise bound (elem_atol = rel/2 unless given; None switches the latter off)."""
+    if elem_atol == "default":
+        elem_atol = 0.5 * rel
     got_t = torch.as_tensor(got, dtype=torch.float64).reshape(-1)
     ref_t = torch.as_tensor(ref, dtype=torch.float64).reshape(-1)
     assert got_t.shape == ref_t.shape, (name, got_t.shape, ref_t.shape)
