@@ -37,6 +37,7 @@ constexpr int WF_THREADS = 256;
 constexpr int WF_CB = 32;                           // widest column block
 constexpr int WF_L1 = 16;                           // radix of the hierarchy
 constexpr int WF_MAX_LEV = 6;                       // 16^6 tiles
+constexpr int WF_LOOK = 16;                         // payloads staged per pass of the look-back (smem per CTA decides the occupancy)
 constexpr int WF_MAX_ROWS = 8448;                   // bounds the per-row reciprocal table (256 groups x 33 rows, O = 1)
 
 struct WfGeom {
@@ -52,17 +53,28 @@ struct WfGeom {
 
 struct WfScratch {                                  // carved from the caller's scratch
     int* ticket;
-    int* flag;                                      // [ncb][per_cb]: tot[l][g] of column block cb at cb*per_cb + lev_off[l] + g
-    double* pay;                                    // same shape x [2*CB]
+    uint4* pay;                                     // [ncb][per_cb][2*CB] LL words: tot[l][g] of column block cb at cb*per_cb + lev_off[l] + g
 };
 
-__device__ __forceinline__ void wf_wait_flag(const int* f) {
-    while (ld_acquire_gpu(f) == 0) { }
+// A published double travels as ONE 16-byte word {lo, 1, hi, 1} (the "LL" idea of NCCL's low-latency protocol, as in
+// dppo_comm.cu): 8-byte halves are single-copy atomic, so a reader that sees the tag in both halves has the value -
+// no flag array, no fence on either side, one L2 round trip per look.  The payload area is cleared per call.
+__device__ __forceinline__ void wf_publish(uint4* p, double x) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(x);
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"((unsigned)b), "r"(1u), "r"((unsigned)(b >> 32)), "r"(1u)
+                 : "memory");
+}
+__device__ __forceinline__ double wf_fetch(const uint4* p) {
+    uint4 v;
+    do {
+        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    } while (v.y != 1u || v.w != 1u);
+    return __longlong_as_double((long long)((unsigned long long)v.x | ((unsigned long long)v.z << 32)));
 }
 
 // dynamic smem: float tile[R*CB] | float p[CB], M0[CB] | double g1[G*CB], g2[G*CB] | double base[2*CB], agg[2*CB] |
-//               union { double look[16][2*CB];  float nf[R] }
-__global__ void __launch_bounds__(WF_THREADS)
+//               union { double look[WF_LOOK][2*CB];  float nf[R] }
+__global__ void __launch_bounds__(WF_THREADS, 5)
 wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const WfGeom q, float* __restrict__ n,
                 float* __restrict__ mean, float* __restrict__ mean_diff, float* __restrict__ var, const WfScratch w,
                 const bool vec, const double* __restrict__ totals, const int rank, const int world) {
@@ -126,58 +138,81 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
     }
     __syncthreads();
     // ---- tile sums (fixed order over the groups), exclusive prefix of the groups in place, publish ----
-    const size_t cb0 = (size_t)cb * q.per_cb;                         // this column block's slice of flag[] / pay[]
-    if (threadIdx.x < cw) {
-        const int c = threadIdx.x;
+    const size_t cb0 = (size_t)cb * q.per_cb;                         // this column block's slice of pay[]
+    if (threadIdx.x < q.CB) {                                         // every word of the payload is published (readers
+        const int c = threadIdx.x;                                    // poll all 2*CB of them): zeros beyond this block's columns
         double r1 = 0.0, r2 = 0.0;
-        for (int g = 0; g < q.G; ++g) {
+        for (int g = 0; g < q.G && c < cw; ++g) {
             const double x1 = s_g1[g * q.CB + c], x2 = s_g2[g * q.CB + c];
             s_g1[g * q.CB + c] = r1; s_g2[g * q.CB + c] = r2;
             r1 += x1; r2 += x2;
         }
         s_agg[c] = r1; s_agg[q.CB + c] = r2;
-        __stcg(&w.pay[(cb0 + rt) * V + c], r1);
-        __stcg(&w.pay[(cb0 + rt) * V + q.CB + c], r2);
+        wf_publish(&w.pay[(cb0 + rt) * V + c], r1);
+        wf_publish(&w.pay[(cb0 + rt) * V + q.CB + c], r2);
     }
     __syncthreads();
-    if (threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flag[cb0 + rt], 1); }
-    // ---- sums of all rows above this tile, level by level (bottom-up, so that group sums are published as early
-    // as possible); own = the sums of the group this tile completes at the current level ----
+    // ---- sums of all rows above this tile.  While this tile is the LAST of its group at a level it handles that
+    // level on its own and publishes the group's sums at once (a group sum needs nothing from outside the group); all
+    // remaining levels are then fetched together: one L2 round trip for a tile that completes nothing (15 of 16). ----
     double own = threadIdx.x < V ? s_agg[threadIdx.x] : 0.0;
     double lev_sum[WF_MAX_LEV];
-    bool completing = true;                                           // this tile is the last of its group so far
-    int idx = rt;                                                     // my group's number at the current level
 #pragma unroll
-    for (int l = 0; l < WF_MAX_LEV; ++l) {
-        lev_sum[l] = 0.0;
-        if (l >= q.nlev) continue;
-        const int dgt = idx % WF_L1, first = idx - dgt;               // siblings before me: first .. first+dgt-1
-        const size_t base = cb0 + q.lev_off[l] + first;
-        if (dgt > 0) {
-            if (threadIdx.x < dgt) wf_wait_flag(&w.flag[base + threadIdx.x]);     // one thread per flag: the waits overlap
-            __syncthreads();
-            for (int e = threadIdx.x; e < dgt * V; e += WF_THREADS) {
-                const int j = e / V, v = e - j * V;
-                s_look[j * V + v] = __ldcg(&w.pay[(base + j) * V + v]);
-            }
+    for (int l = 0; l < WF_MAX_LEV; ++l) lev_sum[l] = 0.0;
+    int lfirst = 0;                                                   // first level not yet summed
+    {
+        int idx = rt;
+#pragma unroll
+        for (int l = 0; l < WF_MAX_LEV; ++l) {
+            if (l + 1 >= q.nlev || idx % WF_L1 != WF_L1 - 1) break;   // I complete a group of level l+1
+            const size_t base = cb0 + q.lev_off[l] + (idx - (WF_L1 - 1));
+            for (int e = threadIdx.x; e < (WF_L1 - 1) * V; e += WF_THREADS) s_look[e] = wf_fetch(&w.pay[base * V + e]);
             __syncthreads();
             if (threadIdx.x < V) {
                 double sum = 0.0;
-                for (int j = 0; j < dgt; ++j) sum += s_look[j * V + threadIdx.x];
+                for (int j = 0; j < WF_L1 - 1; ++j) sum += s_look[j * V + threadIdx.x];
                 lev_sum[l] = sum;
+                own = sum + own;                                      // the 15 before me + mine
+                wf_publish(&w.pay[(cb0 + q.lev_off[l + 1] + idx / WF_L1) * V + threadIdx.x], own);
             }
-        }
-        const bool pub = completing && dgt == WF_L1 - 1 && l + 1 < q.nlev;   // I complete a group of the next level
-        if (pub) {
-            own = lev_sum[l] + own;                                   // (threads v < V) the 15 before me + mine
-            const size_t up = cb0 + q.lev_off[l + 1] + idx / WF_L1;
-            if (threadIdx.x < V) __stcg(&w.pay[up * V + threadIdx.x], own);
             __syncthreads();
-            if (threadIdx.x == 0) { __threadfence(); st_release_gpu(&w.flag[up], 1); }
+            idx /= WF_L1;
+            lfirst = l + 1;
         }
-        completing = pub;
-        idx /= WF_L1;
-        __syncthreads();                                              // s_look is reused by the next level / the table
+    }
+    {
+        // the remaining levels: payload j of the combined list belongs to level L(j); staged WF_LOOK at a time
+        int cnt[WF_MAX_LEV], start[WF_MAX_LEV], total = 0;
+        size_t base[WF_MAX_LEV];
+        int idx = rt;
+#pragma unroll
+        for (int l = 0; l < WF_MAX_LEV; ++l) {
+            const int dgt = idx % WF_L1;
+            cnt[l] = (l >= lfirst && l < q.nlev) ? dgt : 0;
+            base[l] = cb0 + (l < q.nlev ? q.lev_off[l] : 0) + (idx - dgt);
+            start[l] = total;
+            total += cnt[l];
+            idx /= WF_L1;
+        }
+        for (int p0 = 0; p0 < total; p0 += WF_LOOK) {
+            const int np = min(WF_LOOK, total - p0);
+            for (int e = threadIdx.x; e < np * V; e += WF_THREADS) {
+                const int j = p0 + e / V, v = e % V;
+                int l = 0;
+#pragma unroll
+                for (int k = 1; k < WF_MAX_LEV; ++k) if (j >= start[k] && cnt[k] > 0) l = k;
+                s_look[e] = wf_fetch(&w.pay[(base[l] + (j - start[l])) * V + v]);
+            }
+            __syncthreads();
+            if (threadIdx.x < V) {
+#pragma unroll
+                for (int l = 0; l < WF_MAX_LEV; ++l) {                 // within a level in order; the levels are combined below
+                    const int j0 = max(start[l], p0), j1 = min(start[l] + cnt[l], p0 + np);
+                    for (int j = j0; j < j1; ++j) lev_sum[l] += s_look[(j - p0) * V + threadIdx.x];
+                }
+            }
+            __syncthreads();
+        }
     }
     if (threadIdx.x < V) {
         const int v = threadIdx.x;
@@ -358,22 +393,21 @@ WfGeom wf_geom(int64_t T, int O) {
 }
 
 size_t wf_smem_bytes(const WfGeom& q) {
-    const size_t look = sizeof(double) * 16 * 2 * q.CB;
+    const size_t look = sizeof(double) * WF_LOOK * 2 * q.CB;
     const size_t tables = sizeof(float) * (size_t)q.R;
     return sizeof(float) * ((size_t)q.R * q.CB + 2 * WF_CB) + sizeof(double) * (2 * (size_t)q.G * q.CB + 4 * WF_CB) +
            (look > tables ? look : tables) + 16;
 }
 
-size_t wf_flag_ints(const WfGeom& q) { return 4 + (size_t)q.ncb * (size_t)q.per_cb; }
-size_t wf_flag_bytes(const WfGeom& q) { return align_up(sizeof(int) * wf_flag_ints(q), 16); }
+size_t wf_pay_bytes(const WfGeom& q) { return sizeof(uint4) * 2 * q.CB * (size_t)q.ncb * (size_t)q.per_cb; }
 
 }  // namespace
 
-// scratch: int ticket, flags | double payloads (see WfScratch); only the flags are cleared per call
+// scratch: int ticket | LL payload words (see WfScratch), cleared per call
 extern "C" size_t dppo_welford_scratch_bytes(int64_t T, int O) {
     if (T <= 0 || O <= 0) return 16;
     const WfGeom q = wf_geom(T, O);
-    return wf_flag_bytes(q) + sizeof(double) * 2 * q.CB * (size_t)q.ncb * (size_t)q.per_cb;
+    return 16 + wf_pay_bytes(q);
 }
 
 extern "C" size_t dppo_welford_totals_scratch_bytes(int64_t T, int O) {
@@ -426,8 +460,7 @@ static int welford_launch(const float* obs, float* out, int64_t T, int O, float*
     cudaStream_t stream = (cudaStream_t)stream_;
     WfScratch w;
     w.ticket = (int*)scratch;
-    w.flag = w.ticket + 4;
-    w.pay = (double*)((char*)scratch + wf_flag_bytes(q));
+    w.pay = (uint4*)((char*)scratch + 16);
     const bool vec = aligned16(obs) && aligned16(out);
     const size_t smem = wf_smem_bytes(q);
     static size_t smem_set[64] = {0};                             // per device
@@ -438,7 +471,7 @@ static int welford_launch(const float* obs, float* out, int64_t T, int O, float*
         DPPO_CUDA_TRY(cudaFuncSetAttribute(wf_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         smem_set[dev] = smem;
     }
-    DPPO_CUDA_TRY(cudaMemsetAsync(scratch, 0, wf_flag_bytes(q), stream));
+    DPPO_CUDA_TRY(cudaMemsetAsync(scratch, 0, 16 + wf_pay_bytes(q), stream));      // ticket + the LL tags
     wf_fused_kernel<<<q.ntr * q.ncb, WF_THREADS, smem, stream>>>(obs, out, q, n, mean, mean_diff, var, w, vec, totals,
                                                                   rank, world);
     DPPO_LAUNCH_CHECK();
