@@ -211,6 +211,14 @@ int dppo_comm_local_handle(dppo_comm* c, void* handle_host);
 int dppo_comm_open_peers(dppo_comm* c, const void* handles_host);
 int dppo_comm_create_loopback(int world, int P_pad, dppo_comm** out_array);
 int dppo_comm_destroy(dppo_comm* c);
+/* Exchange algorithm of dppo_allreduce_adam: PUSH_ALL sends every rank's bucket to every peer (one NVLink hop; default
+ * for W <= 4), OWNER sends each column block to one owning rank that adds the W slices in rank order and sends the sum
+ * back to all (two hops, a quarter of the bytes at W = 8; default for W > 4).  Same results bit for bit.  All ranks must
+ * choose the same algorithm, between epochs. */
+#define DPPO_COMM_ALGO_PUSH_ALL 1
+#define DPPO_COMM_ALGO_OWNER    2
+int dppo_comm_set_algorithm(dppo_comm* c, int algo);
+int dppo_comm_get_algorithm(dppo_comm* c);
 /* A rank that waits for peers which never push (a dead process, unequal numbers of calls) gives up after a few
  * seconds of polling and records it; dppo_comm_check returns DPPO_E_COMM from then on (0 otherwise).  It
  * synchronises the device.  The reference has no such detection: a dead worker deadlocks the chief

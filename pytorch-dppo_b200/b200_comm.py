@@ -44,6 +44,9 @@ class PeerComm:
         handles = exchange(self.group, nv.comm_local_handle(self.handle))
         if self.world > 1:
             nv.comm_open_peers(self.handle, handles)
+        algo = os.environ.get("DPPO_COMM_ALGO")            # "push_all" | "owner"; default by world size (owner for W > 4)
+        if algo:
+            nv.comm_set_algorithm(self.handle, {"push_all": nv.COMM_ALGO_PUSH_ALL, "owner": nv.COMM_ALGO_OWNER}[algo])
         dist.barrier(group=self.group)
 
     def allreduce_adam(self, eng, k, gshared):
@@ -74,7 +77,10 @@ class PeerComm:
         return 1
 
     def describe(self):
-        return {"mode": self.mode, "world": self.world,
+        algo = None
+        if self.mode == "p2p" and self.handle is not None:
+            algo = {nv.COMM_ALGO_PUSH_ALL: "push_all", nv.COMM_ALGO_OWNER: "owner"}.get(nv.comm_get_algorithm(self.handle))
+        return {"mode": self.mode, "world": self.world, "algorithm": algo,
                 "kernel": "dppo_allreduce_adam (push over NVLink peer memory + flags, fused with Adam)"
                 if self.mode == "p2p" else "dppo_reduce_partials + NCCL all_reduce + dppo_reduce_adam"}
 

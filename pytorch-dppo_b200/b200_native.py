@@ -78,6 +78,8 @@ def _load():
         "dppo_comm_create_loopback": (i32, [i32, i32, c.POINTER(vp)]),
         "dppo_comm_destroy": (i32, [vp]),
         "dppo_comm_check": (i32, [vp]),
+        "dppo_comm_set_algorithm": (i32, [vp, i32]),
+        "dppo_comm_get_algorithm": (i32, [vp]),
         "dppo_update_set_path": (i32, [i32]),
         "dppo_allreduce_adam": (i32, [vp, vp, i32, vp, vp, vp, vp, vp, i32, i32, dbl, dbl, dbl, dbl, vp, vp, vp, vp, vp]),
         "dppo_allreduce_adam_loopback": (i32, [c.POINTER(vp), i32, c.POINTER(vp), c.POINTER(i32), c.POINTER(vp),
@@ -363,6 +365,17 @@ def comm_open_peers(comm, handles):
 
 def comm_destroy(comm):
     lib.dppo_comm_destroy(comm)
+
+
+COMM_ALGO_PUSH_ALL, COMM_ALGO_OWNER = 1, 2
+
+
+def comm_set_algorithm(comm, algo):
+    check(lib.dppo_comm_set_algorithm(comm, algo))
+
+
+def comm_get_algorithm(comm):
+    return lib.dppo_comm_get_algorithm(comm)
 
 
 def comm_check(comm):

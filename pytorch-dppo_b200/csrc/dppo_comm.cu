@@ -21,6 +21,16 @@
 //   reference.  Receive slots are double-buffered by epoch parity; a slot is rewritten two epochs
 //   later, after its reader has pushed the epoch in between (which it does after reading).
 //
+// Two exchange algorithms in the same kernel (dppo_comm_set_algorithm; default by world size):
+//   DPPO_COMM_ALGO_PUSH_ALL  as above: one NVLink hop, every rank sends its whole bucket to every peer
+//                            (W-1)*P floats out per rank - the lowest latency, right for W <= 4;
+//   DPPO_COMM_ALGO_OWNER     column block jb belongs to rank jb mod W: every rank pushes its slice of the block to the
+//                            owner only, the owner adds the W slices in rank order (plus the shared bucket's content)
+//                            and pushes the SUM to every rank, all ranks run Adam on it.  Two hops, but 2*(W-1)/W * P
+//                            floats out per rank instead of (W-1)*P: at W = 8 a quarter of the bytes, which is what
+//                            the exchange was bound by there.  The sum is formed by one rank and copied, so replicas
+//                            stay bit-identical by construction.
+//
 // CTAs walk the column blocks in index order on every GPU and push ALL their blocks before they
 // poll any, so a poll only ever waits for pushes that depend on nothing.  That argument needs every
 // rank's CTAs to actually run: the grid is capped at what is co-resident on this GPU (occupancy x SMs),
@@ -51,6 +61,8 @@ struct CommDev {                            // everything a kernel needs, by val
     unsigned* err;                          // this rank: non-zero once a poll has timed out
     uint4* ag[CM_MAX_WORLD];                // ag[r]: rank r's all-gather buffer [2][world][CM_AG_MAX] LL words (peer-mapped)
     unsigned* ag_epoch;                     // this rank: completed all-gathers
+    uint4* gs[CM_MAX_WORLD];                // gs[r]: rank r's buffer for the owners' sums [2][n4][2] LL words (OWNER algorithm)
+    int algo;
 };
 
 }  // namespace
@@ -58,7 +70,7 @@ struct CommDev {                            // everything a kernel needs, by val
 struct dppo_comm {
     int rank, world, P_pad, n4, gblocks, loopback, grid;
     void* base;                             // this rank's allocation
-    size_t bytes, recv_bytes, flag_bytes;
+    size_t bytes, recv_bytes, flag_bytes, gs_bytes;
     void* peer_base[CM_MAX_WORLD];          // mapped bases (peer_base[rank] == base)
     CommDev dev;
 };
@@ -131,8 +143,9 @@ __global__ void __launch_bounds__(CM_THREADS) allreduce_adam_kernel(const Launch
         __syncthreads();                                  // red[] of the previous column block consumed
         red[g][lane] = a;
         __syncthreads();
-        // warps 0..world-1: warp w pushes to rank w (all warps hold the same sum)
-        if (g < C.world && i < n4) {
+        // PUSH_ALL: warps 0..world-1, warp w pushes to rank w (all warps hold the same sum); OWNER: warp 0 pushes to the owner
+        const int owner = jb % C.world;
+        if ((C.algo == DPPO_COMM_ALGO_OWNER ? g == 0 : g < C.world) && i < n4) {
             float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
             for (int r = 0; r < CM_THREADS / 32; ++r) {
@@ -140,7 +153,7 @@ __global__ void __launch_bounds__(CM_THREADS) allreduce_adam_kernel(const Launch
                 mine.x = __fadd_rn(mine.x, x.x); mine.y = __fadd_rn(mine.y, x.y);
                 mine.z = __fadd_rn(mine.z, x.z); mine.w = __fadd_rn(mine.w, x.w);
             }
-            uint4* dst = C.recv[g] + (((size_t)par * C.world + C.rank) * n4 + i) * 2;
+            uint4* dst = C.recv[C.algo == DPPO_COMM_ALGO_OWNER ? owner : g] + (((size_t)par * C.world + C.rank) * n4 + i) * 2;
             st_ll(dst, mine.x, mine.y, epoch);
             st_ll(dst + 1, mine.z, mine.w, epoch);
         }
@@ -151,8 +164,10 @@ __global__ void __launch_bounds__(CM_THREADS) allreduce_adam_kernel(const Launch
     // then adds the W slices in rank order and runs Adam.
     for (int jb = blockIdx.x; jb < C.gblocks; jb += gridDim.x) {
         const int i = jb * CM_RQ + lane;
+        const bool owner_algo = C.algo == DPPO_COMM_ALGO_OWNER;
+        const bool gather_here = !owner_algo || (jb % C.world) == C.rank;     // this rank adds the W slices of the block
         __syncthreads();                                  // red[] of phase 1 / of the previous column block consumed
-        if (g < C.world && i < n4) {
+        if (gather_here && g < C.world && i < n4) {
             const uint4* q = C.recv[C.rank] + (((size_t)par * C.world + g) * n4 + i) * 2;
             uint4 lo = ld_ll(q), hi = ld_ll(q + 1);
             if (lo.y != epoch || lo.w != epoch || hi.y != epoch || hi.w != epoch) {
@@ -166,16 +181,38 @@ __global__ void __launch_bounds__(CM_THREADS) allreduce_adam_kernel(const Launch
             red[g][lane] = make_float4(__uint_as_float(lo.x), __uint_as_float(lo.z), __uint_as_float(hi.x), __uint_as_float(hi.z));
         }
         __syncthreads();
-        if (g != 0 || i >= n4) continue;
         float4 G = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int r = 0; r < C.world; ++r) {
-            const float4 x = red[r][lane];
-            G.x = __fadd_rn(G.x, x.x); G.y = __fadd_rn(G.y, x.y); G.z = __fadd_rn(G.z, x.z); G.w = __fadd_rn(G.w, x.w);
+        if (gather_here && i < n4) {                      // (every warp forms the same sum: warp w pushes it to rank w below)
+            for (int r = 0; r < C.world; ++r) {
+                const float4 x = red[r][lane];
+                G.x = __fadd_rn(G.x, x.x); G.y = __fadd_rn(G.y, x.y); G.z = __fadd_rn(G.z, x.z); G.w = __fadd_rn(G.w, x.w);
+            }
+            if (A.gshared) {                              // shared bucket content on top (as dppo_adam.cu)
+                const float4 s0 = A.gshared[i];
+                G.x = __fadd_rn(s0.x, G.x); G.y = __fadd_rn(s0.y, G.y); G.z = __fadd_rn(s0.z, G.z); G.w = __fadd_rn(s0.w, G.w);
+            }
         }
-        if (A.gshared) {                                  // shared bucket content on top (as dppo_adam.cu)
-            const float4 s0 = A.gshared[i];
-            G.x = __fadd_rn(s0.x, G.x); G.y = __fadd_rn(s0.y, G.y); G.z = __fadd_rn(s0.z, G.z); G.w = __fadd_rn(s0.w, G.w);
+        if (owner_algo) {
+            if (gather_here && g < C.world && i < n4) {   // second hop: the owner's sum to every rank (its own copy included)
+                uint4* dst = C.gs[g] + ((size_t)par * n4 + i) * 2;
+                st_ll(dst, G.x, G.y, epoch);
+                st_ll(dst + 1, G.z, G.w, epoch);
+            }
+            if (g == 0 && i < n4) {
+                const uint4* q = C.gs[C.rank] + ((size_t)par * n4 + i) * 2;
+                uint4 lo = ld_ll(q), hi = ld_ll(q + 1);
+                if (lo.y != epoch || lo.w != epoch || hi.y != epoch || hi.w != epoch) {
+                    const long long t0 = clock64();
+                    while (true) {
+                        lo = ld_ll(q); hi = ld_ll(q + 1);
+                        if (lo.y == epoch && lo.w == epoch && hi.y == epoch && hi.w == epoch) break;
+                        if (clock64() - t0 > CM_SPIN_BUDGET) { atomicExch(C.err, 1u); break; }
+                    }
+                }
+                G = make_float4(__uint_as_float(lo.x), __uint_as_float(lo.z), __uint_as_float(hi.x), __uint_as_float(hi.z));
+            }
         }
+        if (g != 0 || i >= n4) continue;
         float4 p = A.theta[i], mm = A.m[i], vv = A.v[i];
         if (A.theta_prev) A.theta_prev[i] = p;
         adam_one(G.x, p.x, mm.x, vv.x, s);
@@ -215,7 +252,8 @@ AdamScalars make_scalars(int step, double lr, double beta1, double beta2, double
 size_t layout(dppo_comm* c) {
     c->recv_bytes = align_up(sizeof(uint4) * 2 * 2 * (size_t)c->world * c->n4, 256);    // LL: 2x the payload
     c->flag_bytes = align_up(sizeof(uint4) * 2 * (size_t)c->world * CM_AG_MAX, 256);   // the small all-gather's slots
-    return c->recv_bytes + c->flag_bytes + 256;
+    c->gs_bytes = align_up(sizeof(uint4) * 2 * 2 * (size_t)c->n4, 256);                // the owners' sums (OWNER algorithm)
+    return c->recv_bytes + c->flag_bytes + c->gs_bytes + 256;
 }
 
 void fill_dev(dppo_comm* c) {
@@ -223,8 +261,11 @@ void fill_dev(dppo_comm* c) {
     for (int r = 0; r < c->world; ++r) {
         c->dev.recv[r] = (uint4*)c->peer_base[r];
         c->dev.ag[r] = (uint4*)((char*)c->peer_base[r] + c->recv_bytes);
+        c->dev.gs[r] = (uint4*)((char*)c->peer_base[r] + c->recv_bytes + c->flag_bytes);
     }
-    c->dev.epoch = (unsigned*)((char*)c->base + c->recv_bytes + c->flag_bytes);
+    if (c->dev.algo != DPPO_COMM_ALGO_PUSH_ALL && c->dev.algo != DPPO_COMM_ALGO_OWNER)
+        c->dev.algo = c->world > 4 ? DPPO_COMM_ALGO_OWNER : DPPO_COMM_ALGO_PUSH_ALL;
+    c->dev.epoch = (unsigned*)((char*)c->base + c->recv_bytes + c->flag_bytes + c->gs_bytes);
     c->dev.done = c->dev.epoch + 1;
     c->dev.err = c->dev.epoch + 2;
     c->dev.ag_epoch = c->dev.epoch + 3;
@@ -263,6 +304,14 @@ extern "C" int dppo_comm_create(int rank, int world, int P_pad, dppo_comm** out)
     *out = c;
     return 0;
 }
+
+// PUSH_ALL / OWNER (see the top of this file); every rank of a communicator must choose the same, between epochs.
+extern "C" int dppo_comm_set_algorithm(dppo_comm* c, int algo) {
+    if (!c || (algo != DPPO_COMM_ALGO_PUSH_ALL && algo != DPPO_COMM_ALGO_OWNER)) return DPPO_E_BADARG;
+    c->dev.algo = algo;
+    return 0;
+}
+extern "C" int dppo_comm_get_algorithm(dppo_comm* c) { return c ? c->dev.algo : DPPO_E_BADARG; }
 
 extern "C" int dppo_comm_handle_bytes(void) { return (int)sizeof(cudaIpcMemHandle_t); }
 

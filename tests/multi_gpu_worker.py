@@ -78,7 +78,7 @@ def main():
         torch.cuda.synchronize()
         err = float((ref.flat - flat).abs().max()) / float(flat.abs().max())
         assert err < 1e-5, err
-        print("MULTI_GPU_OK world=%d mode=%s rel_err_vs_single_gpu=%.2e" % (world, comm.mode, err), flush=True)
+        print("MULTI_GPU_OK world=%d mode=%s algo=%s rel_err_vs_single_gpu=%.2e" % (world, comm.mode, comm.describe().get("algorithm"), err), flush=True)
     # ---- observation statistics shared by the workers in rank order (main.py:54, model.py:61-80) ----
     stats = Shared_obs_stats(O, device=dev)
     norm = stats.observes_batch(buf.raw_obs, comm=comm)

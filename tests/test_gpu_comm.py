@@ -16,8 +16,9 @@ DEV = "cuda"
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("W,nparts", [(1, 5), (2, 147), (4, 16), (8, 3)])
-def test_loopback_sum_order_and_identical_replicas(W, nparts):
+@pytest.mark.parametrize("algo", ["push_all", "owner"])
+@pytest.mark.parametrize("W,nparts", [(1, 5), (2, 147), (4, 16), (8, 3), (8, 147), (3, 20)])
+def test_loopback_sum_order_and_identical_replicas(W, nparts, algo):
     """G = gshared + g_0 + g_1 + ... in rank order (model.py:53-55 with arrival order := rank order),
     buffers start at ones (model.py:51), every replica ends bit-identical; five epochs so that both
     receive-slot parities are reused."""
@@ -26,6 +27,8 @@ def test_loopback_sum_order_and_identical_replicas(W, nparts):
     g = torch.Generator().manual_seed(W * 100 + nparts)
     theta0 = torch.randn(P, generator=g)
     comms = nv.comm_create_loopback(W, P)
+    for c in comms:                                    # both exchange algorithms must give the same sum in the same order
+        nv.comm_set_algorithm(c, nv.COMM_ALGO_PUSH_ALL if algo == "push_all" else nv.COMM_ALGO_OWNER)
     th = [theta0.to(DEV).clone() for _ in range(W)]
     m = [torch.zeros(P, device=DEV) for _ in range(W)]
     v = [torch.zeros(P, device=DEV) for _ in range(W)]
@@ -57,6 +60,35 @@ def test_loopback_sum_order_and_identical_replicas(W, nparts):
             nv.comm_destroy(c)
 
 
+def test_owner_and_push_all_algorithms_are_bitwise_equal():
+    """The OWNER algorithm (slice to one owner, sum back to all) and PUSH_ALL (everything to everyone) add the same
+    values in the same order: identical parameters and Adam state after five epochs at W = 8."""
+    import b200_native as nv
+    P, W, nparts = 71720, 8, 37
+    res = []
+    for algo in (nv.COMM_ALGO_PUSH_ALL, nv.COMM_ALGO_OWNER):
+        g = torch.Generator().manual_seed(5)
+        theta0 = torch.randn(P, generator=g)
+        comms = nv.comm_create_loopback(W, P)
+        for c in comms:
+            nv.comm_set_algorithm(c, algo)
+        th = [theta0.to(DEV).clone() for _ in range(W)]
+        m = [torch.zeros(P, device=DEV) for _ in range(W)]
+        v = [torch.zeros(P, device=DEV) for _ in range(W)]
+        gsh = [torch.ones(P, device=DEV) for _ in range(W)]
+        try:
+            for step in range(1, 6):
+                parts = [(torch.randn(nparts, P, generator=g) * 0.01).to(DEV) for _ in range(W)]
+                nv.allreduce_adam_loopback(comms, parts, gsh, th, None, m, v, step, 3e-4)
+            torch.cuda.synchronize()
+        finally:
+            for c in comms:
+                nv.comm_destroy(c)
+        res.append((th[0].clone(), m[3].clone(), v[7].clone()))
+    for a, b in zip(*res):
+        assert torch.equal(a, b)
+
+
 def test_world_one_is_bitwise_the_single_gpu_path():
     import b200_native as nv
     P, nparts = 71720, 147
@@ -83,9 +115,11 @@ def test_world_one_is_bitwise_the_single_gpu_path():
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-@pytest.mark.parametrize("mode", ["p2p", "nccl"])
+@pytest.mark.parametrize("mode", ["p2p", "p2p-owner", "nccl"])
 def test_two_gpus_match_single_process(mode):
-    env = dict(os.environ, DPPO_COMM=mode)
+    env = dict(os.environ, DPPO_COMM=mode.split("-")[0])
+    if mode.endswith("owner"):
+        env["DPPO_COMM_ALGO"] = "owner"
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                           "--master-addr", "127.0.0.1", "--master-port", "29613",
                           os.path.join(ROOT, "tests", "multi_gpu_worker.py")], env=env, capture_output=True, text=True,
