@@ -2045,6 +2045,9 @@ void pick_tiling(int B, int* TM, int* nparts) {
     int tm = ((B + sms - 1) / sms + 3) & ~3;
     if (tm < 4) tm = 4;
     if (tm > UPD_TM_MAX) tm = UPD_TM_MAX;
+    // a tile always occupies 32 MMA columns: once full tiles fit in one wave, fill them (B = 4096: 128 CTAs of 32
+    // samples instead of 147 of 28 - the same time per CTA, 13 % fewer gradient partials for K3 to add)
+    if (tm > 16 && (B + UPD_TM_MAX - 1) / UPD_TM_MAX <= sms) tm = UPD_TM_MAX;
     const int ntiles = (B + tm - 1) / tm;
     *TM = tm;
     *nparts = ntiles < sms ? ntiles : sms;
