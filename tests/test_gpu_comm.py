@@ -129,6 +129,17 @@ def test_two_gpus_match_single_process(mode):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_gpus_lagging_rank_is_detected_not_waited_for_forever():
+    """A rank that makes one call fewer: the other rank's poll runs out of its clock budget, the kernel returns and
+    dppo_comm_check reports it (unbounded spin)."""
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29619",
+                          os.path.join(ROOT, "tests", "multi_gpu_lag_worker.py")], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "LAG_DETECTED" in out.stdout and "LAG_NOT_DETECTED" not in out.stdout
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
 def test_two_gpus_main_launcher():
     """pytorch-dppo_b200/main.py `run` under torchrun: train.train on every rank, exchange inside K3."""
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
