@@ -1610,6 +1610,26 @@ __device__ float block_sum(float x, float* red) {
     return r;
 }
 
+// three deterministic block sums (the same fixed tree as block_sum) sharing their barriers; r1 / r2: two more scratch
+// arrays of UPD_THREADS floats (the mu / mu_old area of the tile, dead by then)
+__device__ void block_sum3(float a, float b, float c, float* r0, float* r12, float& oa, float& ob, float& oc) {
+    float* r1 = r12;
+    float* r2 = r12 + UPD_THREADS;
+    __syncthreads();
+    r0[threadIdx.x] = a; r1[threadIdx.x] = b; r2[threadIdx.x] = c;
+    __syncthreads();
+    for (int s = UPD_THREADS / 2; s > 0; s >>= 1) {
+        if (threadIdx.x < s) {
+            r0[threadIdx.x] += r0[threadIdx.x + s];
+            r1[threadIdx.x] += r1[threadIdx.x + s];
+            r2[threadIdx.x] += r2[threadIdx.x + s];
+        }
+        __syncthreads();
+    }
+    oa = r0[0]; ob = r1[0]; oc = r2[0];
+    __syncthreads();
+}
+
 __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __grid_constant__ UpdArgs P) {
     extern __shared__ __align__(1024) float S[];
     const dppo_dims& d = P.d;
@@ -1675,10 +1695,34 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
             const Net nf = net_of(run_old ? P.theta_old : P.theta, P.lay);
             first_layers_prefetch(S + P.o_stage, nf.W1, nf.V1, d, reinterpret_cast<uint64_t*>(S + P.o_bars));
         }
-        // ---- zero the activation area (pads must read as 0), then gather --------------------
-        for (int i = threadIdx.x; i < P.o_zero_end; i += UPD_THREADS) S[i] = 0.f;
+        // ---- gather + zero the activation area (pads must read as 0) ---------------------------
+        // The gathered words are fetched into registers first (two dependent global loads each: position, then value), the
+        // activation area is zeroed with 128-bit stores while they are in flight, then the words are dropped in.
+        constexpr int GQ = 4;                                 // gathered obs words per thread and round
+        const int nobs = valid * d.O;
+        float gx[GQ];
+        int ge[GQ];
+#pragma unroll
+        for (int q = 0; q < GQ; ++q) {
+            const int e = threadIdx.x + q * UPD_THREADS;
+            ge[q] = e;
+            gx[q] = 0.f;
+            if (e < nobs) {
+                const int m = e / d.O, k = e - m * d.O;
+                const size_t r = P.idx ? (size_t)__ldg(P.idx + b0 + m) : (size_t)(b0 + m);
+                gx[q] = __ldg(P.obs + r * d.O + k);
+            }
+        }
+        {
+            float4* z4 = reinterpret_cast<float4*>(S);
+            const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = threadIdx.x; i < (P.o_zero_end >> 2); i += UPD_THREADS) z4[i] = zero;   // o_zero_end is a multiple of 4
+        }
         __syncthreads();
-        for (int e = threadIdx.x; e < valid * d.O; e += UPD_THREADS) {
+#pragma unroll
+        for (int q = 0; q < GQ; ++q)
+            if (ge[q] < nobs) { const int m = ge[q] / d.O, k = ge[q] - m * d.O; S[P.o_x + m * P.ldO + k] = gx[q]; }
+        for (int e = threadIdx.x + GQ * UPD_THREADS; e < nobs; e += UPD_THREADS) {      // wide observations: the rest
             const int m = e / d.O, k = e - m * d.O;
             const size_t r = P.idx ? (size_t)__ldg(P.idx + b0 + m) : (size_t)(b0 + m);
             S[P.o_x + m * P.ldO + k] = __ldg(P.obs + r * d.O + k);
@@ -1984,9 +2028,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
 
     K2_TICK(25);
     // ---- per-CTA loss sums (scaled so that K3 only has to add them) -----------------------------
-    const float sc = block_sum(lsum_clip, red);
-    const float sv = block_sum(lsum_val, red);
-    const float se = block_sum(lsum_ent, red);
+    float sc, sv, se;                                                 // the three loss sums in one pass over the tree
+    block_sum3(lsum_clip, lsum_val, lsum_ent, red, S + P.o_mu, sc, sv, se);
     if (threadIdx.x == 0 && !P.fwd_only) {
         float* lp = P.loss_partials + 4 * blockIdx.x;
         if (P.flavour == DPPO_FLAVOUR_DPPO) {
