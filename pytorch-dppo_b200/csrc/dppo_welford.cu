@@ -37,8 +37,9 @@ constexpr int WF_THREADS = 256;
 constexpr int WF_CB = 32;                           // widest column block
 constexpr int WF_L1 = 16;                           // radix of the hierarchy
 constexpr int WF_MAX_LEV = 6;                       // 16^6 tiles
-constexpr int WF_LOOK = 16;                         // payloads staged per pass of the look-back (smem per CTA decides the occupancy)
+constexpr int WF_RPG = 33;                          // rows per group of a full tile (the unrolled case of both passes)
 constexpr int WF_MAX_ROWS = 8448;                   // bounds the per-row reciprocal table (256 groups x 33 rows, O = 1)
+constexpr int WF_INFL = 4;                          // look-back loads a thread keeps in flight (4 parts x 4 >= 15)
 
 struct WfGeom {
     int O, CB, ncb;                                 // columns, columns per block (last block may be narrower), blocks
@@ -49,6 +50,10 @@ struct WfGeom {
     int lev_n[WF_MAX_LEV];                          // groups per column block at each level (lev_n[0] = ntr)
     int lev_off[WF_MAX_LEV];                        // offset of level l in the per-column-block arrays
     int per_cb;                                     // entries per column block over all levels
+    unsigned magic;                                 // floor(2^32 / CB) + 1: it / CB == umulhi(it, magic) for it < 2^32 / CB
+    int vshift;                                     // 2*CB <= 1 << vshift (5 or 6): word index of a look-back slot by mask
+    // shared memory carve-up (bytes from the start of the dynamic region); the tile is at 0
+    int o_p, o_m0, o_g1, o_g2, o_agg, o_base, o_lsum, o_part, o_nf, o_ctl, smem;
 };
 
 struct WfScratch {                                  // carved from the caller's scratch
@@ -64,16 +69,53 @@ __device__ __forceinline__ void wf_publish(uint4* p, double x) {
     asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"((unsigned)b), "r"(1u), "r"((unsigned)(b >> 32)), "r"(1u)
                  : "memory");
 }
-__device__ __forceinline__ double wf_fetch(const uint4* p) {
+__device__ __forceinline__ uint4 wf_look(const uint4* p) {
     uint4 v;
-    do {
-        asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
-    } while (v.y != 1u || v.w != 1u);
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ bool wf_there(const uint4& v) { return v.y == 1u && v.w == 1u; }
+__device__ __forceinline__ double wf_value(const uint4& v) {
     return __longlong_as_double((long long)((unsigned long long)v.x | ((unsigned long long)v.z << 32)));
 }
 
-// dynamic smem: float tile[R*CB] | float p[CB], M0[CB] | double g1[G*CB], g2[G*CB] | double base[2*CB], agg[2*CB] |
-//               union { double look[WF_LOOK][2*CB];  float nf[R] }
+// Sums of lists of consecutive payloads.  List u = payloads [lb[u], lb[u] + lc[u]) of V words each, lc <= 15.  A warp
+// covers 8 words x 4 parts of one list: lane = part*8 + word, part h adds entries 4h..4h+3 in index order with all its
+// loads in flight at once (one L2 round trip for everything that is already published, which is the normal case:
+// tickets are handed out in order; 8 lanes read 128 contiguous bytes), and two butterfly steps add the parts as
+// (p0+p1)+(p2+p3) - a fixed tree, so the result does not depend on timing.   part[u*V + word].
+__device__ __forceinline__ void wf_gather(const uint4* __restrict__ pay, const long long* lb, const int* lc, const int nlists,
+                                          const int V, const int vshift, double* part) {
+    const int slots = nlists << (vshift + 2);                         // lists x (words rounded up to 32 or 64) x 4 parts
+    for (int e = threadIdx.x; e < slots; e += WF_THREADS) {           // (whole warps: slots is a multiple of 32)
+        const int h = (e >> 3) & 3, blk = e >> 5;
+        const int v = ((blk & ((1 << (vshift - 3)) - 1)) << 3) + (e & 7), u = blk >> (vshift - 3);
+        const int n = v < V ? min(lc[u] - h * WF_INFL, WF_INFL) : 0;
+        double sum = 0.0;
+        if (n > 0) {
+            const uint4* p = pay + (lb[u] + h * WF_INFL) * V + v;
+            uint4 wv[WF_INFL];
+#pragma unroll
+            for (int k = 0; k < WF_INFL; ++k)
+                if (k < n) wv[k] = wf_look(p + k * V);
+#pragma unroll
+            for (int k = 0; k < WF_INFL; ++k)
+                if (k < n) {
+                    while (!wf_there(wv[k])) wv[k] = wf_look(p + k * V);
+                    sum += wf_value(wv[k]);
+                }
+        }
+        sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+        sum += __shfl_xor_sync(0xffffffffu, sum, 16);
+        if (h == 0 && v < V) part[u * V + v] = sum;
+    }
+}
+
+// it / d for it < 2^32 / d with magic = floor(2^32 / d) + 1 (d > 1)
+__device__ __forceinline__ int wf_div(int it, int d, unsigned magic) { return d == 1 ? it : (int)__umulhi((unsigned)it, magic); }
+
+// dynamic smem: float tile[R*CB] | float p[CB], M0[CB] | double g1[G*CB], g2[G*CB], agg[2*CB], base[2*CB],
+//               lsum[nlev][2*CB], part[nlev][2*CB] | float nf[R] | long long lb[WF_MAX_LEV]; int lc[WF_MAX_LEV]; mbarrier
 __global__ void __launch_bounds__(WF_THREADS, 5)
 wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const WfGeom q, float* __restrict__ n,
                 float* __restrict__ mean, float* __restrict__ mean_diff, float* __restrict__ var, const WfScratch w,
@@ -81,157 +123,62 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_ticket;
     float* s = reinterpret_cast<float*>(smem_raw);
-    float* s_p = s + q.R * q.CB;
-    float* s_m0 = s_p + WF_CB;
-    double* s_g1 = reinterpret_cast<double*>(s_m0 + WF_CB);
-    double* s_g2 = s_g1 + q.G * q.CB;
-    double* s_base = s_g2 + q.G * q.CB;
-    double* s_agg = s_base + 2 * WF_CB;
-    double* s_look = s_agg + 2 * WF_CB;
-    float* s_nf = reinterpret_cast<float*>(s_look);   // the look-back staging is dead when the table is built
+    float* s_p = reinterpret_cast<float*>(smem_raw + q.o_p);
+    float* s_m0 = reinterpret_cast<float*>(smem_raw + q.o_m0);
+    double* s_g1 = reinterpret_cast<double*>(smem_raw + q.o_g1);
+    double* s_g2 = reinterpret_cast<double*>(smem_raw + q.o_g2);
+    double* s_agg = reinterpret_cast<double*>(smem_raw + q.o_agg);
+    double* s_base = reinterpret_cast<double*>(smem_raw + q.o_base);
+    double* s_lsum = reinterpret_cast<double*>(smem_raw + q.o_lsum);
+    double* s_part = reinterpret_cast<double*>(smem_raw + q.o_part);
+    float* s_nf = reinterpret_cast<float*>(smem_raw + q.o_nf);
+    long long* s_lb = reinterpret_cast<long long*>(smem_raw + q.o_ctl);
+    int* s_lc = reinterpret_cast<int*>(s_lb + WF_MAX_LEV);
+    unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_lb + WF_MAX_LEV + WF_MAX_LEV / 2);
+    const int V = 2 * q.CB;
 
-    if (threadIdx.x == 0) s_ticket = atomicAdd(w.ticket, 1);
+    if (threadIdx.x == 0) {
+        s_ticket = atomicAdd(w.ticket, 1);
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned)__cvta_generic_to_shared(s_bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
-    const int rt = s_ticket / q.ncb, cb = s_ticket - rt * q.ncb;     // row tile, column block
-    const int col0 = cb * q.CB, cw = min(q.CB, q.O - col0);           // this block's columns
-    const int V = 2 * q.CB;                                           // payload doubles per tile
+    // Tiles are handed out in ticket order, so every tile above this one has started
+    const int ticket = s_ticket;
+    int rt = ticket, cb = 0;                                          // row tile, column block
+    if (q.ncb > 1) { rt = ticket / q.ncb; cb = ticket - rt * q.ncb; }
+    const int col0 = cb * q.CB, cw = min(q.CB, q.O - col0);
     const int64_t row0 = (int64_t)rt * q.R;
     const int rows = (int)min((int64_t)q.R, q.T - row0);
+    const int ld = q.CB;                                              // (CB == O for whole-row tiles)
+    const long long cb0 = (long long)cb * q.per_cb;
+    const unsigned magic = cw == q.CB ? q.magic : (cw > 1 ? 0xffffffffu / (unsigned)cw + 1u : 0u);
+    // whole-row tiles of aligned arrays travel as ONE bulk async copy each way (no registers, no LSU instructions)
+    const int nel = rows * cw;
+    const bool bulk = vec && cw == q.O && (nel & 3) == 0;
+    if (bulk) {
+        if (threadIdx.x == 0) {
+            const unsigned bar = (unsigned)__cvta_generic_to_shared(s_bar), bytes = (unsigned)nel * 4u;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             (unsigned)__cvta_generic_to_shared(s)), "l"(obs + row0 * q.O), "r"(bytes), "r"(bar) : "memory");
+        }
+    } else if (cw == q.O) {
+        for (int i = threadIdx.x; i < nel; i += WF_THREADS) s[i] = __ldcs(obs + row0 * q.O + i);
+    } else {
+        for (int i = threadIdx.x; i < nel; i += WF_THREADS) {
+            const int r = wf_div(i, cw, magic), c = i - r * cw;
+            s[r * ld + c] = __ldcs(obs + (row0 + r) * q.O + col0 + c);
+        }
+    }
     const float n0f = n[col0];                                        // read before this tile publishes anything:
     for (int c = threadIdx.x; c < cw; c += WF_THREADS) {              // the state is rewritten only by the LAST row
         s_p[c] = mean[col0 + c];                                      // tile, which waits (transitively) for every
         s_m0[c] = mean_diff[col0 + c];                                // other tile's sums
     }
-    // ---- tile -> shared memory (the only read of obs) ----
-    if (cw == q.O) {
-        const int nel = rows * q.O;
-        const int64_t off = row0 * q.O;
-        if (vec && (nel & 3) == 0) {
-            const float4* g4 = reinterpret_cast<const float4*>(obs + off);
-            float4* s4 = reinterpret_cast<float4*>(s);
-            for (int i = threadIdx.x; i < nel / 4; i += WF_THREADS) s4[i] = __ldcs(&g4[i]);
-        } else {
-            for (int i = threadIdx.x; i < nel; i += WF_THREADS) s[i] = __ldcs(obs + off + i);
-        }
-    } else {
-        for (int i = threadIdx.x; i < rows * cw; i += WF_THREADS) {
-            const int r = i / cw, c = i - r * cw;
-            s[r * q.CB + c] = __ldcs(obs + (row0 + r) * q.O + col0 + c);
-        }
-    }
-    const int ld = (cw == q.O) ? q.O : q.CB;                          // row stride of the tile in shared memory
-    __syncthreads();
-    // ---- group-local sums: item (g,c) walks rows [g*RPG, min((g+1)*RPG, rows)) of column c ----
-    for (int it = threadIdx.x; it < q.G * cw; it += WF_THREADS) {
-        const int g = it / cw, c = it - g * cw;
-        const float p = s_p[c];
-        double a1 = 0.0, a2 = 0.0;
-        const int r0 = g * q.RPG, r1 = min(r0 + q.RPG, rows);
-#pragma unroll 4
-        for (int r = r0; r < r1; ++r) {
-            const double d = (double)__fsub_rn(s[r * ld + c], p);
-            a1 += d;
-            a2 = fma(d, d, a2);
-        }
-        s_g1[g * q.CB + c] = a1;
-        s_g2[g * q.CB + c] = a2;
-    }
-    __syncthreads();
-    // ---- tile sums (fixed order over the groups), exclusive prefix of the groups in place, publish ----
-    const size_t cb0 = (size_t)cb * q.per_cb;                         // this column block's slice of pay[]
-    if (threadIdx.x < q.CB) {                                         // every word of the payload is published (readers
-        const int c = threadIdx.x;                                    // poll all 2*CB of them): zeros beyond this block's columns
-        double r1 = 0.0, r2 = 0.0;
-        for (int g = 0; g < q.G && c < cw; ++g) {
-            const double x1 = s_g1[g * q.CB + c], x2 = s_g2[g * q.CB + c];
-            s_g1[g * q.CB + c] = r1; s_g2[g * q.CB + c] = r2;
-            r1 += x1; r2 += x2;
-        }
-        s_agg[c] = r1; s_agg[q.CB + c] = r2;
-        wf_publish(&w.pay[(cb0 + rt) * V + c], r1);
-        wf_publish(&w.pay[(cb0 + rt) * V + q.CB + c], r2);
-    }
-    __syncthreads();
-    // ---- sums of all rows above this tile.  While this tile is the LAST of its group at a level it handles that
-    // level on its own and publishes the group's sums at once (a group sum needs nothing from outside the group); all
-    // remaining levels are then fetched together: one L2 round trip for a tile that completes nothing (15 of 16). ----
-    double own = threadIdx.x < V ? s_agg[threadIdx.x] : 0.0;
-    double lev_sum[WF_MAX_LEV];
-#pragma unroll
-    for (int l = 0; l < WF_MAX_LEV; ++l) lev_sum[l] = 0.0;
-    int lfirst = 0;                                                   // first level not yet summed
-    {
-        int idx = rt;
-#pragma unroll
-        for (int l = 0; l < WF_MAX_LEV; ++l) {
-            if (l + 1 >= q.nlev || idx % WF_L1 != WF_L1 - 1) break;   // I complete a group of level l+1
-            const size_t base = cb0 + q.lev_off[l] + (idx - (WF_L1 - 1));
-            for (int e = threadIdx.x; e < (WF_L1 - 1) * V; e += WF_THREADS) s_look[e] = wf_fetch(&w.pay[base * V + e]);
-            __syncthreads();
-            if (threadIdx.x < V) {
-                double sum = 0.0;
-                for (int j = 0; j < WF_L1 - 1; ++j) sum += s_look[j * V + threadIdx.x];
-                lev_sum[l] = sum;
-                own = sum + own;                                      // the 15 before me + mine
-                wf_publish(&w.pay[(cb0 + q.lev_off[l + 1] + idx / WF_L1) * V + threadIdx.x], own);
-            }
-            __syncthreads();
-            idx /= WF_L1;
-            lfirst = l + 1;
-        }
-    }
-    {
-        // the remaining levels: payload j of the combined list belongs to level L(j); staged WF_LOOK at a time
-        int cnt[WF_MAX_LEV], start[WF_MAX_LEV], total = 0;
-        size_t base[WF_MAX_LEV];
-        int idx = rt;
-#pragma unroll
-        for (int l = 0; l < WF_MAX_LEV; ++l) {
-            const int dgt = idx % WF_L1;
-            cnt[l] = (l >= lfirst && l < q.nlev) ? dgt : 0;
-            base[l] = cb0 + (l < q.nlev ? q.lev_off[l] : 0) + (idx - dgt);
-            start[l] = total;
-            total += cnt[l];
-            idx /= WF_L1;
-        }
-        for (int p0 = 0; p0 < total; p0 += WF_LOOK) {
-            const int np = min(WF_LOOK, total - p0);
-            for (int e = threadIdx.x; e < np * V; e += WF_THREADS) {
-                const int j = p0 + e / V, v = e % V;
-                int l = 0;
-#pragma unroll
-                for (int k = 1; k < WF_MAX_LEV; ++k) if (j >= start[k] && cnt[k] > 0) l = k;
-                s_look[e] = wf_fetch(&w.pay[(base[l] + (j - start[l])) * V + v]);
-            }
-            __syncthreads();
-            if (threadIdx.x < V) {
-#pragma unroll
-                for (int l = 0; l < WF_MAX_LEV; ++l) {                 // within a level in order; the levels are combined below
-                    const int j0 = max(start[l], p0), j1 = min(start[l] + cnt[l], p0 + np);
-                    for (int j = j0; j < j1; ++j) lev_sum[l] += s_look[(j - p0) * V + threadIdx.x];
-                }
-            }
-            __syncthreads();
-        }
-    }
-    if (threadIdx.x < V) {
-        const int v = threadIdx.x;
-        double above = 0.0;                                           // highest level first: a fixed order
-#pragma unroll
-        for (int l = WF_MAX_LEV - 1; l >= 0; --l) above += lev_sum[l];
-        // statistics shared by several workers: the rollouts of the workers before this one (rank order) come first
-        double prior = 0.0;
-        if (totals != nullptr) {
-            const int c = v < q.CB ? v : v - q.CB;
-            if (c < cw)
-                for (int r = 0; r < rank; ++r)
-                    prior += totals[(size_t)r * (1 + 2 * q.O) + 1 + (v < q.CB ? 0 : q.O) + col0 + c];
-        }
-        s_base[v] = prior + above;
-    }
-    __syncthreads();
-    // ---- per-row 1/n_t in fp32, once per row instead of once per element ----
-    double n0 = (double)n0f, rows_all = (double)q.T;               // rows before this rollout / rows of all workers
+    // rows of all workers before this rollout / in all (statistics shared by several workers); 1/n_t per row in fp32,
+    // once per row instead of once per element
+    double n0 = (double)n0f, rows_all = (double)q.T;
     if (totals != nullptr) {
         rows_all = 0.0;
         for (int r = 0; r < world; ++r) {
@@ -240,10 +187,104 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
             rows_all += tr;
         }
     }
-    for (int r = threadIdx.x; r < rows; r += WF_THREADS)
-        s_nf[r] = __frcp_rn((float)(n0 + (double)(row0 + r + 1)));   // n_t < 2^24 is exact in fp32
+    {
+        const double nb = n0 + (double)row0 + 1.0;
+        for (int r = threadIdx.x; r < rows; r += WF_THREADS) s_nf[r] = __frcp_rn((float)(nb + (double)r));
+    }
+    // the lists of the look-back (digit l of the tile number counts the level-l groups before mine inside my
+    // level-(l+1) group); a tile whose low digits are 15 completes those groups and sums them itself below
+    int lfirst = 0;
+#pragma unroll
+    for (int l = 0; l + 1 < WF_MAX_LEV; ++l)
+        if (lfirst == l && l + 1 < q.nlev && ((rt >> (4 * l)) & (WF_L1 - 1)) == WF_L1 - 1) lfirst = l + 1;
+    if (threadIdx.x < WF_MAX_LEV) {
+        const int l = threadIdx.x, idx = rt >> (4 * l), dgt = idx & (WF_L1 - 1);
+        s_lb[l] = cb0 + (l < q.nlev ? q.lev_off[l] : 0) + (idx - dgt);
+        s_lc[l] = l < q.nlev ? dgt : 0;                               // (levels below lfirst: 15, used by the completion)
+    }
+    if (bulk) {
+        unsigned ok = 0;
+        const unsigned bar = (unsigned)__cvta_generic_to_shared(s_bar);
+        while (!ok)
+            asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                         : "=r"(ok) : "r"(bar), "r"(0u) : "memory");
+    }
     __syncthreads();
-    // ---- the new state, by the tile that holds the last row of this column block ----
+
+    // ---- pass A: group-local sums.  Item (g,c) walks rows [g*RPG, min((g+1)*RPG, rows)) of column c ----
+    for (int it = threadIdx.x; it < q.G * cw; it += WF_THREADS) {
+        const int g = wf_div(it, cw, magic), c = it - g * cw;
+        const float p = s_p[c];
+        double a1 = 0.0, a2 = 0.0;
+        const int r0 = g * q.RPG, r1 = min(r0 + q.RPG, rows);
+        const float* ps = s + r0 * ld + c;
+        if (r1 - r0 == WF_RPG) {
+#pragma unroll 11
+            for (int k = 0; k < WF_RPG; ++k) {
+                const double d = (double)__fsub_rn(ps[k * ld], p);
+                a1 += d;
+                a2 = fma(d, d, a2);
+            }
+        } else {
+            for (int k = 0; k < r1 - r0; ++k) {
+                const double d = (double)__fsub_rn(ps[k * ld], p);
+                a1 += d;
+                a2 = fma(d, d, a2);
+            }
+        }
+        s_g1[g * q.CB + c] = a1;
+        s_g2[g * q.CB + c] = a2;
+    }
+    __syncthreads();
+    // tile sums (fixed order over the groups), exclusive prefix of the groups in place, publish
+    double own = 0.0;
+    if (threadIdx.x < V) {                                            // every word of the payload is published (readers
+        const int v = threadIdx.x, c = v < q.CB ? v : v - q.CB;       // poll all 2*CB of them): zeros beyond this block's columns
+        double* a = v < q.CB ? s_g1 : s_g2;
+        double run = 0.0;
+        if (c < cw)
+            for (int g = 0; g < q.G; ++g) {
+                const double x1 = a[g * q.CB + c];
+                a[g * q.CB + c] = run;
+                run += x1;
+            }
+        s_agg[v] = run;
+        own = run;
+        wf_publish(&w.pay[(cb0 + rt) * V + v], run);
+    }
+    // While this tile is the LAST of its group at a level it adds up that level now and publishes the group's sums
+    // at once (a group sum needs nothing from outside the group)
+    for (int l = 0; l < lfirst; ++l) {
+        __syncthreads();
+        wf_gather(w.pay, s_lb + l, s_lc + l, 1, V, q.vshift, s_part);
+        __syncthreads();
+        if (threadIdx.x < V) {
+            const double sum = s_part[threadIdx.x];
+            s_lsum[l * V + threadIdx.x] = sum;
+            own = sum + own;                                          // the 15 before me + mine
+            wf_publish(&w.pay[(cb0 + q.lev_off[l + 1] + (rt >> (4 * (l + 1)))) * V + threadIdx.x], own);
+        }
+    }
+    __syncthreads();
+    // ---- the sums of all rows above this tile: the remaining levels, all in flight together ----
+    wf_gather(w.pay + 0, s_lb + lfirst, s_lc + lfirst, q.nlev - lfirst, V, q.vshift, s_part);
+    __syncthreads();
+    if (threadIdx.x < V) {
+        const int v = threadIdx.x;
+        double above = 0.0;                                           // highest level first: a fixed order
+        for (int l = q.nlev - 1; l >= lfirst; --l) above += s_part[(l - lfirst) * V + v];
+        for (int l = lfirst - 1; l >= 0; --l) above += s_lsum[l * V + v];
+        // statistics shared by several workers: the rollouts of the workers before this one (rank order) come first
+        double prior = 0.0;
+        if (totals != nullptr) {
+            const int c = v < q.CB ? v : v - q.CB;
+            if (c < cw)
+                for (int r = 0; r < rank; ++r) prior += totals[(size_t)r * (1 + 2 * q.O) + 1 + (v < q.CB ? 0 : q.O) + col0 + c];
+        }
+        s_base[v] = prior + above;
+    }
+    __syncthreads();
+    // the new state, by the tile that holds the last row of this column block
     if (rt == q.ntr - 1 && threadIdx.x < cw) {
         const int c = threadIdx.x;
         double t1 = s_base[c] + s_agg[c], t2 = s_base[q.CB + c] + s_agg[q.CB + c];
@@ -260,14 +301,14 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
         n[col0 + c] = nn;
         mean[col0 + c] = (float)((double)s_p[c] + t1 * inv);
         mean_diff[col0 + c] = md;
-        var[col0 + c] = fmaxf(__fdiv_rn(md, nn), 1e-2f);             // model.py:75
+        var[col0 + c] = fmaxf(__fdiv_rn(md, nn), 1e-2f);               // model.py:75
     }
-    // ---- per-row statistics + normalise, in place in shared memory ----
-    // The state at the first row of a group comes from the fp64 prefix sums; from there the group's <= 33 rows follow
-    // the reference's own fp32 recurrence (model.py:71-75: mean += (x-mean)/n; M2 += (x-mean_old)(x-mean)), so no
-    // fp64 arithmetic or conversion is spent per element and no error accumulates beyond a group.
+    // ---- pass B: per-row statistics + normalise, in place in shared memory.  The state at the first row of a group
+    // comes from the fp64 prefix sums; from there the group's <= 33 rows follow the reference's own fp32 recurrence
+    // (model.py:71-75: mean += (x-mean)/n; M2 += (x-mean_old)(x-mean)), so no fp64 arithmetic or conversion is spent per
+    // element and no error accumulates beyond a group.
     for (int it = threadIdx.x; it < q.G * cw; it += WF_THREADS) {
-        const int g = it / cw, c = it - g * cw;
+        const int g = wf_div(it, cw, magic), c = it - g * cw;
         const int r0 = g * q.RPG, r1 = min(r0 + q.RPG, rows);
         if (r0 >= r1) continue;
         const double ng = n0 + (double)(row0 + r0);                  // rows before the group
@@ -278,37 +319,47 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
             mean_f = (float)((double)s_p[c] + t);
             m2_f = (float)((double)s_m0[c] + a2 - a1 * t);
         }
-#pragma unroll 4
-        for (int r = r0; r < r1; ++r) {
-            const float x = s[r * ld + c], inv = s_nf[r];
-            const float d = __fsub_rn(x, mean_f);                    // x - mean_old
+        float* ps = s + r0 * ld + c;
+        const float* pn = s_nf + r0;
+        auto row = [&](int k) {
+            const float xv = ps[k * ld], inv = pn[k];
+            const float d = __fsub_rn(xv, mean_f);                   // x - mean_old
             mean_f = fmaf(d, inv, mean_f);                           // model.py:73
-            const float e = __fsub_rn(x, mean_f);                    // x - mean
+            const float e = __fsub_rn(xv, mean_f);                   // x - mean
             m2_f = fmaf(d, e, m2_f);                                 // model.py:74
             // var = max(M2/n, 1e-2), xhat = (x-mean)/sqrt(var) (model.py:75-80) as multiply-by-reciprocal and
             // rsqrt.approx (2 ulp): var >= 1e-2, so no denormal handling is needed
             const float var_t = fmaxf(m2_f * inv, 1e-2f);
             float rs;
             asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(var_t));
-            s[r * ld + c] = fminf(fmaxf(e * rs, -5.f), 5.f);
+            ps[k * ld] = fminf(fmaxf(e * rs, -5.f), 5.f);
+        };
+        if (r1 - r0 == WF_RPG) {
+#pragma unroll 11
+            for (int k = 0; k < WF_RPG; ++k) row(k);
+        } else {
+            for (int k = 0; k < r1 - r0; ++k) row(k);
         }
     }
-    __syncthreads();
-    // ---- stream the tile out (the only write) ----
-    if (cw == q.O) {
-        const int nel = rows * q.O;
-        const int64_t off = row0 * q.O;
-        if (vec && (nel & 3) == 0) {
-            float4* o4 = reinterpret_cast<float4*>(out + off);
-            const float4* s4 = reinterpret_cast<const float4*>(s);
-            for (int i = threadIdx.x; i < nel / 4; i += WF_THREADS) __stcs(&o4[i], s4[i]);
-        } else {
-            for (int i = threadIdx.x; i < nel; i += WF_THREADS) __stcs(out + off + i, s[i]);
+    // stream the tile out (the only write)
+    if (bulk) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // the rows were written through the generic proxy
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + row0 * q.O),
+                         "r"((unsigned)__cvta_generic_to_shared(s)), "r"((unsigned)nel * 4u) : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the tile must outlive the copy's reads
         }
+        return;
+    }
+    __syncthreads();
+    if (cw == q.O) {
+        for (int i = threadIdx.x; i < nel; i += WF_THREADS) __stcs(out + row0 * q.O + i, s[i]);
     } else {
-        for (int i = threadIdx.x; i < rows * cw; i += WF_THREADS) {
-            const int r = i / cw, c = i - r * cw;
-            __stcs(out + (row0 + r) * q.O + col0 + c, s[r * q.CB + c]);
+        for (int i = threadIdx.x; i < nel; i += WF_THREADS) {
+            const int r = wf_div(i, cw, magic), c = i - r * cw;
+            __stcs(out + (row0 + r) * q.O + col0 + c, s[r * ld + c]);
         }
     }
 }
@@ -368,7 +419,7 @@ WfGeom wf_geom(int64_t T, int O) {
     // the same banks: half of all shared-memory wavefronts were conflicts)
     q.G = WF_THREADS / q.CB;
     if (q.G < 1) q.G = 1;
-    q.RPG = 33;
+    q.RPG = WF_RPG;
     while (q.RPG > 1 && (int64_t)q.G * q.RPG > WF_MAX_ROWS) q.RPG -= 2;
     q.R = (q.G * q.RPG) & ~3;                       // multiple of 4 rows keeps whole-row tiles 16-byte aligned
     if (q.R < 4) q.R = 4;
@@ -389,14 +440,23 @@ WfGeom wf_geom(int64_t T, int O) {
         n = (n + WF_L1 - 1) / WF_L1;                // groups one level up (the last may be partial: never read)
     }
     q.per_cb = off;
+    q.magic = q.CB > 1 ? 0xffffffffu / (unsigned)q.CB + 1u : 0u;
+    q.vshift = 2 * q.CB <= 32 ? 5 : 6;
+    const int V = 2 * q.CB;
+    size_t o = sizeof(float) * (((size_t)q.R * q.CB + 3) & ~(size_t)3);
+    q.o_p = (int)o; o += sizeof(float) * WF_CB;
+    q.o_m0 = (int)o; o += sizeof(float) * WF_CB;
+    q.o_g1 = (int)o; o += sizeof(double) * q.G * q.CB;
+    q.o_g2 = (int)o; o += sizeof(double) * q.G * q.CB;
+    q.o_agg = (int)o; o += sizeof(double) * V;
+    q.o_base = (int)o; o += sizeof(double) * V;
+    q.o_lsum = (int)o; o += sizeof(double) * q.nlev * V;
+    q.o_part = (int)o; o += sizeof(double) * q.nlev * V;
+    q.o_nf = (int)o; o += sizeof(float) * (((size_t)q.R + 3) & ~(size_t)3);
+    o = (o + 15) & ~(size_t)15;
+    q.o_ctl = (int)o; o += sizeof(long long) * (WF_MAX_LEV + WF_MAX_LEV / 2) + 16;
+    q.smem = (int)o;
     return q;
-}
-
-size_t wf_smem_bytes(const WfGeom& q) {
-    const size_t look = sizeof(double) * WF_LOOK * 2 * q.CB;
-    const size_t tables = sizeof(float) * (size_t)q.R;
-    return sizeof(float) * ((size_t)q.R * q.CB + 2 * WF_CB) + sizeof(double) * (2 * (size_t)q.G * q.CB + 4 * WF_CB) +
-           (look > tables ? look : tables) + 16;
 }
 
 size_t wf_pay_bytes(const WfGeom& q) { return sizeof(uint4) * 2 * q.CB * (size_t)q.ncb * (size_t)q.per_cb; }
@@ -406,8 +466,7 @@ size_t wf_pay_bytes(const WfGeom& q) { return sizeof(uint4) * 2 * q.CB * (size_t
 // scratch: int ticket | LL payload words (see WfScratch), cleared per call
 extern "C" size_t dppo_welford_scratch_bytes(int64_t T, int O) {
     if (T <= 0 || O <= 0) return 16;
-    const WfGeom q = wf_geom(T, O);
-    return 16 + wf_pay_bytes(q);
+    return 16 + wf_pay_bytes(wf_geom(T, O));
 }
 
 extern "C" size_t dppo_welford_totals_scratch_bytes(int64_t T, int O) {
@@ -453,6 +512,7 @@ static int welford_launch(const float* obs, float* out, int64_t T, int O, float*
     if (T == 0) return 0;
     if (!obs || !out || !n || !mean || !mean_diff || !var || !scratch) return DPPO_E_BADARG;
     if (O > 4096) return DPPO_E_TOOLARGE;
+    const bool vec = aligned16(obs) && aligned16(out);
     const WfGeom q = wf_geom(T, O);
     if ((int64_t)q.ntr * q.ncb > 0x3fffffff) return DPPO_E_TOOLARGE;
     if (scratch_bytes < dppo_welford_scratch_bytes(T, O)) return DPPO_E_SCRATCH;
@@ -461,8 +521,7 @@ static int welford_launch(const float* obs, float* out, int64_t T, int O, float*
     WfScratch w;
     w.ticket = (int*)scratch;
     w.pay = (uint4*)((char*)scratch + 16);
-    const bool vec = aligned16(obs) && aligned16(out);
-    const size_t smem = wf_smem_bytes(q);
+    const size_t smem = (size_t)q.smem;
     static size_t smem_set[64] = {0};                             // per device
     int dev = 0;
     DPPO_CUDA_TRY(cudaGetDevice(&dev));
@@ -472,8 +531,7 @@ static int welford_launch(const float* obs, float* out, int64_t T, int O, float*
         smem_set[dev] = smem;
     }
     DPPO_CUDA_TRY(cudaMemsetAsync(scratch, 0, 16 + wf_pay_bytes(q), stream));      // ticket + the LL tags
-    wf_fused_kernel<<<q.ntr * q.ncb, WF_THREADS, smem, stream>>>(obs, out, q, n, mean, mean_diff, var, w, vec, totals,
-                                                                  rank, world);
+    wf_fused_kernel<<<q.ntr * q.ncb, WF_THREADS, smem, stream>>>(obs, out, q, n, mean, mean_diff, var, w, vec, totals, rank, world);
     DPPO_LAUNCH_CHECK();
     return 0;
 }

@@ -174,6 +174,36 @@ def test_welford_in_place_and_large(nv):
     assert float(st[0][0]) == T
 
 
+@pytest.mark.parametrize("T,O,inplace", [((1 << 19) + 13, 17, False), (1 << 19, 17, True), ((1 << 21) + 460, 4, False),
+                                         (300001, 31, True)])
+def test_welford_long_rollouts(nv, T, O, inplace):
+    """Rollouts of thousands of tiles (three and four levels of the look-back hierarchy, tiles moved by bulk async
+    copies, the ragged last tile by the threads): checked against fp64 prefix statistics, against a second run bit
+    for bit, and - on the first rows - against the sequential oracle."""
+    g = torch.Generator().manual_seed(T + O)
+    obs = (0.5 + 2.0 * torch.randn(T, O, generator=g))
+    outs = []
+    for rep in range(2):
+        X = obs.to(DEV)
+        Y = X if inplace else torch.empty_like(X)
+        st = [torch.zeros(O, device=DEV) for _ in range(4)]
+        nv.welford(X, Y, st[0], st[1], st[2], st[3], _u8(nv.welford_scratch_bytes(T, O)))
+        torch.cuda.synchronize()
+        outs.append((Y.clone(), torch.stack(st)))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    x64 = obs.double()
+    n = torch.arange(1, T + 1, dtype=torch.float64)[:, None]
+    mean = x64.cumsum(0) / n
+    m2 = (x64 ** 2).cumsum(0) - n * mean ** 2
+    ref = ((x64 - mean) / (m2 / n).clamp_min(1e-2).sqrt()).clamp(-5, 5)
+    assert_close_scaled(outs[0][0].cpu(), ref, 2e-5, "prefix-normalised")
+    assert float(outs[0][1][0][0]) == T
+    assert_close_scaled(outs[0][1][1].cpu(), mean[-1], 1e-5, "final mean")
+    ost = orc.welford_new(O)
+    want = orc.welford_observe_normalize(ost, obs[:3000])
+    assert_close_scaled(outs[0][0][:3000].cpu(), want, 1e-5, "first rows vs the sequential oracle")
+
+
 # ---------------------------------------------------------------- K3 reduce + clip + Adam
 @pytest.mark.parametrize("nparts,clipnorm", [(1, 0.0), (5, 0.0), (147, 0.0), (3, 0.5), (3, 1e9)])
 def test_reduce_adam_vs_oracle(nv, nparts, clipnorm):
