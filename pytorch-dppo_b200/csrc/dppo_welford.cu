@@ -37,8 +37,14 @@ constexpr int WF_THREADS = 256;
 constexpr int WF_CB = 32;                           // widest column block
 constexpr int WF_L1 = 16;                           // radix of the hierarchy
 constexpr int WF_MAX_LEV = 6;                       // 16^6 tiles
-constexpr int WF_RPG = 33;                          // rows per group of a full tile (the unrolled case of both passes)
-constexpr int WF_MAX_ROWS = 8448;                   // bounds the per-row reciprocal table (256 groups x 33 rows, O = 1)
+#ifndef WF_RPG_V
+#define WF_RPG_V 33
+#define WF_UNROLL_V 11
+#define WF_MINB_V 5
+#endif
+constexpr int WF_UNROLL = WF_UNROLL_V;
+constexpr int WF_RPG = WF_RPG_V;                          // rows per group of a full tile (the unrolled case of both passes)
+constexpr int WF_MAX_ROWS = 256 * WF_RPG;                   // bounds the per-row reciprocal table (256 groups x 33 rows, O = 1)
 constexpr int WF_INFL = 4;                          // look-back loads a thread keeps in flight (4 parts x 4 >= 15)
 
 struct WfGeom {
@@ -51,7 +57,7 @@ struct WfGeom {
     int lev_off[WF_MAX_LEV];                        // offset of level l in the per-column-block arrays
     int per_cb;                                     // entries per column block over all levels
     unsigned magic;                                 // floor(2^32 / CB) + 1: it / CB == umulhi(it, magic) for it < 2^32 / CB
-    int vshift;                                     // 2*CB <= 1 << vshift (5 or 6): word index of a look-back slot by mask
+    int nblk;                                       // ceil(2*CB / 8): blocks of 8 payload words (look-back slots)
     // shared memory carve-up (bytes from the start of the dynamic region); the tile is at 0
     int o_p, o_m0, o_g1, o_g2, o_agg, o_base, o_lsum, o_part, o_nf, o_ctl, smem;
 };
@@ -85,25 +91,32 @@ __device__ __forceinline__ double wf_value(const uint4& v) {
 // tickets are handed out in order; 8 lanes read 128 contiguous bytes), and two butterfly steps add the parts as
 // (p0+p1)+(p2+p3) - a fixed tree, so the result does not depend on timing.   part[u*V + word].
 __device__ __forceinline__ void wf_gather(const uint4* __restrict__ pay, const long long* lb, const int* lc, const int nlists,
-                                          const int V, const int vshift, double* part) {
-    const int slots = nlists << (vshift + 2);                         // lists x (words rounded up to 32 or 64) x 4 parts
-    for (int e = threadIdx.x; e < slots; e += WF_THREADS) {           // (whole warps: slots is a multiple of 32)
+                                          const int V, const int nblk, double* part) {
+    const int slots = nlists * nblk * 32;                             // lists x blocks of 8 words x 4 parts: whole warps
+    const unsigned inv = 65536u / (unsigned)nblk + 1u;                // blk / nblk for blk < 6 * 8
+    for (int e = threadIdx.x; e < slots; e += WF_THREADS) {
         const int h = (e >> 3) & 3, blk = e >> 5;
-        const int v = ((blk & ((1 << (vshift - 3)) - 1)) << 3) + (e & 7), u = blk >> (vshift - 3);
+        const int u = (int)(((unsigned)blk * inv) >> 16);
+        const int v = ((blk - u * nblk) << 3) + (e & 7);
         const int n = v < V ? min(lc[u] - h * WF_INFL, WF_INFL) : 0;
         double sum = 0.0;
-        if (n > 0) {
-            const uint4* p = pay + (lb[u] + h * WF_INFL) * V + v;
-            uint4 wv[WF_INFL];
+        const uint4* p = pay + (lb[u] + h * WF_INFL) * V + v;
+        uint4 wv[WF_INFL];
 #pragma unroll
-            for (int k = 0; k < WF_INFL; ++k)
-                if (k < n) wv[k] = wf_look(p + k * V);
+        for (int k = 0; k < WF_INFL; ++k)
+            if (k < n) wv[k] = wf_look(p + k * V);
 #pragma unroll
-            for (int k = 0; k < WF_INFL; ++k)
-                if (k < n) {
-                    while (!wf_there(wv[k])) wv[k] = wf_look(p + k * V);
-                    sum += wf_value(wv[k]);
+        for (int k = 0; k < WF_INFL; ++k) {                           // polling keeps the warp converged (the butterfly
+            bool need = k < n && !wf_there(wv[k]);                    // below wants all 32 lanes)
+#ifdef WF_X_NO_WAIT
+            need = false;
+#endif
+            while (__any_sync(0xffffffffu, need))
+                if (need) {
+                    wv[k] = wf_look(p + k * V);
+                    need = !wf_there(wv[k]);
                 }
+            if (k < n) sum += wf_value(wv[k]);
         }
         sum += __shfl_xor_sync(0xffffffffu, sum, 8);
         sum += __shfl_xor_sync(0xffffffffu, sum, 16);
@@ -111,12 +124,27 @@ __device__ __forceinline__ void wf_gather(const uint4* __restrict__ pay, const l
     }
 }
 
+// Experiment builds (tools/build_variant.py --file dppo_welford.cu <name> -D...; never the shipped library; the
+// WF_X_* ones give wrong results and exist for timing only - profiles/r02_k4_summary.md has the numbers):
+//   DPPO_K4_TIMING      phase clocks      WF_X_COPY_ONLY=1   tile in, tile out, nothing else
+//   WF_X_NO_LOOKBACK    no look-back      WF_X_NO_WAIT       look-back loads without waiting for the tags
+//   WF_X_LEVEL0_ONLY    look-back of level 0 only
+#ifdef DPPO_K4_TIMING
+// phase clocks of an experiment build (tools/build_variant.py --file dppo_welford.cu k4timing -DDPPO_K4_TIMING):
+// thread 0 of every CTA adds the nanoseconds between marks
+__device__ unsigned long long wf_phase_ns[8];
+__device__ __forceinline__ unsigned long long wf_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define WF_MARK(i) do { if (threadIdx.x == 0) { const unsigned long long t_ = wf_now(); atomicAdd(&wf_phase_ns[i], t_ - t_mark); t_mark = t_; } } while (0)
+#else
+#define WF_MARK(i) do { } while (0)
+#endif
+
 // it / d for it < 2^32 / d with magic = floor(2^32 / d) + 1 (d > 1)
 __device__ __forceinline__ int wf_div(int it, int d, unsigned magic) { return d == 1 ? it : (int)__umulhi((unsigned)it, magic); }
 
 // dynamic smem: float tile[R*CB] | float p[CB], M0[CB] | double g1[G*CB], g2[G*CB], agg[2*CB], base[2*CB],
 //               lsum[nlev][2*CB], part[nlev][2*CB] | float nf[R] | long long lb[WF_MAX_LEV]; int lc[WF_MAX_LEV]; mbarrier
-__global__ void __launch_bounds__(WF_THREADS, 5)
+__global__ void __launch_bounds__(WF_THREADS, WF_MINB_V)
 wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const WfGeom q, float* __restrict__ n,
                 float* __restrict__ mean, float* __restrict__ mean_diff, float* __restrict__ var, const WfScratch w,
                 const bool vec, const double* __restrict__ totals, const int rank, const int world) {
@@ -136,6 +164,9 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
     int* s_lc = reinterpret_cast<int*>(s_lb + WF_MAX_LEV);
     unsigned long long* s_bar = reinterpret_cast<unsigned long long*>(s_lb + WF_MAX_LEV + WF_MAX_LEV / 2);
     const int V = 2 * q.CB;
+#ifdef DPPO_K4_TIMING
+    unsigned long long t_mark = wf_now();
+#endif
 
     if (threadIdx.x == 0) {
         s_ticket = atomicAdd(w.ticket, 1);
@@ -143,6 +174,7 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
+    WF_MARK(0);                                                       // ticket
     // Tiles are handed out in ticket order, so every tile above this one has started
     const int ticket = s_ticket;
     int rt = ticket, cb = 0;                                          // row tile, column block
@@ -210,7 +242,19 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
                          : "=r"(ok) : "r"(bar), "r"(0u) : "memory");
     }
     __syncthreads();
+    WF_MARK(1);                                                       // tile in shared memory
 
+#ifdef WF_X_COPY_ONLY                                                 // timing experiment: load + store only
+    if (bulk) {
+        if (threadIdx.x == 0) {
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + row0 * q.O),
+                         "r"((unsigned)__cvta_generic_to_shared(s)), "r"((unsigned)nel * 4u) : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        }
+        return;
+    }
+#endif
     // ---- pass A: group-local sums.  Item (g,c) walks rows [g*RPG, min((g+1)*RPG, rows)) of column c ----
     for (int it = threadIdx.x; it < q.G * cw; it += WF_THREADS) {
         const int g = wf_div(it, cw, magic), c = it - g * cw;
@@ -219,7 +263,7 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
         const int r0 = g * q.RPG, r1 = min(r0 + q.RPG, rows);
         const float* ps = s + r0 * ld + c;
         if (r1 - r0 == WF_RPG) {
-#pragma unroll 11
+#pragma unroll WF_UNROLL
             for (int k = 0; k < WF_RPG; ++k) {
                 const double d = (double)__fsub_rn(ps[k * ld], p);
                 a1 += d;
@@ -236,6 +280,7 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
         s_g2[g * q.CB + c] = a2;
     }
     __syncthreads();
+    WF_MARK(2);                                                       // pass A
     // tile sums (fixed order over the groups), exclusive prefix of the groups in place, publish
     double own = 0.0;
     if (threadIdx.x < V) {                                            // every word of the payload is published (readers
@@ -256,7 +301,7 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
     // at once (a group sum needs nothing from outside the group)
     for (int l = 0; l < lfirst; ++l) {
         __syncthreads();
-        wf_gather(w.pay, s_lb + l, s_lc + l, 1, V, q.vshift, s_part);
+        wf_gather(w.pay, s_lb + l, s_lc + l, 1, V, q.nblk, s_part);
         __syncthreads();
         if (threadIdx.x < V) {
             const double sum = s_part[threadIdx.x];
@@ -266,9 +311,15 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
         }
     }
     __syncthreads();
+    WF_MARK(3);                                                       // published (+ completed groups)
     // ---- the sums of all rows above this tile: the remaining levels, all in flight together ----
-    wf_gather(w.pay + 0, s_lb + lfirst, s_lc + lfirst, q.nlev - lfirst, V, q.vshift, s_part);
+#if defined(WF_X_LEVEL0_ONLY)
+    wf_gather(w.pay + 0, s_lb + lfirst, s_lc + lfirst, lfirst == 0 ? 1 : 0, V, q.nblk, s_part);
+#elif !defined(WF_X_NO_LOOKBACK)
+    wf_gather(w.pay + 0, s_lb + lfirst, s_lc + lfirst, q.nlev - lfirst, V, q.nblk, s_part);
+#endif
     __syncthreads();
+    WF_MARK(4);                                                       // look-back
     if (threadIdx.x < V) {
         const int v = threadIdx.x;
         double above = 0.0;                                           // highest level first: a fixed order
@@ -335,7 +386,7 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
             ps[k * ld] = fminf(fmaxf(e * rs, -5.f), 5.f);
         };
         if (r1 - r0 == WF_RPG) {
-#pragma unroll 11
+#pragma unroll WF_UNROLL
             for (int k = 0; k < WF_RPG; ++k) row(k);
         } else {
             for (int k = 0; k < r1 - r0; ++k) row(k);
@@ -345,12 +396,14 @@ wf_fused_kernel(const float* __restrict__ obs, float* __restrict__ out, const Wf
     if (bulk) {
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // the rows were written through the generic proxy
         __syncthreads();
+        WF_MARK(5);                                                   // pass B
         if (threadIdx.x == 0) {
             asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + row0 * q.O),
                          "r"((unsigned)__cvta_generic_to_shared(s)), "r"((unsigned)nel * 4u) : "memory");
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the tile must outlive the copy's reads
         }
+        WF_MARK(6);                                                   // store read out
         return;
     }
     __syncthreads();
@@ -441,7 +494,7 @@ WfGeom wf_geom(int64_t T, int O) {
     }
     q.per_cb = off;
     q.magic = q.CB > 1 ? 0xffffffffu / (unsigned)q.CB + 1u : 0u;
-    q.vshift = 2 * q.CB <= 32 ? 5 : 6;
+    q.nblk = (2 * q.CB + 7) / 8;
     const int V = 2 * q.CB;
     size_t o = sizeof(float) * (((size_t)q.R * q.CB + 3) & ~(size_t)3);
     q.o_p = (int)o; o += sizeof(float) * WF_CB;
@@ -462,6 +515,14 @@ WfGeom wf_geom(int64_t T, int O) {
 size_t wf_pay_bytes(const WfGeom& q) { return sizeof(uint4) * 2 * q.CB * (size_t)q.ncb * (size_t)q.per_cb; }
 
 }  // namespace
+
+#ifdef DPPO_K4_TIMING
+extern "C" int dppo_welford_phase_ns(unsigned long long* out8, int reset) {
+    DPPO_CUDA_TRY(cudaMemcpyFromSymbol(out8, wf_phase_ns, sizeof(unsigned long long) * 8));
+    if (reset) { unsigned long long z[8] = {0}; DPPO_CUDA_TRY(cudaMemcpyToSymbol(wf_phase_ns, z, sizeof(z))); }
+    return 0;
+}
+#endif
 
 // scratch: int ticket | LL payload words (see WfScratch), cleared per call
 extern "C" size_t dppo_welford_scratch_bytes(int64_t T, int O) {
