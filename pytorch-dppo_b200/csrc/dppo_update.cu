@@ -47,6 +47,7 @@ __device__ long long g_k2_clock[64];
 #endif
 #ifdef DPPO_K2_TRACE
 __device__ long long g_k2_trace[4 * 64 * 8];
+__device__ const float* g_k2_trace_bias;            // trace the forward layer with this bias vector (null: the wide ones)
 #define K2_TR(role, gp, ev) do { if (trace_on && lane == 0) g_k2_trace[(((role) * 64 + (gp)) << 3) + (ev)] = clock64() - trace_t0; } while (0)
 #else
 #define K2_TR(role, gp, ev) do { } while (0)
@@ -632,7 +633,7 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
     };
     __syncthreads();                                        // previous users of the staging region are done
 #ifdef DPPO_K2_TRACE
-    const bool trace_on = blockIdx.x == 0 && !DX && K > 256;
+    const bool trace_on = blockIdx.x == 0 && !DX && (g_k2_trace_bias ? bias == g_k2_trace_bias : K > 256);
     const long long trace_t0 = clock64();
 #endif
     if (warp == 6) {
@@ -2373,6 +2374,9 @@ extern "C" int dppo_policy_forward(const dppo_dims* d, const float* states, int 
 }
 
 #ifdef DPPO_K2_TRACE
+extern "C" int dppo_debug_k2_trace_bias(const float* bias_dev) {
+    return (int)cudaMemcpyToSymbol(g_k2_trace_bias, &bias_dev, sizeof(bias_dev));
+}
 extern "C" int dppo_debug_k2_trace(long long* out_host) {
     return (int)cudaMemcpyFromSymbol(out_host, g_k2_trace, sizeof(long long) * 4 * 64 * 8);
 }

@@ -10,6 +10,10 @@ idx=torch.randperm(T,device='cuda')[:B].int()
 npart=nv.update_nparts(m.dims,B)
 parts=torch.empty(npart,m.P_pad,device='cuda');lp=torch.empty(npart,4,device='cuda')
 old=m.flat.clone()
+import os
+if os.environ.get('K2_TRACE_PARAM'):          # name of the bias whose forward layer is traced, e.g. p_fc2.bias / v_fc2.bias
+    off=m.offsets[nv.PARAM_NAMES.index(os.environ['K2_TRACE_PARAM'])]
+    nv.lib.dppo_debug_k2_trace_bias(ctypes.c_void_p(m.flat.data_ptr()+4*off))
 for _ in range(3):
     nv.update_fused(0,m.dims,obs,act,adv,ret,None,idx,m.flat,old,0.2,0.0,parts,lp)
 torch.cuda.synchronize()
