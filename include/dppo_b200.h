@@ -135,6 +135,13 @@ int dppo_welford_shared(const float* obs, float* out, int64_t T, int O,
  *   loss_partials         OUT [nparts][4] per-CTA sums of the loss terms
  *                         (clip, value, entropy, unused), already scaled
  * Deterministic: no atomics, fixed reduction order. */
+/* Large minibatches of nets whose hidden layers all run on the tensor-core routines take two launches: the update
+ * kernel leaves every layer's input and dz feature-major in an internal per-device buffer, a second pass forms all
+ * weight gradients from it as batch-level GEMMs over 4 ranges of samples - dppo_update_nparts is then 4 instead of
+ * one partial per CTA.  The buffer is allocated by dppo_update_prepare (or by the first plain call; a call that
+ * finds it missing while its stream is being captured returns DPPO_E_SCRATCH).  DPPO_K2_DWG=0 in the environment
+ * keeps the single-launch form.  No reference counterpart (autograd forms dW inside loss.backward(), train.py:162). */
+int    dppo_update_prepare(const dppo_dims* d, int B);
 int    dppo_update_nparts(const dppo_dims* d, int B);
 size_t dppo_update_partials_bytes(const dppo_dims* d, int B);
 int dppo_update_fused(int flavour, const dppo_dims* d,

@@ -75,6 +75,7 @@ class UpdateEngine:
         self.m = torch.zeros_like(self.theta)
         self.v = torch.zeros_like(self.theta)
         self.step = 0
+        nv.update_prepare(self.dims, self.B)
         self.nparts = nv.update_nparts(self.dims, self.B)
         self.partials = torch.empty(self.nparts, self.P_pad, device=dev)
         self.loss_partials = torch.empty(self.nparts, 4, device=dev)

@@ -66,6 +66,7 @@ def _load():
         "dppo_welford_shared": (i32, [vp, vp, i64, i32, vp, vp, vp, vp, vp, i32, i32, vp, sz, vp]),
         "dppo_comm_allgather": (i32, [vp, vp, vp, i32, vp]),
         "dppo_comm_allgather_loopback": (i32, [c.POINTER(vp), i32, c.POINTER(vp), c.POINTER(vp), i32, vp]),
+        "dppo_update_prepare": (i32, [dp, i32]),
         "dppo_update_nparts": (i32, [dp, i32]),
         "dppo_update_partials_bytes": (sz, [dp, i32]),
         "dppo_update_fused": (i32, [i32, dp, vp, vp, vp, vp, vp, vp, i32, vp, vp, flt, flt, vp, vp, vp]),
@@ -198,6 +199,11 @@ def comm_allgather_loopback(comms, srcs, dsts):
     s = (vp * W)(*[_ptr(t, torch.float64) for t in srcs])
     d = (vp * W)(*[_ptr(t, torch.float64) for t in dsts])
     check(lib.dppo_comm_allgather_loopback(cc, W, s, d, srcs[0].numel(), _stream()))
+
+
+def update_prepare(dims, B):
+    """Allocate the library's per-device buffer of the two-launch update (large minibatches); call before a graph capture."""
+    check(lib.dppo_update_prepare(ctypes.byref(dims), B))
 
 
 def update_nparts(dims, B):

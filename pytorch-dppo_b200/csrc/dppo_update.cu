@@ -122,6 +122,16 @@ struct UpdArgs {
     const float* eps;                               // [B][A] standard-normal draws (nullable: action = mu)
     float *f_mu, *f_v, *f_act, *f_logp, *f_obs;     // output columns (nullable), row r of the batch lands in row
     long long f_row0, f_stride;                     //   f_row0 + r * f_stride  (straight into the SoA rollout buffer)
+    // batch-level dW (dwg): 0 off.  1: the update kernel forms no dW; it leaves every layer's input and every dz
+    // feature-major in Z ([rows][Bp], Bp = 32 * tiles) and its loss sums in zloss.  2: the dW pass over Z - CTA =
+    // (range of samples, parameter, 32 input features, 128 outputs), one wide-layer call whose "weights" are dz^T.
+    int dwg, Bp, dwg_units, dwg_chunk, zloss_rows;
+    float* Z;
+    float* zloss;                                   // [zloss_rows][4]
+    int zr_x, zr_h1, zr_g1, zr_h2, zr_g2;           // first rows of the input operands (Kf rows, the ones row, pad to 32)
+    int zr_d1p, zr_d1v, zr_d2p, zr_d2v, zr_dmu, zr_dv;   // first rows of dz: p_fc1, v_fc1, p_fc2, v_fc2, [dmu | dls], dv
+    alignas(64) CUtensorMap map_dz[6];              // dz^T of v_fc2, p_fc2, v_fc1, p_fc1, mu (+ log_std), v: box 32 (samples) x 128 (n)
+    alignas(64) CUtensorMap map_in[5];              // the inputs x^T, h1^T, g1^T, h2^T, g2^T (+ ones rows): box 32 (samples) x 32 (kf), no swizzle
     alignas(64) CUtensorMap map_fwd[2][4];          // [theta, theta_old][W2, V2, W1, V1]: box 32 (k) x 128 (n), SWIZZLE_128B
     alignas(64) CUtensorMap map_dx[2];              // theta's W2, V2 for dX: box 128 (k) x 32 (n), no swizzle
 };
@@ -542,6 +552,16 @@ __device__ __forceinline__ void tma_pair_elect(uint32_t dst0, uint32_t dst1, con
         "@t cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2, {%6, %7}], [%3];\n\t}"
         ::"r"(dst0), "r"(dst1), "l"(map), "r"(bar), "r"(a0), "r"(b0), "r"(a1), "r"(b1), "r"(bytes), "r"(two) : "memory");
 }
+// two more tiles onto a barrier whose arrival comes later (tma_pair_elect): only the byte count is announced here
+__device__ __forceinline__ void tma_pair_more_elect(uint32_t dst0, uint32_t dst1, const CUtensorMap* map, int a0, int b0, int a1, int b1,
+                                                    uint32_t bar, uint32_t bytes, uint32_t two) {
+    asm volatile(
+        "{\n\t.reg .pred e, t;\n\tsetp.ne.b32 t, %9, 0;\n\telect.sync _|e, 0xffffffff;\n\tand.pred t, t, e;\n\t"
+        "@e mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%3], %8;\n\t"
+        "@e cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%2, {%4, %5}], [%3];\n\t"
+        "@t cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2, {%6, %7}], [%3];\n\t}"
+        ::"r"(dst0), "r"(dst1), "l"(map), "r"(bar), "r"(a0), "r"(b0), "r"(a1), "r"(b1), "r"(bytes), "r"(two) : "memory");
+}
 __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
                  "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
@@ -561,13 +581,17 @@ __device__ __forceinline__ void ts_split(float x, uint32_t& hi, uint32_t& lo) {
     hi = __float_as_uint(h);
     lo = __float_as_uint(x - h);
 }
-// the same block by ONE warp, straight-line: lane = (row group of 4, chunk), eight rows per lane, loads first
-__device__ __forceinline__ void ts_stage_block_warp(unsigned char* bh, const float* src, int ld, int k0, int K, int lane) {
+// the same block by ONE warp, straight-line: lane = (row group of 4, chunk), eight rows per lane.  Load and store are
+// separate so that the loads of the next block can be in flight while the warp waits for its slot (the 32-row operand
+// of the batch-level dW pass comes from global memory)
+__device__ __forceinline__ void ts_block_load(float4 (&xv)[8], const float* src, int ld, int k0, int K, int lane) {
     const int kc = lane & 7, m0 = lane >> 3, k = k0 + 4 * kc;
-    float4 xv[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i)
-        xv[i] = (k < K) ? *reinterpret_cast<const float4*>(src + (m0 + 4 * i) * ld + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        xv[i] = (k < K) ? *reinterpret_cast<const float4*>(src + (size_t)(m0 + 4 * i) * ld + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+}
+__device__ __forceinline__ void ts_block_store(unsigned char* bh, const float4 (&xv)[8], int lane) {
+    const int kc = lane & 7, m0 = lane >> 3;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         uint32_t hh[4], ll[4];
@@ -576,6 +600,11 @@ __device__ __forceinline__ void ts_stage_block_warp(unsigned char* bh, const flo
         *reinterpret_cast<uint4*>(bh + o) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
         *reinterpret_cast<uint4*>(bh + TS_BT_BYTES + o) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
     }
+}
+__device__ __forceinline__ void ts_stage_block_warp(unsigned char* bh, const float* src, int ld, int k0, int K, int lane) {
+    float4 xv[8];
+    ts_block_load(xv, src, ld, k0, K, lane);
+    ts_block_store(bh, xv, lane);
 }
 // the 32 samples' columns [k0, k0+32) of src[32][ld] -> [hi | lo] K-major tiles, by `nthr` threads (t = 0..nthr-1)
 __device__ __forceinline__ void ts_stage_samples(unsigned char* bh, const float* src, int ld, int k0, int K, int t, int nthr) {
@@ -605,10 +634,28 @@ __device__ __forceinline__ void ts_stage_samples(unsigned char* bh, const float*
 //             tiles of 128 k, the rings run across tiles, the accumulators are drained between tiles.
 // ---------------------------------------------------------------------------
 constexpr int TS_PH_RF = 10;
+// Extras of a wide-layer call (all zero / null for a plain layer):
+//   kofs/row0  offsets of the TMA coordinates (reduction index / first tile row)
+//   dwg        batch-level dW pass: the "weights" are dz^T [n][samples] (feature-major, TMA), the 32-row operand is a
+//              block of 32 input features in^T [kf][samples] read from global memory, the reduction runs over a range
+//              of samples, and out[kf][n] = dW[n][kf] goes to this split's partial bucket instead of the activations:
+//              gW[n * ldw + kf0 + kf] for kf0 + kf < Kf, the column kf0 + kf == Kf (the ones row) is the bias gradient
+//              gb[n]; rows n >= n1 keep only that column (gb2[n - n1] + add2: d log_std rides with the mu head).
+//              The 32-row operand's blocks arrive by TMA too (bmap, rows brow0.., raw tiles in braw) on the same barrier
+//              as the dz tiles; the sample warps split them from shared memory as in every other layer.
+struct TsX {
+    int kofs, row0;
+    int dwg;
+    const CUtensorMap* bmap; int brow0; float* braw;   // dwg: the 32-row operand's blocks by TMA (box 32 x 32) into braw[slot][block][32][32]
+    float *gW, *gb, *gb2;
+    int ldw, kf0, Kf, n1;
+    float add2;
+};
 template <bool DX>
 __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* __restrict__ bias, int N, int K,
                                           const float* bsrc, int ldb, float* dst, int ldo, unsigned char* ts, uint64_t* bars,
-                                          unsigned ph, uint32_t tmem) {
+                                          unsigned ph, uint32_t tmem, const TsX& Xref) {
+    const TsX X = Xref;                                     // in registers: nothing below may reload it after a store
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int R = DX ? N : K;                               // reduction length
     const int nrb = (R + TC_KB - 1) / TC_KB;                // k-blocks per tile
@@ -628,8 +675,13 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
         const uint32_t two = (nrb - 2 * p >= 2) ? 1u : 0u;
         const uint32_t d0 = smem_u32(raw + (2 * s) * TS_RAW_BYTES), bar = smem_u32(&raw_full[s]);
         const int blk = 2 * p;
+        if (!DX && X.bmap != nullptr) {                      // dwg: the 32-row operand's two blocks (4 KB each) first
+            const uint32_t b0 = smem_u32(X.braw + (2 * s) * 1024);
+            tma_pair_more_elect(b0, b0 + 4096, X.bmap, TC_KB * blk + X.kofs, X.brow0, TC_KB * (blk + 1) + X.kofs, X.brow0, bar,
+                                (1u + two) * 4096u, two);
+        }
         if (DX) tma_pair_elect(d0, d0 + TS_RAW_BYTES, map, 128 * mt, TC_KB * blk, 128 * mt, TC_KB * (blk + 1), bar, (1u + two) * TS_RAW_BYTES, two);
-        else tma_pair_elect(d0, d0 + TS_RAW_BYTES, map, TC_KB * blk, 128 * mt, TC_KB * (blk + 1), 128 * mt, bar, (1u + two) * TS_RAW_BYTES, two);
+        else tma_pair_elect(d0, d0 + TS_RAW_BYTES, map, TC_KB * blk + X.kofs, 128 * mt + X.row0, TC_KB * (blk + 1) + X.kofs, 128 * mt + X.row0, bar, (1u + two) * TS_RAW_BYTES, two);
     };
     __syncthreads();                                        // previous users of the staging region are done
 #ifdef DPPO_K2_TRACE
@@ -721,7 +773,12 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                 K2_TR(1, gp, 0);
                 if (gp >= 2) mbar_wait(&mma_done[s], par(TS_PH_MD + s, u - 1));
                 K2_TR(1, gp, 1);
-                if (blk < nrb) ts_stage_block_warp(bst + (2 * s + i) * 2 * TS_BT_BYTES, bsrc, ldb, blk * TC_KB, R, lane);
+                if (!DX && X.bmap != nullptr) {             // dwg: this pair's raw blocks have landed with the dz tiles
+                    mbar_wait(&raw_full[s], par(TS_PH_RAW + s, u));
+                    if (blk < nrb) ts_stage_block_warp(bst + (2 * s + i) * 2 * TS_BT_BYTES, X.braw + (2 * s + i) * 1024, 32, 0, 32, lane);
+                } else if (blk < nrb) {
+                    ts_stage_block_warp(bst + (2 * s + i) * 2 * TS_BT_BYTES, bsrc, ldb, blk * TC_KB, R, lane);
+                }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&a_full[s]);
@@ -733,6 +790,8 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                 if (gp + 2 < NP) {
                     K2_TR(2, gp, 0);
                     mbar_wait(&raw_free[gp & 1], par(TS_PH_RF + (gp & 1), gp >> 1));
+                    if (!DX && X.bmap != nullptr)           // dwg: the sample warps have read their raw blocks too
+                        mbar_wait(&a_full[gp & 1], par(TS_PH_AF + (gp & 1), gp >> 1));
                     K2_TR(2, gp, 1);
                     tma_pair(gp + 2);
                     K2_TR(2, gp, 2);
@@ -780,7 +839,7 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
         // ---------------- epilogue: lane = feature, this warp's 16 samples; the four small halves first ----------------
         {
             const int q = warp & 3, f = 128 * mt + 32 * q + lane, c0 = 16 * (warp >> 2);
-            const float bb = (!DX && f < N) ? __ldg(bias + f) : 0.f;   // forward: bias of my feature (in flight during the loads)
+            const float bb = (!DX && bias != nullptr && f < N) ? __ldg(bias + f) : 0.f;   // forward: bias of my feature (in flight during the loads)
             float sum[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j) sum[j] = 0.f;
@@ -802,13 +861,35 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                     for (int j = 0; j < 16; ++j) {
                         float* ap = dst + (c0 + j) * ldo + f;
                         const float h = *ap;
-                        *ap = sum[j] * (1.f - h * h);
+                        sum[j] *= 1.f - h * h;
+                        *ap = sum[j];
                     }
+                }
+            } else if (X.dwg) {
+                const int n = X.row0 + f;                   // f counts from the first tile row of this call
+                if (n < X.n1) {
+                    float* row = X.gW + (size_t)n * X.ldw;
+                    const int kfa = X.kf0 + c0;
+                    if ((X.ldw & 3) == 0 && kfa + 16 <= X.Kf) {       // whole 64 bytes inside the row, 16-byte aligned
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            reinterpret_cast<float4*>(row + kfa)[j] = make_float4(sum[4 * j], sum[4 * j + 1], sum[4 * j + 2], sum[4 * j + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            if (kfa + j < X.Kf) row[kfa + j] = sum[j];
+                            else if (kfa + j == X.Kf) X.gb[n] = sum[j];
+                        }
+                    }
+                } else if (n < N + X.row0 && X.gb2 != nullptr) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        if (X.kf0 + c0 + j == X.Kf) X.gb2[n - X.n1] = sum[j] + X.add2;
                 }
             } else {
                 if (f < N) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) dst[(c0 + j) * ldo + f] = tanh_act(sum[j] + bb);
+                    for (int j = 0; j < 16; ++j) { sum[j] = tanh_act(sum[j] + bb); dst[(c0 + j) * ldo + f] = sum[j]; }
                 }
             }
         }
@@ -913,9 +994,12 @@ __device__ __noinline__ unsigned fwd_first_ts(const float* Ws, const float* __re
             tmem_ld_issue<16>(tb, v[1]);
             tmem_ld_wait();
             if (n < N) {
+                float o[16];
 #pragma unroll
-                for (int j = 0; j < 16; ++j)
-                    out[(c0 + j) * ldout + n] = tanh_act((__uint_as_float(v[0][j]) + __uint_as_float(v[1][j])) + bb[t]);
+                for (int j = 0; j < 16; ++j) {
+                    o[j] = tanh_act((__uint_as_float(v[0][j]) + __uint_as_float(v[1][j])) + bb[t]);
+                    out[(c0 + j) * ldout + n] = o[j];
+                }
             }
         }
     }
@@ -1015,8 +1099,10 @@ __device__ __forceinline__ unsigned fwd_layer(const float* __restrict__ W, const
                                           const float* in, int ldin, float* out, int ldout, float* stage, int SF,
                                           uint64_t* bars, unsigned ph, uint32_t tmem, const CUtensorMap* wmap) {
     // wide GEMM-shaped layers go to the tensor cores (tcgen05), the rest stays on the FP32 pipe
-    if (wmap != nullptr && N >= 32 && K >= 64 && (K & 3) == 0)          // = ts_eligible() on the host
-        return ts_layer<false>(wmap, bias, N, K, in, ldin, out, ldout, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
+    if (wmap != nullptr && N >= 32 && K >= 64 && (K & 3) == 0) {        // = ts_eligible() on the host
+        TsX x = {};
+        return ts_layer<false>(wmap, bias, N, K, in, ldin, out, ldout, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, x);
+    }
     // 4*CN columns per warp: 28 fits N = 100 (reference widths) in four blocks, 32 otherwise
     const int blocks32 = (N + 31) / 32;
     if (N > 28 * (blocks32 - 1) && N <= 28 * blocks32 && blocks32 <= 8)
@@ -1193,8 +1279,10 @@ __device__ __noinline__ unsigned dx_layer_t(const float* __restrict__ W, int N, 
 __device__ __forceinline__ unsigned dx_layer(const float* __restrict__ W, int N, int K, const float* dOut, int ldd,
                                          float* act, int lda, float* stage, int SF, uint64_t* bars, unsigned ph,
                                          const CUtensorMap* xmap, uint32_t tmem) {
-    if (xmap != nullptr && N >= 32 && K >= 64 && (K & 3) == 0)               // = ts_eligible() on the host
-        return ts_layer<true>(xmap, nullptr, N, K, dOut, ldd, act, lda, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem);
+    if (xmap != nullptr && N >= 32 && K >= 64 && (K & 3) == 0) {             // = ts_eligible() on the host
+        TsX x = {};
+        return ts_layer<true>(xmap, nullptr, N, K, dOut, ldd, act, lda, reinterpret_cast<unsigned char*>(stage), bars, ph, tmem, x);
+    }
     const int KQ = (K + 3) >> 2;
     if (KQ > UPD_THREADS / 4) return dx_layer_t<4>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
     if (KQ > UPD_THREADS / 8) return dx_layer_t<2>(W, N, K, dOut, ldd, act, lda, stage, SF, bars, ph);
@@ -1631,6 +1719,21 @@ __device__ void block_sum3(float a, float b, float c, float* r0, float* r12, flo
     __syncthreads();
 }
 
+// features [0, nf) of a sample-major shared-memory array (32 rows of ld floats, ld a multiple of 4) -> feature-major
+// rows of Z, this tile's 32 columns.  A warp takes four features at a time: lane = sample, one 128-bit load along the
+// features, four stores of a whole 128-byte row each.
+__device__ __forceinline__ void z_dump(float* zrow0, int zld, const float* src, int ld, int nf) {
+    const int warp = threadIdx.x >> 5, m = threadIdx.x & 31;
+    for (int f = 4 * warp; f < nf; f += 4 * (UPD_THREADS / 32)) {
+        const float4 v = *reinterpret_cast<const float4*>(src + m * ld + f);
+        float* z = zrow0 + (size_t)f * zld + m;
+        z[0] = v.x;
+        if (f + 1 < nf) z[zld] = v.y;
+        if (f + 2 < nf) z[2 * (size_t)zld] = v.z;
+        if (f + 3 < nf) z[3 * (size_t)zld] = v.w;
+    }
+}
+
 __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __grid_constant__ UpdArgs P) {
     extern __shared__ __align__(1024) float S[];
     const dppo_dims& d = P.d;
@@ -1663,6 +1766,57 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot;
     unsigned ph = 0;
+    if (P.dwg == 2) {
+        // ---- batch-level dW pass: dW[n][kf] = sum over this CTA's range of samples of dz[s][n] * in[s][kf] ----------
+        // One wide-layer call per CTA: "weights" = dz^T (rows n, TMA from Z), 32-row operand = the 32 input features
+        // kf0.. of in^T (rows of Z, read by the sample warps), reduction over the samples; the ones row behind every
+        // input operand makes column Kf the bias gradient.  The split's partial bucket gets every element once.
+        const int split = blockIdx.x / P.dwg_units;
+        int u = blockIdx.x - split * P.dwg_units;
+        const int s0 = split * P.dwg_chunk, ns = min(P.dwg_chunk, P.Bp - s0);
+        float* bucket = P.partials + (size_t)split * P.lay.P_pad;
+        const GradOut gs = grad_of(bucket, P.lay);
+        if (u == 0) {
+            if (threadIdx.x < DPPO_N_PARAMS)                           // padding floats of the bucket stay 0
+                for (int j = P.lay.size[threadIdx.x]; j < ((P.lay.size[threadIdx.x] + 3) & ~3); ++j)
+                    bucket[P.lay.off[threadIdx.x] + j] = 0.f;
+            if (threadIdx.x < 4) {                                    // the update kernel's loss sums, rows in order
+                const int nsp = gridDim.x / P.dwg_units;
+                const int r0 = (int)((long long)P.zloss_rows * split / nsp), r1 = (int)((long long)P.zloss_rows * (split + 1) / nsp);
+                float a = 0.f;
+                for (int r = r0; r < r1; ++r) a += P.zloss[4 * r + threadIdx.x];
+                P.loss_partials[4 * split + threadIdx.x] = a;
+            }
+        }
+        for (int p = 0; p < 6 && ns > 0; ++p) {
+            int Np, Kf, zin, n1;
+            float *gW, *gb, *gb2 = nullptr;
+            int im;                                                   // which input operand (map_in)
+            if (p == 0) { Np = d.G2; Kf = d.G1; zin = P.zr_g1; im = 2; gW = gs.V2; gb = gs.c2; n1 = Np; }
+            else if (p == 1) { Np = d.H2; Kf = d.H1; zin = P.zr_h1; im = 1; gW = gs.W2; gb = gs.b2; n1 = Np; }
+            else if (p == 2) { Np = d.G1; Kf = d.O; zin = P.zr_x; im = 0; gW = gs.V1; gb = gs.c1; n1 = Np; }
+            else if (p == 3) { Np = d.H1; Kf = d.O; zin = P.zr_x; im = 0; gW = gs.W1; gb = gs.b1; n1 = Np; }
+            else if (p == 4) { Np = 2 * d.A; Kf = d.H2; zin = P.zr_h2; im = 3; gW = gs.Wmu; gb = gs.bmu; gb2 = gs.ls; n1 = d.A; }
+            else { Np = 1; Kf = d.G2; zin = P.zr_g2; im = 4; gW = gs.Wv; gb = gs.bv; n1 = Np; }
+            const int kfb = (Kf + 1 + 31) >> 5, nt = (Np + 127) >> 7;
+            if (u >= kfb * nt) { u -= kfb * nt; continue; }
+            const int t = u / kfb, b = u - t * kfb;
+            TsX x = {};
+            x.dwg = 1; x.kofs = s0; x.row0 = 128 * t;
+            x.gW = gW; x.gb = gb; x.gb2 = gb2; x.ldw = Kf; x.kf0 = 32 * b; x.Kf = Kf; x.n1 = n1;
+            x.add2 = (P.flavour == DPPO_FLAVOUR_PPO && split == 0) ? -P.ent_coeff : 0.f;     // ppo.py:152-153,167
+            x.bmap = &P.map_in[im]; x.brow0 = 32 * b; x.braw = S;                           // (the activation area is free in this pass)
+            ph = ts_layer<false>(&P.map_dz[p], nullptr, min(128, Np - 128 * t), ns, P.Z + (size_t)(zin + 32 * b) * P.Bp + s0, P.Bp,
+                                 nullptr, 0, reinterpret_cast<unsigned char*>(S + P.o_stage),
+                                 reinterpret_cast<uint64_t*>(S + P.o_bars), ph, tmem, x);
+            break;
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x < 32)
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+        return;
+    }
     // head weights of both networks stay in shared memory for the whole kernel
     // (when shared memory is tight - Humanoid with 256-wide nets - they are read from global memory instead)
     if (P.heads_in_smem) {
@@ -1680,7 +1834,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
             hs_old.Wmu = no.Wmu; hs_old.bmu = no.bmu; hs_old.Wv = no.Wv; hs_old.bv = no.bv; hs_old.ldw = d.H2;
         }
     }
-    if (threadIdx.x < DPPO_N_PARAMS && !P.fwd_only)                    // padding floats of the bucket stay 0
+    if (threadIdx.x < DPPO_N_PARAMS && !P.fwd_only && !P.dwg)          // padding floats of the bucket stay 0
         for (int j = P.lay.size[threadIdx.x]; j < ((P.lay.size[threadIdx.x] + 3) & ~3); ++j)
             part[P.lay.off[threadIdx.x] + j] = 0.f;
     float lsum_clip = 0.f, lsum_val = 0.f, lsum_ent = 0.f;           // this thread's share of the loss sums
@@ -1739,6 +1893,14 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
             if (P.flavour == DPPO_FLAVOUR_PPO) S[P.o_lpo + m] = __ldg(P.logp_old + r);
         }
         __syncthreads();
+        if (P.dwg) {                                                      // batch-level dW: x^T and the ones rows of the five inputs
+            z_dump(P.Z + (size_t)P.zr_x * P.Bp + tile * UPD_ROWS, P.Bp, S + P.o_x, P.ldO, d.O);
+            for (int e = threadIdx.x; e < 5 * UPD_ROWS; e += UPD_THREADS) {
+                const int o = e >> 5, m = e & 31;
+                const int r = o == 0 ? P.zr_x + d.O : o == 1 ? P.zr_h1 + d.H1 : o == 2 ? P.zr_g1 + d.G1 : o == 3 ? P.zr_h2 + d.H2 : P.zr_g2 + d.G2;
+                P.Z[(size_t)r * P.Bp + tile * UPD_ROWS + m] = 1.f;
+            }
+        }
 
         K2_TICK(2);
         const float lo = 1.f - P.clip, hi = 1.f + P.clip;               // clamp bounds (train.py:151)
@@ -1981,6 +2143,13 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
             ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr, &nw);              // train.py:142
         ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr, nullptr);                    // train.py:145 / ppo.py:148
         if (P.fwd_only) { write_policy_outputs(); continue; }
+        if (P.dwg) {                                                      // batch-level dW: the layers' inputs, feature-major
+            float* zc = P.Z + tile * UPD_ROWS;
+            z_dump(zc + (size_t)P.zr_h1 * P.Bp, P.Bp, S + P.o_h1, P.ldH1, d.H1);
+            z_dump(zc + (size_t)P.zr_g1 * P.Bp, P.Bp, S + P.o_g1, P.ldG1, d.G1);
+            z_dump(zc + (size_t)P.zr_h2 * P.Bp, P.Bp, S + P.o_h2, P.ldH2, d.H2);
+            z_dump(zc + (size_t)P.zr_g2 * P.Bp, P.Bp, S + P.o_g2, P.ldG2, d.G2);
+        }
         if (same_old) {
             for (int e = threadIdx.x; e < UPD_ROWS * P.ldA; e += UPD_THREADS) S[P.o_muo + e] = S[P.o_mu + e];
             for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
@@ -1990,6 +2159,28 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         loss_value();
         __syncthreads();
         K2_TICK(13);
+        if (P.dwg) {
+            // ---- backward, batch-level dW: only the dz chain runs here; every dz goes to Z next to the layer inputs
+            // the forward pass left there, and the dW pass (second launch) forms all weight gradients from them
+            float* zc = P.Z + tile * UPD_ROWS;                             // this tile's 32 columns of Z
+            z_dump(zc + (size_t)P.zr_dmu * P.Bp, P.Bp, S + P.o_dmu, P.ldA, d.A);
+            z_dump(zc + (size_t)(P.zr_dmu + d.A) * P.Bp, P.Bp, S + P.o_muo, P.ldA, d.A);      // dls (kept in the mu_old buffer)
+            z_dump(zc + (size_t)P.zr_dv * P.Bp, P.Bp, S + P.o_dv, 4, 1);
+            head_dx(hs_new.Wmu, hs_new.ldw, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2);          // h2 <- dz2
+            head_dx(hs_new.Wv, 0, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);                          // g2 <- dz2 (value)
+            __syncthreads();
+            z_dump(zc + (size_t)P.zr_d2p * P.Bp, P.Bp, S + P.o_h2, P.ldH2, d.H2);
+            z_dump(zc + (size_t)P.zr_d2v * P.Bp, P.Bp, S + P.o_g2, P.ldG2, d.G2);
+            K2_TICK(17);
+            ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, &P.map_dx[0], tmem);   // h1 <- dz1
+            K2_TICK(20);
+            ph = dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, &P.map_dx[1], tmem);   // g1 <- dz1 (value)
+            z_dump(zc + (size_t)P.zr_d1p * P.Bp, P.Bp, S + P.o_h1, P.ldH1, d.H1);
+            z_dump(zc + (size_t)P.zr_d1v * P.Bp, P.Bp, S + P.o_g1, P.ldG1, d.G1);
+            __syncthreads();                                              // the next tile zeroes the activation area
+            K2_TICK(21);
+            continue;
+        }
         dls_reduce();
         __syncthreads();
 
@@ -2032,7 +2223,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
     float sc, sv, se;                                                 // the three loss sums in one pass over the tree
     block_sum3(lsum_clip, lsum_val, lsum_ent, red, S + P.o_mu, sc, sv, se);
     if (threadIdx.x == 0 && !P.fwd_only) {
-        float* lp = P.loss_partials + 4 * blockIdx.x;
+        float* lp = (P.dwg ? P.zloss : P.loss_partials) + 4 * blockIdx.x;
         if (P.flavour == DPPO_FLAVOUR_DPPO) {
             const float BA = (float)P.B * (float)d.A;
             lp[0] = -sc / BA;
@@ -2244,6 +2435,105 @@ const MapEntry* wide_layer_maps(int dev, const float* theta, const float* theta_
 
 constexpr int MAX_DEVICES = 64;
 
+// ---- batch-level dW (see UpdArgs::dwg) ------------------------------------------------------------------------
+// Used when every hidden layer runs on the tensor-core routines (their epilogues hold a feature's 16 samples in
+// registers, which is the layout Z wants), the trunks have their own activation buffers and the minibatch is large
+// enough for the second launch to pay.  The decision depends on (dims, B, the K2 path, DPPO_K2_DWG) only, so
+// dppo_update_nparts and dppo_update_fused agree.
+constexpr int DWG_KSPLIT = 4;                       // ranges of samples = gradient partials handed to K3
+constexpr int DWG_MIN_B = 1024;
+struct DwgGeom { int on, Bp, rows, units, chunk, nk2; int zr[11]; };
+int g_dwg_enabled = -1;
+bool dwg_enabled() {
+    if (g_dwg_enabled < 0) g_dwg_enabled = getenv("DPPO_K2_DWG") ? atoi(getenv("DPPO_K2_DWG")) : 1;   // (2: timing experiment, first launch only)
+    return g_dwg_enabled != 0;
+}
+DwgGeom dwg_geom(const dppo_dims& d, int B) {
+    DwgGeom G;
+    memset(&G, 0, sizeof(G));
+    if (!dwg_enabled() || k2_path() != DPPO_K2_PATH_AUTO || B < DWG_MIN_B) return G;
+    UpdArgs Q;                                      // the shared-memory plan decides which routines run
+    memset(&Q, 0, sizeof(Q));
+    Q.d = d; Q.B = B;
+    int np;
+    pick_tiling(B, &Q.TM, &np);
+    plan(Q);
+    if (Q.trunk_serial || (size_t)2 * Q.SF * sizeof(float) < (size_t)TS_BYTES) return G;
+    if (!ts_eligible(d.H2, d.H1) || !ts_eligible(d.G2, d.G1)) return G;
+    const bool first_small = Q.small_first && Q.first_ts && d.H1 <= 512 && d.G1 <= 512;
+    if (!first_small && !(ts_eligible(d.H1, d.O) && ts_eligible(d.G1, d.O))) return G;
+    const int ntiles = (B + Q.TM - 1) / Q.TM;
+    G.on = 1;
+    G.nk2 = np;
+    G.Bp = ntiles * UPD_ROWS;
+    int r = 0;
+    auto in_rows = [&](int kf) { const int at = r; r += (kf + 1 + 31) & ~31; return at; };   // Kf rows + the ones row, pad to 32
+    G.zr[0] = in_rows(d.O); G.zr[1] = in_rows(d.H1); G.zr[2] = in_rows(d.G1); G.zr[3] = in_rows(d.H2); G.zr[4] = in_rows(d.G2);
+    auto dz_rows = [&](int n) { const int at = r; r += n; return at; };
+    G.zr[5] = dz_rows(d.H1); G.zr[6] = dz_rows(d.G1); G.zr[7] = dz_rows(d.H2); G.zr[8] = dz_rows(d.G2);
+    G.zr[9] = dz_rows(2 * d.A); G.zr[10] = dz_rows(1);
+    G.rows = r;
+    auto units = [](int Np, int Kf) { return ((Kf + 1 + 31) >> 5) * ((Np + 127) >> 7); };
+    G.units = units(d.G2, d.G1) + units(d.H2, d.H1) + units(d.G1, d.O) + units(d.H1, d.O) + units(2 * d.A, d.H2) + units(1, d.G2);
+    G.chunk = ((G.Bp + DWG_KSPLIT - 1) / DWG_KSPLIT + 63) & ~63;
+    return G;
+}
+size_t dwg_scratch_bytes(const DwgGeom& G) { return sizeof(float) * ((size_t)G.rows * G.Bp + 4 * (size_t)G.nk2) + 256; }
+
+// the per-device Z buffer (grown on demand; never while the stream is being captured into a graph)
+void* g_zbuf[64] = {nullptr};
+size_t g_zcap[64] = {0};
+int dwg_scratch(int dev, size_t bytes, cudaStream_t stream, float** out) {
+    if (g_zcap[dev] < bytes) {
+        cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+        if (stream != nullptr && cudaStreamIsCapturing(stream, &st) == cudaSuccess && st != cudaStreamCaptureStatusNone)
+            return DPPO_E_SCRATCH;                  // dppo_update_prepare (or one plain call) must come before the capture
+        if (g_zbuf[dev]) {
+            DPPO_CUDA_TRY(cudaDeviceSynchronize());
+            DPPO_CUDA_TRY(cudaFree(g_zbuf[dev]));
+            g_zbuf[dev] = nullptr; g_zcap[dev] = 0;
+        }
+        DPPO_CUDA_TRY(cudaMalloc(&g_zbuf[dev], bytes));
+        g_zcap[dev] = bytes;
+    }
+    *out = (float*)g_zbuf[dev];
+    return 0;
+}
+struct DzMaps { int dev; const float* Z; dppo_dims d; int Bp; bool ok; CUtensorMap m[6]; CUtensorMap in[5]; };
+DzMaps g_dzmaps[64];
+const DzMaps* dz_maps(int dev, float* Z, const dppo_dims& d, const DwgGeom& G) {
+    DzMaps& e = g_dzmaps[dev];
+    if (e.Z == Z && e.Bp == G.Bp && e.dev == dev && memcmp(&e.d, &d, sizeof(d)) == 0 && e.ok) return &e;
+    e.dev = dev; e.Z = Z; e.d = d; e.Bp = G.Bp;
+    const int rows[6] = {G.zr[8], G.zr[7], G.zr[6], G.zr[5], G.zr[9], G.zr[10]};          // v_fc2, p_fc2, v_fc1, p_fc1, mu, v
+    const int n[6] = {d.G2, d.H2, d.G1, d.H1, 2 * d.A, 1};
+    bool ok = true;
+    for (int i = 0; i < 6 && ok; ++i)
+        ok = make_wmap(&e.m[i], Z + (size_t)rows[i] * G.Bp, n[i], G.Bp, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
+    const int kf[5] = {d.O, d.H1, d.G1, d.H2, d.G2};                                      // inputs: Kf rows + ones, padded to 32
+    for (int i = 0; i < 5 && ok; ++i)
+        ok = make_wmap(&e.in[i], Z + (size_t)G.zr[i] * G.Bp, (kf[i] + 1 + 31) & ~31, G.Bp, TC_KB, 32, CU_TENSOR_MAP_SWIZZLE_NONE);
+    e.ok = ok;
+    return &e;
+}
+
+}  // namespace
+
+extern "C" int dppo_update_prepare(const dppo_dims* d, int B) {
+    const int rc = check_dims(d);
+    if (rc) return rc;
+    if (B < 1) return DPPO_E_BADARG;
+    const DwgGeom G = dwg_geom(*d, B);
+    if (!G.on) return 0;
+    int dev = 0;
+    DPPO_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return DPPO_E_BADARG;
+    float* z;
+    return dwg_scratch(dev, dwg_scratch_bytes(G), nullptr, &z);
+}
+
+namespace {
+
 }  // namespace
 
 // per-device caches below are indexed by the CUDA device ordinal: one host thread per device, any number of
@@ -2284,7 +2574,7 @@ extern "C" int dppo_update_nparts(const dppo_dims* d, int B) {
     if (B < 1) return DPPO_E_BADARG;
     int TM, np;
     pick_tiling(B, &TM, &np);
-    return np;
+    return dwg_geom(*d, B).on ? DWG_KSPLIT : np;
 }
 
 extern "C" size_t dppo_update_partials_bytes(const dppo_dims* d, int B) {
@@ -2293,6 +2583,7 @@ extern "C" size_t dppo_update_partials_bytes(const dppo_dims* d, int B) {
     fill_layout(*d, L);
     int TM, np;
     pick_tiling(B, &TM, &np);
+    if (dwg_geom(*d, B).on) np = DWG_KSPLIT;
     return sizeof(float) * (size_t)np * L.P_pad;
 }
 
@@ -2326,8 +2617,28 @@ static int plan_and_launch(UpdArgs& P, const dppo_dims* d, int B, const float* t
         DPPO_CUDA_TRY(cudaFuncSetAttribute(update_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         smem_set[dev] = smem;
     }
+    const DwgGeom G = P.fwd_only ? DwgGeom{} : dwg_geom(*d, B);
+    if (G.on) {
+        if (!P.use_ts) return DPPO_E_TOOLARGE;                  // (the tensor maps could not be made)
+        float* z;
+        const int rc = dwg_scratch(dev, dwg_scratch_bytes(G), (cudaStream_t)stream_, &z);
+        if (rc) return rc;
+        const DzMaps* zm = dz_maps(dev, z, *d, G);
+        if (!zm->ok) return DPPO_E_TOOLARGE;
+        memcpy(P.map_dz, zm->m, sizeof(P.map_dz));
+        memcpy(P.map_in, zm->in, sizeof(P.map_in));
+        P.dwg = 1; P.Bp = G.Bp; P.dwg_units = G.units; P.dwg_chunk = G.chunk; P.zloss_rows = nparts;
+        P.Z = z; P.zloss = z + (size_t)G.rows * G.Bp;
+        P.zr_x = G.zr[0]; P.zr_h1 = G.zr[1]; P.zr_g1 = G.zr[2]; P.zr_h2 = G.zr[3]; P.zr_g2 = G.zr[4];
+        P.zr_d1p = G.zr[5]; P.zr_d1v = G.zr[6]; P.zr_d2p = G.zr[7]; P.zr_d2v = G.zr[8]; P.zr_dmu = G.zr[9]; P.zr_dv = G.zr[10];
+    }
     update_fused_kernel<<<nparts, UPD_THREADS, smem, (cudaStream_t)stream_>>>(P);
     DPPO_LAUNCH_CHECK();
+    if (G.on && g_dwg_enabled != 2) {                           // second launch: all weight gradients from Z
+        P.dwg = 2;
+        update_fused_kernel<<<G.units * DWG_KSPLIT, UPD_THREADS, smem, (cudaStream_t)stream_>>>(P);
+        DPPO_LAUNCH_CHECK();
+    }
     return 0;
 }
 

@@ -21,9 +21,9 @@ buf=(ctypes.c_longlong*(4*64*8))()
 nv.lib.dppo_debug_k2_trace(buf)
 def ev(role,gp,e): return buf[((role*64+gp)<<3)+e]
 print('pair | A: start raw-seen split0 md-seen st-done arrived | B: start md-seen arrived | TMA: start free-seen issued | I: start af-seen committed [tile-done]')
-for gp in range(8):
+for gp in range(int(os.environ.get('K2_TRACE_PAIRS','8'))):
     print('%4d | %6d %6d %6d %6d %6d %6d | %6d %6d %6d | %6d %6d %6d | %6d %6d %6d %6d'%((gp,)+tuple(ev(0,gp,e) for e in range(6))+tuple(ev(1,gp,e) for e in range(3))+tuple(ev(2,gp,e) for e in range(3))+tuple(ev(3,gp,e) for e in range(4))))
 print('A detail (relative to start): raw-seen split0 md-seen st0-done split1-done st1-done arrived')
-for gp in range(8):
+for gp in range(int(os.environ.get('K2_TRACE_PAIRS','8'))):
     b=ev(0,gp,0); print('%4d | %s'%(gp,' '.join('%6d'%(ev(0,gp,e)-b) for e in (1,2,3,6,7,4,5))))
 print('epilogue: start %d end %d'%(ev(0,63,0),ev(0,63,1)))
