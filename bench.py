@@ -438,7 +438,8 @@ def main():
         "timing": "each kernel replayed %d x back to back from its own CUDA graph (events around the replay); the step is "
                   "one graph of all of them" % kt["reps"],
         "kernels": {
-            "k2_update_fused": {"us": kt["k2_us"], "launches_per_step": wl["E"]},
+            "k2_update_fused": {"us": kt["k2_us"], "launches_per_step": wl["E"] * engine.k2_launches,
+                                "what": "one dppo_update_fused call" + (" = the update kernel + the batch-level dW pass (same kernel, second launch)" if engine.k2_launches == 2 else "")},
             "k3_reduce_adam": {"us": kt["k3_us"], "launches_per_step": wl["E"] * k3_launches,
                                "hbm_gbs": (K3_BYTES_PER_PARAM * P + 4.0 * P * engine.nparts) / (kt["k3_us"] * 1e-6) / 1e9},
             "k1_gae_scan": {"us": kt["k1_us"], "launches_per_step": 1,

@@ -139,9 +139,13 @@ int dppo_welford_shared(const float* obs, float* out, int64_t T, int O,
  * kernel leaves every layer's input and dz feature-major in an internal per-device buffer, a second pass forms all
  * weight gradients from it as batch-level GEMMs over 4 ranges of samples - dppo_update_nparts is then 4 instead of
  * one partial per CTA.  The buffer is allocated by dppo_update_prepare (or by the first plain call; a call that
- * finds it missing while its stream is being captured returns DPPO_E_SCRATCH).  DPPO_K2_DWG=0 in the environment
- * keeps the single-launch form.  No reference counterpart (autograd forms dW inside loss.backward(), train.py:162). */
+ * finds it missing while its stream is being captured returns DPPO_E_SCRATCH); it is shared by all calls on a device,
+ * which must therefore be ordered on one stream, and it only grows (captured graphs keep pointing at the buffer they
+ * were captured with).  DPPO_K2_DWG=0 in the environment or dppo_update_set_batch_dw(0) keeps the single-launch form -
+ * the choice changes dppo_update_nparts, so make it before buffers are sized.  No reference counterpart (autograd forms dW inside loss.backward(), train.py:162). */
 int    dppo_update_prepare(const dppo_dims* d, int B);
+int    dppo_update_set_batch_dw(int on);                  /* returns the previous setting */
+int    dppo_update_launches(const dppo_dims* d, int B);   /* kernels one dppo_update_fused call launches: 1 or 2 */
 int    dppo_update_nparts(const dppo_dims* d, int B);
 size_t dppo_update_partials_bytes(const dppo_dims* d, int B);
 int dppo_update_fused(int flavour, const dppo_dims* d,

@@ -76,6 +76,7 @@ class UpdateEngine:
         self.v = torch.zeros_like(self.theta)
         self.step = 0
         nv.update_prepare(self.dims, self.B)
+        self.k2_launches = nv.update_launches(self.dims, self.B)
         self.nparts = nv.update_nparts(self.dims, self.B)
         self.partials = torch.empty(self.nparts, self.P_pad, device=dev)
         self.loss_partials = torch.empty(self.nparts, 4, device=dev)
@@ -176,7 +177,7 @@ class UpdateEngine:
             nv.update_fused(self.flavour, self.dims, buf.obs, buf.act, buf.adv, buf.ret,
                             buf.logp if self.flavour == nv.FLAVOUR_PPO else None, self.idx_dev[k], self.theta,
                             old, self.clip, self.ent_coeff, self.partials, self.loss_partials)
-            n += 1
+            n += self.k2_launches
             if self.comm is not None:
                 n += self.comm.allreduce_adam(self, k, gshared)
             else:

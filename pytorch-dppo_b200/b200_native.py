@@ -67,6 +67,8 @@ def _load():
         "dppo_comm_allgather": (i32, [vp, vp, vp, i32, vp]),
         "dppo_comm_allgather_loopback": (i32, [c.POINTER(vp), i32, c.POINTER(vp), c.POINTER(vp), i32, vp]),
         "dppo_update_prepare": (i32, [dp, i32]),
+        "dppo_update_launches": (i32, [dp, i32]),
+        "dppo_update_set_batch_dw": (i32, [i32]),
         "dppo_update_nparts": (i32, [dp, i32]),
         "dppo_update_partials_bytes": (sz, [dp, i32]),
         "dppo_update_fused": (i32, [i32, dp, vp, vp, vp, vp, vp, vp, i32, vp, vp, flt, flt, vp, vp, vp]),
@@ -204,6 +206,20 @@ def comm_allgather_loopback(comms, srcs, dsts):
 def update_prepare(dims, B):
     """Allocate the library's per-device buffer of the two-launch update (large minibatches); call before a graph capture."""
     check(lib.dppo_update_prepare(ctypes.byref(dims), B))
+
+
+def update_set_batch_dw(on):
+    """Two-launch update with the batch-level dW pass (default for large minibatches) on/off; returns the previous
+    setting.  Changes update_nparts: set it before partial buffers are sized."""
+    return lib.dppo_update_set_batch_dw(1 if on else 0)
+
+
+def update_launches(dims, B):
+    """Kernels one update_fused call launches (2 for the large-minibatch form with the batch-level dW pass)."""
+    n = lib.dppo_update_launches(ctypes.byref(dims), B)
+    if n < 0:
+        check(n)
+    return n
 
 
 def update_nparts(dims, B):

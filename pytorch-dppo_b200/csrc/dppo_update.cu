@@ -1628,12 +1628,32 @@ __device__ __noinline__ void heads_dw(float* __restrict__ gWmu, float* __restric
 // whole forward of one network on the tile (model.py:35-45)
 // ---------------------------------------------------------------------------
 // `next`: the network whose first layers are prefetched into the staging region while this one's heads run
+// features [0, nf) of a sample-major shared-memory array (32 rows of ld floats, ld a multiple of 4) -> feature-major
+// rows of Z, this tile's 32 columns.  A warp takes four features at a time: lane = sample, one 128-bit load along the
+// features, four stores of a whole 128-byte row each.
+__device__ __forceinline__ void z_dump(float* zrow0, int zld, const float* src, int ld, int nf) {
+    const int warp = threadIdx.x >> 5, m = threadIdx.x & 31;
+    for (int f = 4 * warp; f < nf; f += 4 * (UPD_THREADS / 32)) {
+        const float4 v = *reinterpret_cast<const float4*>(src + m * ld + f);
+        float* z = zrow0 + (size_t)f * zld + m;
+        z[0] = v.x;
+        if (f + 1 < nf) z[zld] = v.y;
+        if (f + 2 < nf) z[2 * (size_t)zld] = v.z;
+        if (f + 3 < nf) z[3 * (size_t)zld] = v.w;
+    }
+}
+
 __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, const UpdArgs& P, float* S, float* mu_out,
                                             float* v_out, int tick, unsigned ph, uint32_t tmem, const CUtensorMap* maps,
-                                            const Net* next) {
+                                            const Net* next, int zcol = -1) {
     const dppo_dims& d = P.d;
     float* stage = S + P.o_stage;
     uint64_t* bars = reinterpret_cast<uint64_t*>(S + P.o_bars);
+    // batch-level dW (zcol >= 0: this tile's columns of Z): every hidden activation is copied out feature-major right
+    // after its layer, so that the stores drain while the next layer computes instead of in one burst
+    auto zd = [&](int zr, const float* src, int ld, int nf) {
+        if (zcol >= 0) z_dump(P.Z + (size_t)zr * P.Bp + zcol, P.Bp, src, ld, nf);
+    };
     if (P.small_first) {
         mbar_wait(&bars[0], ph & 1u);                       // this network's W1 and V1 have landed (prefetched)
         ph ^= 1u;
@@ -1655,12 +1675,16 @@ __device__ __forceinline__ unsigned net_forward(const Net& nw, const HeadS& hs, 
                              maps ? maps + 3 : nullptr);
         K2_TICK(tick + 1);
     }
+    zd(P.zr_h1, S + P.o_h1, P.ldH1, d.H1);
+    zd(P.zr_g1, S + P.o_g1, P.ldG1, d.G1);
     ph = fwd_layer<true>(nw.W2, nw.b2, d.H2, d.H1, S + P.o_h1, P.ldH1, S + P.o_h2, P.ldH2, stage, P.SF, bars, ph, tmem,
                          maps ? maps + 0 : nullptr);
     K2_TICK(tick + 2);
+    zd(P.zr_h2, S + P.o_h2, P.ldH2, d.H2);
     ph = fwd_layer<true>(nw.V2, nw.c2, d.G2, d.G1, S + P.o_g1, P.ldG1, S + P.o_g2, P.ldG2, stage, P.SF, bars, ph, tmem,
                          maps ? maps + 1 : nullptr);
     K2_TICK(tick + 3);
+    zd(P.zr_g2, S + P.o_g2, P.ldG2, d.G2);
     if (P.small_first && next != nullptr) first_layers_prefetch(stage, next->W1, next->V1, d, &bars[0]);
     heads_fwd(hs, d.A, d.H2, d.G2, S + P.o_h2, P.ldH2, S + P.o_g2, P.ldG2, mu_out, P.ldA, v_out);
     K2_TICK(tick + 4);
@@ -1717,21 +1741,6 @@ __device__ void block_sum3(float a, float b, float c, float* r0, float* r12, flo
     }
     oa = r0[0]; ob = r1[0]; oc = r2[0];
     __syncthreads();
-}
-
-// features [0, nf) of a sample-major shared-memory array (32 rows of ld floats, ld a multiple of 4) -> feature-major
-// rows of Z, this tile's 32 columns.  A warp takes four features at a time: lane = sample, one 128-bit load along the
-// features, four stores of a whole 128-byte row each.
-__device__ __forceinline__ void z_dump(float* zrow0, int zld, const float* src, int ld, int nf) {
-    const int warp = threadIdx.x >> 5, m = threadIdx.x & 31;
-    for (int f = 4 * warp; f < nf; f += 4 * (UPD_THREADS / 32)) {
-        const float4 v = *reinterpret_cast<const float4*>(src + m * ld + f);
-        float* z = zrow0 + (size_t)f * zld + m;
-        z[0] = v.x;
-        if (f + 1 < nf) z[zld] = v.y;
-        if (f + 2 < nf) z[2 * (size_t)zld] = v.z;
-        if (f + 3 < nf) z[3 * (size_t)zld] = v.w;
-    }
 }
 
 __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __grid_constant__ UpdArgs P) {
@@ -2141,15 +2150,9 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
         // theta_old == theta and the old network's outputs are the new network's, bit for bit
         if (run_old)
             ph = net_forward(no, hs_old, P, S, S + P.o_muo, S + P.o_vo, 3, ph, tmem, P.use_ts ? P.map_fwd[1] : nullptr, &nw);              // train.py:142
-        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr, nullptr);                    // train.py:145 / ppo.py:148
+        ph = net_forward(nw, hs_new, P, S, S + P.o_mu, S + P.o_v, 8, ph, tmem, P.use_ts ? P.map_fwd[0] : nullptr, nullptr,
+                         P.dwg ? tile * UPD_ROWS : -1);                    // train.py:145 / ppo.py:148
         if (P.fwd_only) { write_policy_outputs(); continue; }
-        if (P.dwg) {                                                      // batch-level dW: the layers' inputs, feature-major
-            float* zc = P.Z + tile * UPD_ROWS;
-            z_dump(zc + (size_t)P.zr_h1 * P.Bp, P.Bp, S + P.o_h1, P.ldH1, d.H1);
-            z_dump(zc + (size_t)P.zr_g1 * P.Bp, P.Bp, S + P.o_g1, P.ldG1, d.G1);
-            z_dump(zc + (size_t)P.zr_h2 * P.Bp, P.Bp, S + P.o_h2, P.ldH2, d.H2);
-            z_dump(zc + (size_t)P.zr_g2 * P.Bp, P.Bp, S + P.o_g2, P.ldG2, d.G2);
-        }
         if (same_old) {
             for (int e = threadIdx.x; e < UPD_ROWS * P.ldA; e += UPD_THREADS) S[P.o_muo + e] = S[P.o_mu + e];
             for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
@@ -2172,11 +2175,18 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
             z_dump(zc + (size_t)P.zr_d2p * P.Bp, P.Bp, S + P.o_h2, P.ldH2, d.H2);
             z_dump(zc + (size_t)P.zr_d2v * P.Bp, P.Bp, S + P.o_g2, P.ldG2, d.G2);
             K2_TICK(17);
-            ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, &P.map_dx[0], tmem);   // h1 <- dz1
-            K2_TICK(20);
-            ph = dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, &P.map_dx[1], tmem);   // g1 <- dz1 (value)
-            z_dump(zc + (size_t)P.zr_d1p * P.Bp, P.Bp, S + P.o_h1, P.ldH1, d.H1);
-            z_dump(zc + (size_t)P.zr_d1v * P.Bp, P.Bp, S + P.o_g1, P.ldG1, d.G1);
+            // the wider trunk first: its rows of dz1 drain while the other trunk's dX runs
+            const bool vfirst = d.G1 >= d.H1;
+            for (int pass = 0; pass < 2; ++pass) {
+                if ((pass == 0) == vfirst) {
+                    ph = dx_layer(nw.V2, d.G2, d.G1, S + P.o_g2, P.ldG2, S + P.o_g1, P.ldG1, stage, P.SF, bars, ph, &P.map_dx[1], tmem);   // g1 <- dz1 (value)
+                    z_dump(zc + (size_t)P.zr_d1v * P.Bp, P.Bp, S + P.o_g1, P.ldG1, d.G1);
+                } else {
+                    ph = dx_layer(nw.W2, d.H2, d.H1, S + P.o_h2, P.ldH2, S + P.o_h1, P.ldH1, stage, P.SF, bars, ph, &P.map_dx[0], tmem);   // h1 <- dz1
+                    z_dump(zc + (size_t)P.zr_d1p * P.Bp, P.Bp, S + P.o_h1, P.ldH1, d.H1);
+                }
+                K2_TICK(20 + pass);
+            }
             __syncthreads();                                              // the next tile zeroes the activation area
             K2_TICK(21);
             continue;
@@ -2480,7 +2490,9 @@ DwgGeom dwg_geom(const dppo_dims& d, int B) {
 }
 size_t dwg_scratch_bytes(const DwgGeom& G) { return sizeof(float) * ((size_t)G.rows * G.Bp + 4 * (size_t)G.nk2) + 256; }
 
-// the per-device Z buffer (grown on demand; never while the stream is being captured into a graph)
+// The per-device Z buffer: grown on demand, never while the stream is being captured into a graph, and a buffer that
+// has been handed out is never freed (a captured graph may still point at it - the tensor maps and the pointer are
+// baked into its kernel nodes), so growing leaves the smaller buffer allocated.
 void* g_zbuf[64] = {nullptr};
 size_t g_zcap[64] = {0};
 int dwg_scratch(int dev, size_t bytes, cudaStream_t stream, float** out) {
@@ -2488,12 +2500,9 @@ int dwg_scratch(int dev, size_t bytes, cudaStream_t stream, float** out) {
         cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
         if (stream != nullptr && cudaStreamIsCapturing(stream, &st) == cudaSuccess && st != cudaStreamCaptureStatusNone)
             return DPPO_E_SCRATCH;                  // dppo_update_prepare (or one plain call) must come before the capture
-        if (g_zbuf[dev]) {
-            DPPO_CUDA_TRY(cudaDeviceSynchronize());
-            DPPO_CUDA_TRY(cudaFree(g_zbuf[dev]));
-            g_zbuf[dev] = nullptr; g_zcap[dev] = 0;
-        }
-        DPPO_CUDA_TRY(cudaMalloc(&g_zbuf[dev], bytes));
+        void* p = nullptr;
+        DPPO_CUDA_TRY(cudaMalloc(&p, bytes));
+        g_zbuf[dev] = p;
         g_zcap[dev] = bytes;
     }
     *out = (float*)g_zbuf[dev];
@@ -2575,6 +2584,19 @@ extern "C" int dppo_update_nparts(const dppo_dims* d, int B) {
     int TM, np;
     pick_tiling(B, &TM, &np);
     return dwg_geom(*d, B).on ? DWG_KSPLIT : np;
+}
+
+extern "C" int dppo_update_set_batch_dw(int on) {
+    const int prev = dwg_enabled() ? 1 : 0;
+    g_dwg_enabled = on ? 1 : 0;
+    return prev;
+}
+
+extern "C" int dppo_update_launches(const dppo_dims* d, int B) {
+    const int rc = check_dims(d);
+    if (rc) return rc;
+    if (B < 1) return DPPO_E_BADARG;
+    return dwg_geom(*d, B).on ? 2 : 1;
 }
 
 extern "C" size_t dppo_update_partials_bytes(const dppo_dims* d, int B) {

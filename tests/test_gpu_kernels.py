@@ -341,6 +341,44 @@ def test_update_dppo_vs_oracle(nv, case):
             assert_close_scaled(got[k], grads[k], 1e-5, k)
 
 
+@pytest.mark.parametrize("case,flavour", [((17, 6, (100, 100, 500, 100), 65536, 4096), "dppo"),
+                                          ((17, 6, (100, 100, 500, 100), 8192, 6000), "dppo"),     # CTAs loop over tiles
+                                          ((15, 3, (100, 100, 500, 100), 2048, 2048), "ppo"),
+                                          ((17, 6, (64, 64, 64, 64), 4096, 1024 + 5), "dppo")])      # ragged last tile
+def test_update_two_launch_form_matches_single_launch(nv, case, flavour):
+    """Large minibatches take two launches (the update kernel leaves layer inputs and dz in the library's buffer, a
+    second pass forms every weight gradient as a GEMM over 4 ranges of samples).  Same gradients and loss sums as the
+    single-launch form (per-CTA dW, one partial per CTA) to fp32 reduction-order accuracy, 4 partial rows instead of
+    one per CTA, and bit-repeatable."""
+    O, A, widths, T, B = case
+    fl = nv.FLAVOUR_DPPO if flavour == "dppo" else nv.FLAVOUR_PPO
+    s = _setup_update(nv, O, A, widths, T, B, 11, fl)
+    dims = s[0]
+    prev = nv.update_set_batch_dw(True)
+    try:
+        assert nv.update_launches(dims, B) == 2 and nv.update_nparts(dims, B) == 4
+        G2, L2 = _run_update(nv, fl, *s, ent=0.01)
+        G2b, L2b = _run_update(nv, fl, *s, ent=0.01)
+        nv.update_set_batch_dw(False)
+        assert nv.update_launches(dims, B) == 1 and nv.update_nparts(dims, B) > 4
+        G1, L1 = _run_update(nv, fl, *s, ent=0.01)
+    finally:
+        nv.update_set_batch_dw(bool(prev))
+    assert torch.equal(G2, G2b) and torch.equal(L2, L2b)
+    off, size = s[1], s[2]
+    a, b = from_flat(G2, off, size, dims.shapes()), from_flat(G1, off, size, dims.shapes())
+    for k in orc.PARAM_ORDER:
+        assert_close_scaled(a[k], b[k], 2e-6, k)
+    assert torch.allclose(L2, L1, rtol=2e-6, atol=1e-9)
+    # small minibatches and the FP32-pipe path keep the single-launch form
+    assert nv.update_launches(dims, 512) == 1
+    p0 = nv.update_set_path(nv.K2_PATH_FP32)
+    try:
+        assert nv.update_launches(dims, B) == 1
+    finally:
+        nv.update_set_path(p0)
+
+
 @pytest.mark.parametrize("case", CASES)
 def test_update_ppo_vs_oracle(nv, case):
     O, A, widths, T, B = case
