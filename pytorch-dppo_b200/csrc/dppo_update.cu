@@ -2124,6 +2124,28 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
                     else for (int e = threadIdx.x; e < UPD_ROWS; e += UPD_THREADS) S[P.o_vo + e] = S[P.o_v + e];
                     __syncthreads();
                 }
+                if (P.dwg) {
+                    // batch-level dW: this trunk's layer inputs (a1, a2) and dz leave for Z as they appear; no dW here
+                    float* zc = P.Z + tile * UPD_ROWS;
+                    z_dump(zc + (size_t)(trunk ? P.zr_g1 : P.zr_h1) * P.Bp, P.Bp, a1, ld1, N1);
+                    z_dump(zc + (size_t)(trunk ? P.zr_g2 : P.zr_h2) * P.Bp, P.Bp, a2, ld2, N2);
+                    if (trunk == 0) loss_policy(); else loss_value();
+                    __syncthreads();
+                    if (trunk == 0) {
+                        z_dump(zc + (size_t)P.zr_dmu * P.Bp, P.Bp, S + P.o_dmu, P.ldA, d.A);
+                        z_dump(zc + (size_t)(P.zr_dmu + d.A) * P.Bp, P.Bp, S + P.o_muo, P.ldA, d.A);
+                        head_dx(hs_new.Wmu, hs_new.ldw, d.A, d.H2, S + P.o_dmu, P.ldA, a2, ld2);              // a2 <- dz2
+                    } else {
+                        z_dump(zc + (size_t)P.zr_dv * P.Bp, P.Bp, S + P.o_dv, 4, 1);
+                        head_dx(hs_new.Wv, 0, 1, d.G2, S + P.o_dv, 4, a2, ld2);
+                    }
+                    __syncthreads();
+                    z_dump(zc + (size_t)(trunk ? P.zr_d2v : P.zr_d2p) * P.Bp, P.Bp, a2, ld2, N2);
+                    ph = dx_layer(trunk ? nw.V2 : nw.W2, N2, N1, a2, ld2, a1, ld1, stage, P.SF, bars, ph, &P.map_dx[trunk], tmem);   // a1 <- dz1
+                    z_dump(zc + (size_t)(trunk ? P.zr_d1v : P.zr_d1p) * P.Bp, P.Bp, a1, ld1, N1);
+                    __syncthreads();                          // the buffers are zeroed for the other trunk / the next tile
+                    continue;
+                }
                 if (trunk == 0) {
                     loss_policy();
                     __syncthreads();
@@ -2447,8 +2469,7 @@ constexpr int MAX_DEVICES = 64;
 
 // ---- batch-level dW (see UpdArgs::dwg) ------------------------------------------------------------------------
 // Used when every hidden layer runs on the tensor-core routines (their epilogues hold a feature's 16 samples in
-// registers, which is the layout Z wants), the trunks have their own activation buffers and the minibatch is large
-// enough for the second launch to pay.  The decision depends on (dims, B, the K2 path, DPPO_K2_DWG) only, so
+// registers, which is the layout Z wants) and the minibatch is large enough for the second launch to pay.  The decision depends on (dims, B, the K2 path, DPPO_K2_DWG) only, so
 // dppo_update_nparts and dppo_update_fused agree.
 constexpr int DWG_KSPLIT = 4;                       // ranges of samples = gradient partials handed to K3
 constexpr int DWG_MIN_B = 1024;
@@ -2468,7 +2489,7 @@ DwgGeom dwg_geom(const dppo_dims& d, int B) {
     int np;
     pick_tiling(B, &Q.TM, &np);
     plan(Q);
-    if (Q.trunk_serial || (size_t)2 * Q.SF * sizeof(float) < (size_t)TS_BYTES) return G;
+    if ((size_t)2 * Q.SF * sizeof(float) < (size_t)TS_BYTES) return G;
     if (!ts_eligible(d.H2, d.H1) || !ts_eligible(d.G2, d.G1)) return G;
     const bool first_small = Q.small_first && Q.first_ts && d.H1 <= 512 && d.G1 <= 512;
     if (!first_small && !(ts_eligible(d.H1, d.O) && ts_eligible(d.G1, d.O))) return G;
