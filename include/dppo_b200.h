@@ -137,8 +137,8 @@ int dppo_welford_shared(const float* obs, float* out, int64_t T, int O,
  * Deterministic: no atomics, fixed reduction order. */
 /* Large minibatches of nets whose hidden layers all run on the tensor-core routines take two launches: the update
  * kernel leaves every layer's input and dz feature-major in an internal per-device buffer, a second pass forms all
- * weight gradients from it as batch-level GEMMs over 4 ranges of samples - dppo_update_nparts is then 4 instead of
- * one partial per CTA.  The buffer is allocated by dppo_update_prepare (or by the first plain call; a call that
+ * weight gradients from it as batch-level GEMMs over a few ranges of samples - dppo_update_nparts is then that number
+ * of ranges (<= 8) instead of one partial per CTA.  The buffer is allocated by dppo_update_prepare (or by the first plain call; a call that
  * finds it missing while its stream is being captured returns DPPO_E_SCRATCH); it is shared by all calls on a device,
  * which must therefore be ordered on one stream, and it only grows (captured graphs keep pointing at the buffer they
  * were captured with).  DPPO_K2_DWG=0 in the environment or dppo_update_set_batch_dw(0) keeps the single-launch form -

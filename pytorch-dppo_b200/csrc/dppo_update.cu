@@ -125,13 +125,15 @@ struct UpdArgs {
     // batch-level dW (dwg): 0 off.  1: the update kernel forms no dW; it leaves every layer's input and every dz
     // feature-major in Z ([rows][Bp], Bp = 32 * tiles) and its loss sums in zloss.  2: the dW pass over Z - CTA =
     // (range of samples, parameter, 32 input features, 128 outputs), one wide-layer call whose "weights" are dz^T.
-    int dwg, Bp, dwg_units, dwg_chunk, zloss_rows;
+    int dwg, Bp, dwg_units, dwg_chunk, zloss_rows;   // dwg_chunk: samples per range (the grid is units x ranges)
     float* Z;
     float* zloss;                                   // [zloss_rows][4]
     int zr_x, zr_h1, zr_g1, zr_h2, zr_g2;           // first rows of the input operands (Kf rows, the ones row, pad to 32)
     int zr_d1p, zr_d1v, zr_d2p, zr_d2v, zr_dmu, zr_dv;   // first rows of dz: p_fc1, v_fc1, p_fc2, v_fc2, [dmu | dls], dv
-    alignas(64) CUtensorMap map_dz[6];              // dz^T of v_fc2, p_fc2, v_fc1, p_fc1, mu (+ log_std), v: box 32 (samples) x 128 (n)
-    alignas(64) CUtensorMap map_in[5];              // the inputs x^T, h1^T, g1^T, h2^T, g2^T (+ ones rows): box 32 (samples) x 32 (kf), no swizzle
+    // tile operands (box 32 samples x 128 rows, SWIZZLE_128B): dz^T of v_fc2, p_fc2, v_fc1, p_fc1; for the heads h2^T, g2^T (+ ones)
+    alignas(64) CUtensorMap map_dz[6];
+    // 32-row operands (box 32 x 32, no swizzle): x^T, h1^T, g1^T (+ ones rows); for the heads [dmu | dls]^T and dv^T
+    alignas(64) CUtensorMap map_in[5];
     alignas(64) CUtensorMap map_fwd[2][4];          // [theta, theta_old][W2, V2, W1, V1]: box 32 (k) x 128 (n), SWIZZLE_128B
     alignas(64) CUtensorMap map_dx[2];              // theta's W2, V2 for dX: box 128 (k) x 32 (n), no swizzle
 };
@@ -641,11 +643,13 @@ constexpr int TS_PH_RF = 10;
 //              of samples, and out[kf][n] = dW[n][kf] goes to this split's partial bucket instead of the activations:
 //              gW[n * ldw + kf0 + kf] for kf0 + kf < Kf, the column kf0 + kf == Kf (the ones row) is the bias gradient
 //              gb[n]; rows n >= n1 keep only that column (gb2[n - n1] + add2: d log_std rides with the mu head).
+//              tr: the roles are swapped (the heads: few dz rows, many inputs): the tile's rows are INPUT features (row Kf =
+//              the ones row) and the 32-row operand is a block of dz rows, out[m][n] = dW[m][n] goes to gW[m * ldw + n].
 //              The 32-row operand's blocks arrive by TMA too (bmap, rows brow0.., raw tiles in braw) on the same barrier
 //              as the dz tiles; the sample warps split them from shared memory as in every other layer.
 struct TsX {
     int kofs, row0;
-    int dwg;
+    int dwg, tr;
     const CUtensorMap* bmap; int brow0; float* braw;   // dwg: the 32-row operand's blocks by TMA (box 32 x 32) into braw[slot][block][32][32]
     float *gW, *gb, *gb2;
     int ldw, kf0, Kf, n1;
@@ -863,6 +867,20 @@ __device__ __noinline__ unsigned ts_layer(const CUtensorMap* map, const float* _
                         const float h = *ap;
                         sum[j] *= 1.f - h * h;
                         *ap = sum[j];
+                    }
+                }
+            } else if (X.dwg && X.tr) {
+                const int n = X.row0 + f;                   // input feature (n == Kf: the ones row -> bias gradients)
+                if (n <= X.Kf) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const int m = X.kf0 + c0 + j;       // dz row
+                        if (m < X.n1) {
+                            if (n < X.Kf) X.gW[(size_t)m * X.ldw + n] = sum[j];
+                            else X.gb[m] = sum[j];
+                        } else if (X.gb2 != nullptr && m < 2 * X.n1 && n == X.Kf) {
+                            X.gb2[m - X.n1] = sum[j] + X.add2;
+                        }
                     }
                 }
             } else if (X.dwg) {
@@ -1798,26 +1816,26 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
             }
         }
         for (int p = 0; p < 6 && ns > 0; ++p) {
-            int Np, Kf, zin, n1;
+            // hidden layers (p < 4): tile rows = dz rows (outputs n), 32-row operand = input features.
+            // heads (p >= 4): swapped - tile rows = input features (+ the ones row), 32-row operand = the few dz rows.
+            int rows_t, rows_b, Kf, n1, im;                           // tile-operand rows, 32-row-operand rows
             float *gW, *gb, *gb2 = nullptr;
-            int im;                                                   // which input operand (map_in)
-            if (p == 0) { Np = d.G2; Kf = d.G1; zin = P.zr_g1; im = 2; gW = gs.V2; gb = gs.c2; n1 = Np; }
-            else if (p == 1) { Np = d.H2; Kf = d.H1; zin = P.zr_h1; im = 1; gW = gs.W2; gb = gs.b2; n1 = Np; }
-            else if (p == 2) { Np = d.G1; Kf = d.O; zin = P.zr_x; im = 0; gW = gs.V1; gb = gs.c1; n1 = Np; }
-            else if (p == 3) { Np = d.H1; Kf = d.O; zin = P.zr_x; im = 0; gW = gs.W1; gb = gs.b1; n1 = Np; }
-            else if (p == 4) { Np = 2 * d.A; Kf = d.H2; zin = P.zr_h2; im = 3; gW = gs.Wmu; gb = gs.bmu; gb2 = gs.ls; n1 = d.A; }
-            else { Np = 1; Kf = d.G2; zin = P.zr_g2; im = 4; gW = gs.Wv; gb = gs.bv; n1 = Np; }
-            const int kfb = (Kf + 1 + 31) >> 5, nt = (Np + 127) >> 7;
+            if (p == 0) { rows_t = d.G2; Kf = d.G1; rows_b = Kf + 1; im = 2; gW = gs.V2; gb = gs.c2; n1 = rows_t; }
+            else if (p == 1) { rows_t = d.H2; Kf = d.H1; rows_b = Kf + 1; im = 1; gW = gs.W2; gb = gs.b2; n1 = rows_t; }
+            else if (p == 2) { rows_t = d.G1; Kf = d.O; rows_b = Kf + 1; im = 0; gW = gs.V1; gb = gs.c1; n1 = rows_t; }
+            else if (p == 3) { rows_t = d.H1; Kf = d.O; rows_b = Kf + 1; im = 0; gW = gs.W1; gb = gs.b1; n1 = rows_t; }
+            else if (p == 4) { Kf = d.H2; rows_t = Kf + 1; rows_b = 2 * d.A; im = 3; gW = gs.Wmu; gb = gs.bmu; gb2 = gs.ls; n1 = d.A; }
+            else { Kf = d.G2; rows_t = Kf + 1; rows_b = 1; im = 4; gW = gs.Wv; gb = gs.bv; n1 = 1; }
+            const int kfb = (rows_b + 31) >> 5, nt = (rows_t + 127) >> 7;
             if (u >= kfb * nt) { u -= kfb * nt; continue; }
             const int t = u / kfb, b = u - t * kfb;
             TsX x = {};
-            x.dwg = 1; x.kofs = s0; x.row0 = 128 * t;
+            x.dwg = 1; x.tr = p >= 4 ? 1 : 0; x.kofs = s0; x.row0 = 128 * t;
             x.gW = gW; x.gb = gb; x.gb2 = gb2; x.ldw = Kf; x.kf0 = 32 * b; x.Kf = Kf; x.n1 = n1;
             x.add2 = (P.flavour == DPPO_FLAVOUR_PPO && split == 0) ? -P.ent_coeff : 0.f;     // ppo.py:152-153,167
             x.bmap = &P.map_in[im]; x.brow0 = 32 * b; x.braw = S;                           // (the activation area is free in this pass)
-            ph = ts_layer<false>(&P.map_dz[p], nullptr, min(128, Np - 128 * t), ns, P.Z + (size_t)(zin + 32 * b) * P.Bp + s0, P.Bp,
-                                 nullptr, 0, reinterpret_cast<unsigned char*>(S + P.o_stage),
-                                 reinterpret_cast<uint64_t*>(S + P.o_bars), ph, tmem, x);
+            ph = ts_layer<false>(&P.map_dz[p], nullptr, min(128, rows_t - 128 * t), ns, nullptr, 0, nullptr, 0,
+                                 reinterpret_cast<unsigned char*>(S + P.o_stage), reinterpret_cast<uint64_t*>(S + P.o_bars), ph, tmem, x);
             break;
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -2471,9 +2489,9 @@ constexpr int MAX_DEVICES = 64;
 // Used when every hidden layer runs on the tensor-core routines (their epilogues hold a feature's 16 samples in
 // registers, which is the layout Z wants) and the minibatch is large enough for the second launch to pay.  The decision depends on (dims, B, the K2 path, DPPO_K2_DWG) only, so
 // dppo_update_nparts and dppo_update_fused agree.
-constexpr int DWG_KSPLIT = 4;                       // ranges of samples = gradient partials handed to K3
+constexpr int DWG_MAX_SPLIT = 8;                    // ranges of samples = gradient partials handed to K3 (chosen per shape)
 constexpr int DWG_MIN_B = 1024;
-struct DwgGeom { int on, Bp, rows, units, chunk, nk2; int zr[11]; };
+struct DwgGeom { int on, Bp, rows, units, chunk, nk2, ksplit; int zr[11]; };
 int g_dwg_enabled = -1;
 bool dwg_enabled() {
     if (g_dwg_enabled < 0) g_dwg_enabled = getenv("DPPO_K2_DWG") ? atoi(getenv("DPPO_K2_DWG")) : 1;   // (2: timing experiment, first launch only)
@@ -2504,9 +2522,20 @@ DwgGeom dwg_geom(const dppo_dims& d, int B) {
     G.zr[5] = dz_rows(d.H1); G.zr[6] = dz_rows(d.G1); G.zr[7] = dz_rows(d.H2); G.zr[8] = dz_rows(d.G2);
     G.zr[9] = dz_rows(2 * d.A); G.zr[10] = dz_rows(1);
     G.rows = r;
-    auto units = [](int Np, int Kf) { return ((Kf + 1 + 31) >> 5) * ((Np + 127) >> 7); };
-    G.units = units(d.G2, d.G1) + units(d.H2, d.H1) + units(d.G1, d.O) + units(d.H1, d.O) + units(2 * d.A, d.H2) + units(1, d.G2);
-    G.chunk = ((G.Bp + DWG_KSPLIT - 1) / DWG_KSPLIT + 63) & ~63;
+    auto units = [](int rows_t, int rows_b) { return ((rows_b + 31) >> 5) * ((rows_t + 127) >> 7); };
+    G.units = units(d.G2, d.G1 + 1) + units(d.H2, d.H1 + 1) + units(d.G1, d.O + 1) + units(d.H1, d.O + 1) +
+              units(d.H2 + 1, 2 * d.A) + units(d.G2 + 1, 1);
+    // ranges of samples: every CTA of the pass costs ~5 k cycles (fill, epilogue) + ~1.3 k per pair of k-blocks of its
+    // range, the grid runs in waves of one CTA per SM, K3 pays ~0.3 k per partial bucket
+    const int sms = dppo_sm_count();
+    long best = -1;
+    for (int k = 1; k <= DWG_MAX_SPLIT; ++k) {
+        const int chunk = ((G.Bp + k - 1) / k + 63) & ~63;
+        if ((long)chunk * (k - 1) >= G.Bp) continue;               // the last range would be empty
+        const long waves = ((long)G.units * k + sms - 1) / sms;
+        const long cost = waves * (5000 + 1300L * (chunk / 64)) + 300L * k;
+        if (best < 0 || cost < best) { best = cost; G.ksplit = k; G.chunk = chunk; }
+    }
     return G;
 }
 size_t dwg_scratch_bytes(const DwgGeom& G) { return sizeof(float) * ((size_t)G.rows * G.Bp + 4 * (size_t)G.nk2) + 256; }
@@ -2535,14 +2564,17 @@ const DzMaps* dz_maps(int dev, float* Z, const dppo_dims& d, const DwgGeom& G) {
     DzMaps& e = g_dzmaps[dev];
     if (e.Z == Z && e.Bp == G.Bp && e.dev == dev && memcmp(&e.d, &d, sizeof(d)) == 0 && e.ok) return &e;
     e.dev = dev; e.Z = Z; e.d = d; e.Bp = G.Bp;
-    const int rows[6] = {G.zr[8], G.zr[7], G.zr[6], G.zr[5], G.zr[9], G.zr[10]};          // v_fc2, p_fc2, v_fc1, p_fc1, mu, v
-    const int n[6] = {d.G2, d.H2, d.G1, d.H1, 2 * d.A, 1};
+    // tile operands: dz^T of v_fc2, p_fc2, v_fc1, p_fc1; the heads take their INPUTS (h2^T, g2^T with the ones row) here
+    const int rows[6] = {G.zr[8], G.zr[7], G.zr[6], G.zr[5], G.zr[3], G.zr[4]};
+    const int n[6] = {d.G2, d.H2, d.G1, d.H1, d.H2 + 1, d.G2 + 1};
     bool ok = true;
     for (int i = 0; i < 6 && ok; ++i)
         ok = make_wmap(&e.m[i], Z + (size_t)rows[i] * G.Bp, n[i], G.Bp, TC_KB, 128, CU_TENSOR_MAP_SWIZZLE_128B);
-    const int kf[5] = {d.O, d.H1, d.G1, d.H2, d.G2};                                      // inputs: Kf rows + ones, padded to 32
+    // 32-row operands: the inputs x^T, h1^T, g1^T (Kf rows + ones, padded to 32); for the heads [dmu | dls]^T and dv^T
+    const int brow[5] = {G.zr[0], G.zr[1], G.zr[2], G.zr[9], G.zr[10]};
+    const int bn[5] = {(d.O + 1 + 31) & ~31, (d.H1 + 1 + 31) & ~31, (d.G1 + 1 + 31) & ~31, 2 * d.A, 1};
     for (int i = 0; i < 5 && ok; ++i)
-        ok = make_wmap(&e.in[i], Z + (size_t)G.zr[i] * G.Bp, (kf[i] + 1 + 31) & ~31, G.Bp, TC_KB, 32, CU_TENSOR_MAP_SWIZZLE_NONE);
+        ok = make_wmap(&e.in[i], Z + (size_t)brow[i] * G.Bp, bn[i], G.Bp, TC_KB, 32, CU_TENSOR_MAP_SWIZZLE_NONE);
     e.ok = ok;
     return &e;
 }
@@ -2604,7 +2636,8 @@ extern "C" int dppo_update_nparts(const dppo_dims* d, int B) {
     if (B < 1) return DPPO_E_BADARG;
     int TM, np;
     pick_tiling(B, &TM, &np);
-    return dwg_geom(*d, B).on ? DWG_KSPLIT : np;
+    const DwgGeom G = dwg_geom(*d, B);
+    return G.on ? G.ksplit : np;
 }
 
 extern "C" int dppo_update_set_batch_dw(int on) {
@@ -2626,7 +2659,8 @@ extern "C" size_t dppo_update_partials_bytes(const dppo_dims* d, int B) {
     fill_layout(*d, L);
     int TM, np;
     pick_tiling(B, &TM, &np);
-    if (dwg_geom(*d, B).on) np = DWG_KSPLIT;
+    const DwgGeom G = dwg_geom(*d, B);
+    if (G.on) np = G.ksplit;
     return sizeof(float) * (size_t)np * L.P_pad;
 }
 
@@ -2679,7 +2713,7 @@ static int plan_and_launch(UpdArgs& P, const dppo_dims* d, int B, const float* t
     DPPO_LAUNCH_CHECK();
     if (G.on && g_dwg_enabled != 2) {                           // second launch: all weight gradients from Z
         P.dwg = 2;
-        update_fused_kernel<<<G.units * DWG_KSPLIT, UPD_THREADS, smem, (cudaStream_t)stream_>>>(P);
+        update_fused_kernel<<<G.units * G.ksplit, UPD_THREADS, smem, (cudaStream_t)stream_>>>(P);
         DPPO_LAUNCH_CHECK();
     }
     return 0;

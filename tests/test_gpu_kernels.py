@@ -347,20 +347,20 @@ def test_update_dppo_vs_oracle(nv, case):
                                           ((17, 6, (64, 64, 64, 64), 4096, 1024 + 5), "dppo")])      # ragged last tile
 def test_update_two_launch_form_matches_single_launch(nv, case, flavour):
     """Large minibatches take two launches (the update kernel leaves layer inputs and dz in the library's buffer, a
-    second pass forms every weight gradient as a GEMM over 4 ranges of samples).  Same gradients and loss sums as the
-    single-launch form (per-CTA dW, one partial per CTA) to fp32 reduction-order accuracy, 4 partial rows instead of
-    one per CTA, and bit-repeatable."""
+    second pass forms every weight gradient as a GEMM over a few ranges of samples).  Same gradients and loss sums as
+    the single-launch form (per-CTA dW, one partial per CTA) to fp32 reduction-order accuracy, at most 8 partial rows
+    instead of one per CTA, and bit-repeatable."""
     O, A, widths, T, B = case
     fl = nv.FLAVOUR_DPPO if flavour == "dppo" else nv.FLAVOUR_PPO
     s = _setup_update(nv, O, A, widths, T, B, 11, fl)
     dims = s[0]
     prev = nv.update_set_batch_dw(True)
     try:
-        assert nv.update_launches(dims, B) == 2 and nv.update_nparts(dims, B) == 4
+        assert nv.update_launches(dims, B) == 2 and 1 <= nv.update_nparts(dims, B) <= 8
         G2, L2 = _run_update(nv, fl, *s, ent=0.01)
         G2b, L2b = _run_update(nv, fl, *s, ent=0.01)
         nv.update_set_batch_dw(False)
-        assert nv.update_launches(dims, B) == 1 and nv.update_nparts(dims, B) > 4
+        assert nv.update_launches(dims, B) == 1 and nv.update_nparts(dims, B) > 8
         G1, L1 = _run_update(nv, fl, *s, ent=0.01)
     finally:
         nv.update_set_batch_dw(bool(prev))
