@@ -369,7 +369,7 @@ def test_update_two_launch_form_matches_single_launch(nv, case, flavour):
     a, b = from_flat(G2, off, size, dims.shapes()), from_flat(G1, off, size, dims.shapes())
     for k in orc.PARAM_ORDER:
         assert_close_scaled(a[k], b[k], 2e-6, k)
-    assert torch.allclose(L2, L1, rtol=2e-6, atol=1e-9)
+    assert torch.allclose(L2, L1, rtol=1e-5, atol=1e-9)         # fp32 sums of the per-CTA loss terms in different groupings
     # small minibatches and the FP32-pipe path keep the single-launch form
     assert nv.update_launches(dims, 512) == 1
     p0 = nv.update_set_path(nv.K2_PATH_FP32)
