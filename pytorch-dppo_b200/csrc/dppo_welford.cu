@@ -474,6 +474,12 @@ WfGeom wf_geom(int64_t T, int O) {
     if (q.G < 1) q.G = 1;
     q.RPG = WF_RPG;
     while (q.RPG > 1 && (int64_t)q.G * q.RPG > WF_MAX_ROWS) q.RPG -= 2;
+    // rollouts that would not even give every SM two tiles (the benchmark's 65 536 x 17: 134 tiles) are latency bound
+    // - one tile's load, sums, look-back, normalise, store in a row: shorter groups, more tiles in flight
+    {
+        const int64_t tiles33 = ceil_div64(T, (q.G * q.RPG) & ~3) * q.ncb;
+        if (q.RPG == WF_RPG && tiles33 < 2 * (int64_t)dppo_sm_count() && T >= 4 * q.G * 17) q.RPG = 17;
+    }
     q.R = (q.G * q.RPG) & ~3;                       // multiple of 4 rows keeps whole-row tiles 16-byte aligned
     if (q.R < 4) q.R = 4;
     if ((int64_t)q.R > ((T + 3) & ~(int64_t)3)) {   // short rollouts: one tile, fewer rows per group
