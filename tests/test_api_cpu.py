@@ -40,6 +40,35 @@ def test_param_layout_matches_reference_shapes():
         nv.param_layout(nv.Dims(4, 1, 4096, 64, 64, 64))
 
 
+def test_update_planning_abi_without_a_gpu():
+    """dppo_update_nparts / _launches / _partials_bytes are host-side planning (tiling, shared-memory plan, choice of
+    the two-launch form) and must agree with each other without a device."""
+    import b200_native as nv
+    ref = nv.Dims(17, 6, 100, 100, 500, 100)
+    off, size, p_pad = nv.param_layout(ref)
+    prev = nv.update_set_batch_dw(True)
+    try:
+        # large minibatch, every hidden layer on the tensor-core routines: update kernel + batch-level dW pass
+        assert nv.update_launches(ref, 4096) == 2
+        n = nv.update_nparts(ref, 4096)
+        assert 1 <= n <= 8
+        assert nv.lib.dppo_update_partials_bytes(ctypes.byref(ref), 4096) == 4 * n * p_pad
+        # small minibatches keep one launch and one partial per CTA
+        assert nv.update_launches(ref, 64) == 1 and nv.update_nparts(ref, 64) == 16
+        # a 8-wide net has no tensor-core layers: single launch whatever the minibatch
+        tiny = nv.Dims(3, 2, 8, 12, 20, 4)
+        assert nv.update_launches(tiny, 4096) == 1 and nv.update_nparts(tiny, 4096) > 8
+        # Humanoid 256x256 (trunk-serial tiles) takes the two-launch form too
+        hum = nv.Dims(376, 17, 256, 256, 256, 256)
+        assert nv.update_launches(hum, 4096) == 2 and 1 <= nv.update_nparts(hum, 4096) <= 8
+        nv.update_set_batch_dw(False)
+        assert nv.update_launches(ref, 4096) == 1 and nv.update_nparts(ref, 4096) == 128
+    finally:
+        nv.update_set_batch_dw(bool(prev))
+    with pytest.raises(nv.DppoError):
+        nv.update_nparts(ref, 0)
+
+
 def test_no_cpu_path():
     import b200_native as nv
     x = torch.zeros(8)
