@@ -122,7 +122,7 @@ int dppo_welford_shared(const float* obs, float* out, int64_t T, int O,
 /* ---- K2: fused minibatch gather + actor-critic forward/backward + losses --
  * Replaces ReplayMemory.sample (train.py:31-33) + train.py:140-166 (flavour
  * DPPO) or ppo.py:147-172 (flavour PPO) + Model.forward (model.py:35-45) and
- * the autograd backward.  One launch = one minibatch ("epoch" in the
+ * the autograd backward.  One call = one minibatch ("epoch" in the
  * reference's wording).
  *   obs[T*O], act[T*A], adv[T], ret[T], logp_old[T] (PPO flavour only)
  *                         the rollout buffer, struct-of-arrays
