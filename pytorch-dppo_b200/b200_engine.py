@@ -170,6 +170,10 @@ class UpdateEngine:
         if self.flavour == nv.FLAVOUR_DPPO:
             self.theta_old.copy_(self.theta)                       # model_old = copy of model, train.py:128-129
             n += 1
+        if nv.update_nparts(self.dims, self.B) != self.nparts:
+            # the partial buffers were sized for another form of K2 (update_set_path / update_set_batch_dw after __init__)
+            raise RuntimeError("UpdateEngine: the K2 path changed after the engine was built (partials sized for %d rows, "
+                               "K2 now writes %d); build a new engine" % (self.nparts, nv.update_nparts(self.dims, self.B)))
         for k in range(self.E):
             # epoch 0: model_old is a copy of model (train.py:128-129) - passing theta itself lets K2 skip the
             # second forward; from epoch 1 on theta_old is the lagging copy K3 maintains (train.py:164)
