@@ -1328,6 +1328,33 @@ __device__ __noinline__ void head_dx(const float* Ws, int ldw, int N, int K, con
     __syncthreads();
 }
 
+// both heads in ONE pass (every separately compiled phase costs ~2 k cycles of cold instruction fetch whatever its work):
+// items [0, 32*KQa) are the mu head's (m, k-quad) pairs, the rest the value head's; same arithmetic as head_dx
+__device__ __noinline__ void head_dx2(const float* Wa, int ldwa, int Na, int Ka, const float* dOa, int ldda, float* acta, int ldaa,
+                                      const float* Wb, int Kb, const float* dOb, int lddb, float* actb, int ldab) {
+    const int KQa = (Ka + 3) >> 2, KQb = (Kb + 3) >> 2;
+    for (int e = threadIdx.x; e < UPD_ROWS * (KQa + KQb); e += UPD_THREADS) {
+        const bool second = e >= UPD_ROWS * KQa;
+        const int e2 = second ? e - UPD_ROWS * KQa : e, KQ = second ? KQb : KQa;
+        const int m = e2 / KQ, kq = e2 - m * KQ;
+        const int N = second ? 1 : Na, ldw = second ? 0 : ldwa, ldd = second ? lddb : ldda;
+        const float* Ws = second ? Wb : Wa;
+        const float* dOut = second ? dOb : dOa;
+        float* act = (second ? actb + m * ldab : acta + m * ldaa) + 4 * kq;
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int n = 0; n < N; ++n) {
+            const float dd = dOut[m * ldd + n];
+            const float4 w = *reinterpret_cast<const float4*>(Ws + n * ldw + 4 * kq);
+            s.x = fmaf(dd, w.x, s.x); s.y = fmaf(dd, w.y, s.y); s.z = fmaf(dd, w.z, s.z); s.w = fmaf(dd, w.w, s.w);
+        }
+        float4 h = *reinterpret_cast<float4*>(act);
+        h.x = s.x * (1.f - h.x * h.x); h.y = s.y * (1.f - h.y * h.y);
+        h.z = s.z * (1.f - h.z * h.z); h.w = s.w * (1.f - h.w * h.w);
+        *reinterpret_cast<float4*>(act) = h;
+    }
+    __syncthreads();
+}
+
 // ---------------------------------------------------------------------------
 // dW[n][k] (+)= sum_m dOut[m][n] in[m][k];  db[n] (+)= sum_m dOut[m][n]   (m < 32, ascending:
 // fixed order) written to this CTA's partial bucket (global).
@@ -2209,9 +2236,8 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) update_fused_kernel(const __gr
             z_dump(zc + (size_t)P.zr_dmu * P.Bp, P.Bp, S + P.o_dmu, P.ldA, d.A);
             z_dump(zc + (size_t)(P.zr_dmu + d.A) * P.Bp, P.Bp, S + P.o_muo, P.ldA, d.A);      // dls (kept in the mu_old buffer)
             z_dump(zc + (size_t)P.zr_dv * P.Bp, P.Bp, S + P.o_dv, 4, 1);
-            head_dx(hs_new.Wmu, hs_new.ldw, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2);          // h2 <- dz2
-            head_dx(hs_new.Wv, 0, 1, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);                          // g2 <- dz2 (value)
-            __syncthreads();
+            head_dx2(hs_new.Wmu, hs_new.ldw, d.A, d.H2, S + P.o_dmu, P.ldA, S + P.o_h2, P.ldH2,       // h2 <- dz2, g2 <- dz2 (value)
+                     hs_new.Wv, d.G2, S + P.o_dv, 4, S + P.o_g2, P.ldG2);
             z_dump(zc + (size_t)P.zr_d2p * P.Bp, P.Bp, S + P.o_h2, P.ldH2, d.H2);
             z_dump(zc + (size_t)P.zr_d2v * P.Bp, P.Bp, S + P.o_g2, P.ldG2, d.G2);
             K2_TICK(17);
